@@ -1,0 +1,89 @@
+"""tcgen05 GEMM wrapper (``sg_gemm_bf16``) and its plain-PyTorch restatement used on CPU and as the oracle.
+
+``gemm(a, b, ...)`` computes ``acc[m][n] = sum_k A(m,k) B(n,k)`` where ``a`` is stored ``[M][K]`` (or
+``[K][M]`` when ``a_mn``) and ``b`` is stored ``[N][K]`` (or ``[K][N]`` when ``b_mn``), followed by the fused
+epilogue (bias, activation, activation-gradient, accumulate, optional conv-wgrad column permutation).
+Reference behaviour: ``mshadow::dot`` as used by InnerProduct (src/worker/layer.cc:186-213).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import native
+
+ACT_NONE, ACT_RELU, ACT_STANH = 0, 1, 2
+STANH_A, STANH_B = 1.7159047, 0.66666667
+
+
+def act_fwd_ref(x: torch.Tensor, act: int) -> torch.Tensor:
+    if act == ACT_RELU:
+        return torch.clamp_min(x, 0)
+    if act == ACT_STANH:
+        return STANH_A * torch.tanh(STANH_B * x)
+    return x
+
+
+def act_grad_from_output_ref(y: torch.Tensor, act: int) -> torch.Tensor:
+    if act == ACT_RELU:
+        return (y > 0).to(y.dtype)
+    if act == ACT_STANH:
+        return STANH_A * STANH_B - (STANH_B / STANH_A) * y * y
+    return torch.ones_like(y)
+
+
+def gemm_ref(a, b, a_mn=False, b_mn=False, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None,
+             accumulate_into=None, perm=None):
+    """fp32 PyTorch restatement of the kernel (inputs are upcast; result is fp32)."""
+    A = a.float().t() if a_mn else a.float()
+    B = b.float() if b_mn else b.float().t()
+    v = A @ B
+    if bias is not None:
+        v = v + bias.float()
+    v = act_fwd_ref(v, act)
+    if grad_act != ACT_NONE:
+        v = v * act_grad_from_output_ref(aux.float(), grad_act)
+    if perm is not None:
+        c, kk = perm
+        n = v.shape[1]
+        idx = torch.arange(n, device=v.device)
+        out = torch.empty_like(v)
+        out[:, (idx % c) * kk + idx // c] = v
+        v = out
+    if accumulate_into is not None:
+        v = v + accumulate_into.float()
+    return v
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False, b_mn=False,
+         out32: torch.Tensor | None = None, out16: torch.Tensor | None = None,
+         bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
+         aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None):
+    """Launch the sm_100a kernel.  ``a``/``b`` are 2-D bf16 CUDA tensors whose last dim is contiguous
+    (row stride = leading dimension, multiple of 8).  Outputs are written in place."""
+    lib = native.require()
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.stride(-1) == 1 and b.stride(-1) == 1
+    ep = native.GemmEpilogue()
+    if out32 is not None:
+        assert out32.dtype == torch.float32 and out32.stride(-1) == 1
+        ep.d32, ep.ldd32 = out32.data_ptr(), out32.stride(0)
+    if out16 is not None:
+        assert out16.dtype == torch.bfloat16 and out16.stride(-1) == 1
+        ep.d16, ep.ldd16 = out16.data_ptr(), out16.stride(0)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.is_contiguous()
+        ep.bias = bias.data_ptr()
+    ep.act, ep.grad_act = act, grad_act
+    if grad_act != ACT_NONE:
+        assert aux is not None and aux.stride(-1) == 1
+        ep.aux, ep.ldaux = aux.data_ptr(), aux.stride(0)
+        ep.aux_bf16 = 1 if aux.dtype == torch.bfloat16 else 0
+    ep.accumulate = 1 if accumulate else 0
+    if perm is not None:
+        ep.perm_c, ep.perm_kk = perm
+    rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
+                          b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
+    native.check(rc, "sg_gemm_bf16")
+    native.count_launch()

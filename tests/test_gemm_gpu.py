@@ -1,0 +1,113 @@
+"""tcgen05 GEMM vs a plain PyTorch fp32 reference of the same op (inputs rounded to bf16 in both)."""
+import pytest
+import torch
+
+from singa_b200.ops import gemm as G
+from singa_b200.ops import native
+
+pytestmark = pytest.mark.gpu
+
+
+def _pad8(n):
+    return (n + 7) // 8 * 8
+
+
+def _mk(rows, cols, dev, scale=1.0):
+    """bf16 [rows][cols] view of a padded buffer (ld multiple of 8, padding zero)."""
+    buf = torch.zeros(rows, _pad8(cols), device=dev, dtype=torch.bfloat16)
+    buf[:, :cols] = (torch.randn(rows, cols, device=dev) * scale).to(torch.bfloat16)
+    return buf[:, :cols]
+
+
+def _run(M, N, K, a_mn, b_mn, bn=0, **kw):
+    dev = "cuda"
+    torch.manual_seed(M * 7 + N * 3 + K)
+    a = _mk(K, M, dev) if a_mn else _mk(M, K, dev)
+    b = _mk(K, N, dev) if b_mn else _mk(N, K, dev)
+    out32 = torch.full((M, _pad8(N) if N % 4 else N), float("nan"), device=dev)[:, :N]
+    native.require().sg_gemm_set_tile(bn)
+    try:
+        G.gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn, out32=out32, **kw)
+    finally:
+        native.require().sg_gemm_set_tile(0)
+    torch.cuda.synchronize()
+    kwr = {k: v for k, v in kw.items() if k in ("bias", "act", "grad_act", "aux")}
+    ref = G.gemm_ref(a, b, a_mn, b_mn, **kwr)
+    return out32, ref
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_majors_tiles(a_mn, b_mn, bn):
+    out, ref = _run(256, 512, 384, a_mn, b_mn, bn)
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 2500, 784), (1000, 10, 500), (64, 500, 800), (1000, 500, 1000),
+                                   (130, 70, 72), (1, 8, 8), (777, 1500, 2000)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (False, False), (True, True)])
+def test_gemm_ragged(M, N, K, a_mn, b_mn):
+    out, ref = _run(M, N, K, a_mn, b_mn)
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=3e-2)
+
+
+def test_gemm_epilogue_bias_act():
+    M, N, K = 300, 200, 136
+    bias = torch.randn(N, device="cuda")
+    for act in (G.ACT_RELU, G.ACT_STANH):
+        out, ref = _run(M, N, K, False, True, bias=bias, act=act)
+        torch.testing.assert_close(out, ref, rtol=5e-3, atol=3e-2)
+
+
+def test_gemm_epilogue_gradact_bf16_out_accumulate():
+    M, N, K = 257, 192, 320
+    dev = "cuda"
+    a, b = _mk(M, K, dev, 0.5), _mk(N, K, dev, 0.5)
+    aux = torch.tanh(torch.randn(M, N, device=dev)).to(torch.bfloat16)
+    out16 = torch.zeros(M, N, device=dev, dtype=torch.bfloat16)
+    out32 = torch.ones(M, N, device=dev)
+    G.gemm(a, b, M, N, K, out32=out32, out16=out16, grad_act=G.ACT_STANH, aux=aux, accumulate=True)
+    torch.cuda.synchronize()
+    ref = G.gemm_ref(a, b, grad_act=G.ACT_STANH, aux=aux) + 1.0
+    torch.testing.assert_close(out32, ref, rtol=2e-3, atol=2e-2)
+    torch.testing.assert_close(out16.float(), ref, rtol=2e-2, atol=5e-2)
+    # fp32 aux, relu gradient
+    aux32 = torch.randn(M, N, device=dev)
+    out32 = torch.empty(M, N, device=dev)
+    G.gemm(a, b, M, N, K, out32=out32, grad_act=G.ACT_RELU, aux=aux32)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(out32, G.gemm_ref(a, b, grad_act=G.ACT_RELU, aux=aux32), rtol=2e-3, atol=2e-2)
+
+
+def test_gemm_perm_columns():
+    # conv wgrad: GEMM columns ordered (ky,kx,c) are stored in the reference's (c,ky,kx) order
+    F, C, kk, P = 48, 6, 9, 640
+    dev = "cuda"
+    a, b = _mk(P, F, dev), _mk(P, C * kk, dev)      # both stored [K=P][mn]
+    out = torch.zeros(F, C * kk, device=dev)
+    G.gemm(a, b, F, C * kk, P, a_mn=True, b_mn=True, out32=out, perm=(C, kk))
+    torch.cuda.synchronize()
+    ref = G.gemm_ref(a, b, True, True, perm=(C, kk))
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=3e-2)
+
+
+def test_gemm_large_timing():
+    """8192^3: sanity on numerics of a big persistent run plus a throughput print (not asserted)."""
+    M = N = K = 8192
+    dev = "cuda"
+    a = (torch.randn(M, K, device=dev) * 0.05).to(torch.bfloat16)
+    b = (torch.randn(N, K, device=dev) * 0.05).to(torch.bfloat16)
+    out16 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    for _ in range(3):
+        G.gemm(a, b, M, N, K, out16=out16)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        G.gemm(a, b, M, N, K, out16=out16)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    print(f"\n[gemm 8192^3 bf16] {ms:.3f} ms  {2 * M * N * K / ms / 1e9:.1f} TFLOP/s")
+    ref = (a[:256].float() @ b[:512].float().t())
+    torch.testing.assert_close(out16[:256, :512].float(), ref, rtol=2e-2, atol=5e-2)
