@@ -1,0 +1,444 @@
+// Memory-bound element-wise and reduction kernels (the reference lowers all of these to mshadow's
+// MapPlanKernel / MapRedKeepLowestKernel, include/mshadow/cuda/tensor_gpu-inl.cuh:56-168).
+// Activations are bf16 (or fp32) in HBM, math is fp32 in registers, accesses are 128-bit where the
+// buffer allows it.  Grids are sized to a multiple of the SM count and grid-stride over the data.
+#include <stdint.h>
+
+#include "../include/singa_b200.h"
+#include "common.h"
+#include "philox.cuh"
+#include "vec.cuh"
+
+namespace sg {
+
+constexpr float kStanhA = 1.7159047f;
+constexpr float kStanhB = 0.66666667f;
+
+__device__ __forceinline__ float act_fwd(float v, int act) {
+  if (act == SG_ACT_RELU) return fmaxf(v, 0.f);
+  if (act == SG_ACT_STANH) return kStanhA * tanhf(kStanhB * v);
+  return v;
+}
+__device__ __forceinline__ float act_bwd_from_y(float y, int act) {
+  if (act == SG_ACT_RELU) return y > 0.f ? 1.f : 0.f;
+  if (act == SG_ACT_STANH) return kStanhA * kStanhB - (kStanhB / kStanhA) * y * y;
+  return 1.f;
+}
+
+static inline int ew_grid(long long nvec, int threads) {
+  long long blocks = (nvec + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+// ---------------------------------------------------------------------------------- activation fwd/bwd
+template <typename T>
+__global__ void act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, int act) {
+  constexpr int V = Vec<T>::N;
+  const long long nv = n / V;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nv; i += stride) {
+    float v[V];
+    Vec<T>::load(x + i * V, v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) v[j] = act_fwd(v[j], act);
+    Vec<T>::store(y + i * V, v);
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = nv * V + threadIdx.x; i < n; i += blockDim.x)
+      y[i] = from_float<T>(act_fwd(to_float(x[i]), act));
+  }
+}
+
+template <typename T>
+__global__ void act_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, T* __restrict__ dx,
+                               long long n, int act) {
+  constexpr int V = Vec<T>::N;
+  const long long nv = n / V;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nv; i += stride) {
+    float g[V], o[V];
+    Vec<T>::load(dy + i * V, g);
+    Vec<T>::load(y + i * V, o);
+#pragma unroll
+    for (int j = 0; j < V; ++j) g[j] *= act_bwd_from_y(o[j], act);
+    Vec<T>::store(dx + i * V, g);
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = nv * V + threadIdx.x; i < n; i += blockDim.x)
+      dx[i] = from_float<T>(to_float(dy[i]) * act_bwd_from_y(to_float(y[i]), act));
+  }
+}
+
+// ---------------------------------------------------------------------------------- dropout
+// mask(i) = (u(seed, i) < pkeep) / pkeep, regenerated in backward from (seed, i): no mask tensor.
+// Reference semantics: src/worker/layer.cc:142-160.
+template <typename T>
+__global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, float pkeep,
+                               unsigned long long seed, const unsigned long long* __restrict__ seed_dev) {
+  // seed_dev (optional) holds a per-step value in device memory so a captured CUDA graph draws a fresh
+  // mask on every replay.
+  if (seed_dev != nullptr) seed ^= (*seed_dev + 1ull) * 0x9E3779B97F4A7C15ull;
+  const float inv = 1.f / pkeep;
+  const long long n4 = (n + 3) / 4;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    float u[4];
+    philox_uniform4(seed, static_cast<unsigned long long>(i), u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long e = i * 4 + j;
+      if (e < n) y[e] = from_float<T>(u[j] < pkeep ? to_float(x[e]) * inv : 0.f);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- column sums (bias grad)
+// out[c] (+)= sum_r x[r][c].  One warp-wide column strip per block column, rows split across blockIdx.y,
+// partial sums merged with one atomicAdd per (block, column): `out` must be zeroed (or hold the value to
+// accumulate into) before the launch.  Reference: sum_rows / sumall_except_dim (layer.cc:107,206).
+template <typename T>
+__global__ void colsum_kernel(const T* __restrict__ x, long long ld, int rows, int cols,
+                              float* __restrict__ out) {
+  __shared__ float part[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(rows, r0 + rows_per);
+  float s = 0.f;
+  if (c < cols) {
+    for (int r = r0 + threadIdx.y; r < r1; r += 8) s += to_float(x[static_cast<long long>(r) * ld + c]);
+  }
+  part[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
+    atomicAdd(out + c, t);
+  }
+}
+
+// ---------------------------------------------------------------------------------- cast / pack
+// dst[r][c] (bf16, row stride ldd, padding columns zeroed) = src[r][pc] (fp32, row stride lds) where
+// pc = c for a plain cast, or for conv weights (perm_c = C, perm_kk = k*k): destination column
+// j = kk_idx*C + c reads source column c*kk + kk_idx.
+__global__ void cast_pack_kernel(const float* __restrict__ src, long long lds,
+                                 __nv_bfloat16* __restrict__ dst, long long ldd, int rows, int cols,
+                                 int perm_c, int perm_kk) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int r = static_cast<int>(i / ldd);
+    const int c = static_cast<int>(i - static_cast<long long>(r) * ldd);
+    float v = 0.f;
+    if (c < cols) {
+      const int sc = perm_c > 0 ? (c % perm_c) * perm_kk + (c / perm_c) : c;
+      v = src[static_cast<long long>(r) * lds + sc];
+    }
+    dst[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// Generic dtype conversion of a flat buffer (fp32 <-> bf16).
+template <typename S, typename D>
+__global__ void convert_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += stride)
+    dst[i] = from_float<D>(to_float(src[i]));
+}
+
+// ---------------------------------------------------------------------------------- NCHW <-> NHWC
+// 32x32 smem tile transpose of the (C, HW) plane of every image.
+template <typename S, typename D>
+__global__ void transpose_planes_kernel(const S* __restrict__ src, D* __restrict__ dst, int rows,
+                                        int cols) {
+  // per image: src[rows][cols] -> dst[cols][rows]
+  __shared__ float tile[32][33];
+  const long long img = blockIdx.z;
+  const S* s = src + img * rows * cols;
+  D* d = dst + img * rows * cols;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int r = r0 + j, c = c0 + threadIdx.x;
+    if (r < rows && c < cols) tile[j][threadIdx.x] = to_float(s[static_cast<long long>(r) * cols + c]);
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int c = c0 + j, r = r0 + threadIdx.x;
+    if (r < rows && c < cols) d[static_cast<long long>(c) * rows + r] = from_float<D>(tile[threadIdx.x][j]);
+  }
+}
+
+// ---------------------------------------------------------------------------------- L1 norm (debug norms)
+// out[0] += sum |x|  (reference Blob::asum_data = cblas_sasum / count, src/utils/blob.cc:251-255)
+template <typename T>
+__global__ void asum_kernel(const T* __restrict__ x, long long n, float* __restrict__ out) {
+  float s = 0.f;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += stride)
+    s += fabsf(to_float(x[i]));
+  s = warp_sum(s);
+  __shared__ float ws[32];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? ws[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) atomicAdd(out, t);
+  }
+}
+
+// ---------------------------------------------------------------------------------- Philox fills (param init)
+// kind 0: uniform in [a, b) * scale; kind 1: gaussian(mean=a, std=b) * scale.  Reference: Param::Init,
+// src/utils/param.cc:89-127 (distributions match; streams do not — the reference seeds from wall clock).
+__global__ void fill_random_kernel(float* __restrict__ dst, long long n, int kind, float a, float b,
+                                   float scale, unsigned long long seed) {
+  const long long n4 = (n + 3) / 4;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    float u[4];
+    philox_uniform4(seed, static_cast<unsigned long long>(i), u);
+    float v[4];
+    if (kind == 0) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = (a + (b - a) * u[j]) * scale;
+    } else {
+      // Box-Muller on two pairs
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float r = sqrtf(-2.f * logf(fmaxf(u[2 * j], 1e-12f)));
+        float sn, cs;
+        sincosf(6.283185307179586f * u[2 * j + 1], &sn, &cs);
+        v[2 * j] = (a + b * r * cs) * scale;
+        v[2 * j + 1] = (a + b * r * sn) * scale;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long e = i * 4 + j;
+      if (e < n) dst[e] = v[j];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------- parsers
+// MNIST: uint8 pixel -> x / norm_a - norm_b  (src/worker/layer.cc:440-445)
+template <typename D>
+__global__ void mnist_parse_kernel(const uint8_t* __restrict__ src, D* __restrict__ dst, long long n,
+                                   float norm_a, float norm_b) {
+  const float inv = 1.f / norm_a;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += stride)
+    dst[i] = from_float<D>(static_cast<float>(src[i]) * inv - norm_b);
+}
+
+// RGB: per image random crop offset (train) + mirror flag, uint8 CHW record -> NHWC output * scale, minus
+// optional mean image (fp32 CHW, full size).  Intent of src/worker/layer.cc:573-624 (whose non-mirror path
+// never writes the output — defect §2.8 of the survey; the intended copy is implemented here).
+template <typename D>
+__global__ void rgb_parse_kernel(const uint8_t* __restrict__ src, const float* __restrict__ mean,
+                                 D* __restrict__ dst, int batch, int C, int H, int W, int crop,
+                                 const int* __restrict__ off_h, const int* __restrict__ off_w,
+                                 const int* __restrict__ mirror, float scale) {
+  const int oh = crop > 0 ? crop : H, ow = crop > 0 ? crop : W;
+  const long long total = static_cast<long long>(batch) * oh * ow * C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    long long t = i / C;
+    const int x = static_cast<int>(t % ow); t /= ow;
+    const int y = static_cast<int>(t % oh);
+    const int n = static_cast<int>(t / oh);
+    const int sy = y + (off_h ? off_h[n] : 0);
+    const int sx = (mirror && mirror[n] ? (ow - 1 - x) : x) + (off_w ? off_w[n] : 0);
+    const long long sidx = (static_cast<long long>(c) * H + sy) * W + sx;
+    float v = static_cast<float>(src[static_cast<long long>(n) * C * H * W + sidx]);
+    if (mean) v -= mean[sidx];
+    dst[i] = from_float<D>(v * scale);
+  }
+}
+
+// 2-D bf16 copy that changes the row stride (used to pad a [rows][cols] matrix to a TMA-legal ld).
+__global__ void copy2d_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long lds,
+                                   __nv_bfloat16* __restrict__ dst, long long ldd, int rows, int cols) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int r = static_cast<int>(i / ldd);
+    const int c = static_cast<int>(i - static_cast<long long>(r) * ldd);
+    dst[i] = c < cols ? src[static_cast<long long>(r) * lds + c] : __float2bfloat16_rn(0.f);
+  }
+}
+
+}  // namespace sg
+
+using namespace sg;
+
+#define DTYPE_SWITCH(is_bf16, T, ...)            \
+  if (is_bf16) { using T = __nv_bfloat16; __VA_ARGS__ } \
+  else { using T = float; __VA_ARGS__ }
+
+extern "C" int sg_act_fwd(const void* x, void* y, long long n, int act, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  DTYPE_SWITCH(is_bf16, T, {
+    SG_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, "sg_act_fwd: 16-byte alignment");
+    act_fwd_kernel<T><<<ew_grid(n / Vec<T>::N + 1, 256), 256, 0, s>>>((const T*)x, (T*)y, n, act);
+  })
+  SG_CHECK_LAUNCH("act_fwd");
+  return 0;
+}
+
+extern "C" int sg_act_bwd(const void* dy, const void* y, void* dx, long long n, int act, int is_bf16,
+                          void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  DTYPE_SWITCH(is_bf16, T, {
+    SG_REQUIRE(((uintptr_t)dy & 15) == 0 && ((uintptr_t)y & 15) == 0 && ((uintptr_t)dx & 15) == 0,
+               "sg_act_bwd: 16-byte alignment");
+    act_bwd_kernel<T><<<ew_grid(n / Vec<T>::N + 1, 256), 256, 0, s>>>((const T*)dy, (const T*)y, (T*)dx, n, act);
+  })
+  SG_CHECK_LAUNCH("act_bwd");
+  return 0;
+}
+
+extern "C" int sg_dropout(const void* x, void* y, long long n, float pkeep, unsigned long long seed,
+                          const unsigned long long* seed_dev, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  SG_REQUIRE(pkeep > 0.f && pkeep <= 1.f, "sg_dropout: pkeep must be in (0,1]");
+  DTYPE_SWITCH(is_bf16, T, {
+    dropout_kernel<T><<<ew_grid((n + 3) / 4, 256), 256, 0, s>>>((const T*)x, (T*)y, n, pkeep, seed, seed_dev);
+  })
+  SG_CHECK_LAUNCH("dropout");
+  return 0;
+}
+
+extern "C" int sg_colsum(const void* x, long long ld, int rows, int cols, float* out, int accumulate,
+                         int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || cols <= 0) return 0;
+  if (!accumulate) {
+    if (check_cuda(cudaMemsetAsync(out, 0, sizeof(float) * cols, s), "colsum memset")) return 1;
+  }
+  const int gx = (cols + 31) / 32;
+  int gy = (num_sms() * 4 + gx - 1) / gx;
+  const int max_gy = (rows + 63) / 64;
+  if (gy > max_gy) gy = max_gy;
+  if (gy < 1) gy = 1;
+  DTYPE_SWITCH(is_bf16, T, {
+    colsum_kernel<T><<<dim3(gx, gy), dim3(32, 8), 0, s>>>((const T*)x, ld, rows, cols, out);
+  })
+  SG_CHECK_LAUNCH("colsum");
+  return 0;
+}
+
+extern "C" int sg_cast_pack(const float* src, long long lds, void* dst, long long ldd, int rows,
+                            int cols, int perm_c, int perm_kk, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || cols <= 0) return 0;
+  SG_REQUIRE(ldd >= cols && lds >= cols, "sg_cast_pack: leading dimensions too small");
+  SG_REQUIRE(perm_c == 0 || perm_c * perm_kk == cols, "sg_cast_pack: perm_c*perm_kk must equal cols");
+  const long long total = static_cast<long long>(rows) * ldd;
+  cast_pack_kernel<<<ew_grid(total, 256), 256, 0, s>>>(src, lds, (__nv_bfloat16*)dst, ldd, rows, cols,
+                                                       perm_c, perm_kk);
+  SG_CHECK_LAUNCH("cast_pack");
+  return 0;
+}
+
+extern "C" int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long n,
+                          void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  const int g = ew_grid(n, 256);
+  if (src_bf16 && !dst_bf16)
+    convert_kernel<__nv_bfloat16, float><<<g, 256, 0, s>>>((const __nv_bfloat16*)src, (float*)dst, n);
+  else if (!src_bf16 && dst_bf16)
+    convert_kernel<float, __nv_bfloat16><<<g, 256, 0, s>>>((const float*)src, (__nv_bfloat16*)dst, n);
+  else if (src_bf16)
+    convert_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, s>>>((const __nv_bfloat16*)src, (__nv_bfloat16*)dst, n);
+  else
+    convert_kernel<float, float><<<g, 256, 0, s>>>((const float*)src, (float*)dst, n);
+  SG_CHECK_LAUNCH("convert");
+  return 0;
+}
+
+// per image: [rows][cols] -> [cols][rows]; NCHW->NHWC is rows=C, cols=H*W; NHWC->NCHW is rows=H*W, cols=C.
+extern "C" int sg_transpose_planes(const void* src, int src_bf16, void* dst, int dst_bf16, int batch,
+                                   int rows, int cols, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (batch <= 0 || rows <= 0 || cols <= 0) return 0;
+  SG_REQUIRE(batch <= 65535, "sg_transpose_planes: batch too large for grid.z");
+  dim3 grid((cols + 31) / 32, (rows + 31) / 32, batch), block(32, 8);
+  if (src_bf16 && dst_bf16)
+    transpose_planes_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, s>>>((const __nv_bfloat16*)src, (__nv_bfloat16*)dst, rows, cols);
+  else if (src_bf16)
+    transpose_planes_kernel<__nv_bfloat16, float><<<grid, block, 0, s>>>((const __nv_bfloat16*)src, (float*)dst, rows, cols);
+  else if (dst_bf16)
+    transpose_planes_kernel<float, __nv_bfloat16><<<grid, block, 0, s>>>((const float*)src, (__nv_bfloat16*)dst, rows, cols);
+  else
+    transpose_planes_kernel<float, float><<<grid, block, 0, s>>>((const float*)src, (float*)dst, rows, cols);
+  SG_CHECK_LAUNCH("transpose_planes");
+  return 0;
+}
+
+extern "C" int sg_asum(const void* x, long long n, float* out, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (check_cuda(cudaMemsetAsync(out, 0, sizeof(float), s), "asum memset")) return 1;
+  if (n <= 0) return 0;
+  DTYPE_SWITCH(is_bf16, T, { asum_kernel<T><<<ew_grid(n, 256), 256, 0, s>>>((const T*)x, n, out); })
+  SG_CHECK_LAUNCH("asum");
+  return 0;
+}
+
+extern "C" int sg_fill_random(float* dst, long long n, int kind, float a, float b, float scale,
+                              unsigned long long seed, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  SG_REQUIRE(kind == 0 || kind == 1, "sg_fill_random: kind must be 0 (uniform) or 1 (gaussian)");
+  fill_random_kernel<<<ew_grid((n + 3) / 4, 256), 256, 0, s>>>(dst, n, kind, a, b, scale, seed);
+  SG_CHECK_LAUNCH("fill_random");
+  return 0;
+}
+
+extern "C" int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, float norm_b,
+                              int dst_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n <= 0) return 0;
+  SG_REQUIRE(norm_a != 0.f, "sg_mnist_parse: norm_a must be non-zero");
+  DTYPE_SWITCH(dst_bf16, T, {
+    mnist_parse_kernel<T><<<ew_grid(n, 256), 256, 0, s>>>((const uint8_t*)src_u8, (T*)dst, n, norm_a, norm_b);
+  })
+  SG_CHECK_LAUNCH("mnist_parse");
+  return 0;
+}
+
+extern "C" int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H,
+                            int W, int crop, const int* off_h, const int* off_w, const int* mirror,
+                            float scale, int dst_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (batch <= 0) return 0;
+  SG_REQUIRE(crop >= 0 && crop <= H && crop <= W, "sg_rgb_parse: crop larger than the image");
+  const int oh = crop > 0 ? crop : H, ow = crop > 0 ? crop : W;
+  const long long total = static_cast<long long>(batch) * oh * ow * C;
+  DTYPE_SWITCH(dst_bf16, T, {
+    rgb_parse_kernel<T><<<ew_grid(total, 256), 256, 0, s>>>((const uint8_t*)src_u8, mean, (T*)dst, batch, C, H, W,
+                                                           crop, off_h, off_w, mirror, scale);
+  })
+  SG_CHECK_LAUNCH("rgb_parse");
+  return 0;
+}
+
+extern "C" int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
+                              void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || cols <= 0) return 0;
+  SG_REQUIRE(ldd >= cols && lds >= cols, "sg_copy2d_bf16: leading dimensions too small");
+  copy2d_bf16_kernel<<<ew_grid(static_cast<long long>(rows) * ldd, 256), 256, 0, s>>>(
+      (const __nv_bfloat16*)src, lds, (__nv_bfloat16*)dst, ldd, rows, cols);
+  SG_CHECK_LAUNCH("copy2d_bf16");
+  return 0;
+}

@@ -1,0 +1,262 @@
+// Softmax-loss (fwd+bwd fused), pooling and LRN for channels-last (NHWC) bf16/fp32 activations.
+#include <float.h>
+#include <stdint.h>
+
+#include "../include/singa_b200.h"
+#include "common.h"
+#include "vec.cuh"
+
+namespace sg {
+
+// ------------------------------------------------------------------------------------------------
+// Softmax loss.  One warp per row: max, exp-sum, NLL, rank of the label (top-k), gradient.
+//   metric[0] += scale/N * -log(max(p_label, FLT_MIN));  metric[1] += scale/N * [rank(label) < topk]
+//   grad[r][j] = (p_j - [j == label]) * scale / N
+// Reference: SoftmaxLossLayer, src/worker/layer.cc:718-764 (its `label < 10` limit is not reproduced).
+// ------------------------------------------------------------------------------------------------
+template <typename G>
+__global__ void softmax_loss_kernel(const float* __restrict__ logits, long long ldl,
+                                    const int* __restrict__ labels, int rows, int dim, int topk,
+                                    float scale, float* __restrict__ prob, long long ldp,
+                                    G* __restrict__ grad, long long ldg, float* __restrict__ metric) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
+  float loss_acc = 0.f, hit_acc = 0.f;
+  for (int r = blockIdx.x * warps_per_block + (threadIdx.x >> 5); r < rows;
+       r += gridDim.x * warps_per_block) {
+    const float* x = logits + static_cast<long long>(r) * ldl;
+    float mx = -FLT_MAX;
+    for (int j = lane; j < dim; j += 32) mx = fmaxf(mx, x[j]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int j = lane; j < dim; j += 32) sum += __expf(x[j] - mx);
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    int label = labels[r];
+    label = label < 0 ? 0 : (label >= dim ? dim - 1 : label);
+    const float xl = x[label];
+    float rank = 0.f;
+    for (int j = lane; j < dim; j += 32) rank += (x[j] > xl) ? 1.f : 0.f;
+    rank = warp_sum(rank);
+    const float pl = __expf(xl - mx) * inv;
+    if (lane == 0) {
+      loss_acc += -logf(fmaxf(pl, FLT_MIN));
+      hit_acc += rank < static_cast<float>(topk) ? 1.f : 0.f;
+    }
+    const float gs = scale / rows;
+    for (int j = lane; j < dim; j += 32) {
+      const float pj = __expf(x[j] - mx) * inv;
+      if (prob) prob[static_cast<long long>(r) * ldp + j] = pj;
+      if (grad) grad[static_cast<long long>(r) * ldg + j] = from_float<G>((pj - (j == label ? 1.f : 0.f)) * gs);
+    }
+  }
+  // block-level reduction of the two metrics, one atomic pair per block
+  __shared__ float sl[32], sh[32];
+  if (lane == 0) { sl[threadIdx.x >> 5] = loss_acc; sh[threadIdx.x >> 5] = hit_acc; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float a = threadIdx.x < warps_per_block ? sl[threadIdx.x] : 0.f;
+    float b = threadIdx.x < warps_per_block ? sh[threadIdx.x] : 0.f;
+    a = warp_sum(a); b = warp_sum(b);
+    if (threadIdx.x == 0 && metric) {
+      atomicAdd(metric, a * scale / rows);
+      atomicAdd(metric + 1, b * scale / rows);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Pooling, NHWC.  Window clipped at the bottom/right edge; AVE always divides by k*k
+// (reference: mshadow pool/unpool, include/mshadow/tensor_expr_ext.h:790-848; layer.cc:512-540).
+// Output size is computed by the caller (ceil form, see ops/pool.py).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void pool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C,
+                                int OH, int OW, int k, int s, int pad, int is_max) {
+  const long long total = static_cast<long long>(N) * OH * OW * C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    long long t = i / C;
+    const int ox = static_cast<int>(t % OW); t /= OW;
+    const int oy = static_cast<int>(t % OH);
+    const int n = static_cast<int>(t / OH);
+    const int y0 = oy * s - pad, x0 = ox * s - pad;
+    const int y1 = min(y0 + k, H), x1 = min(x0 + k, W);
+    float acc = is_max ? -FLT_MAX : 0.f;
+    for (int yy = max(y0, 0); yy < y1; ++yy)
+      for (int xx = max(x0, 0); xx < x1; ++xx) {
+        const float v = to_float(x[((static_cast<long long>(n) * H + yy) * W + xx) * C + c]);
+        acc = is_max ? fmaxf(acc, v) : acc + v;
+      }
+    if (!is_max) acc *= 1.f / (k * k);
+    y[i] = from_float<T>(acc);
+  }
+}
+
+// Gather-form backward (no atomics): every input element sums over the windows that contain it.
+// MAX routes the gradient to every element equal to the window max (the reference's tie rule).
+template <typename T>
+__global__ void pool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y,
+                                const T* __restrict__ dy, T* __restrict__ dx, int N, int H, int W,
+                                int C, int OH, int OW, int k, int s, int pad, int is_max) {
+  const long long total = static_cast<long long>(N) * H * W * C;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    long long t = i / C;
+    const int xx = static_cast<int>(t % W); t /= W;
+    const int yy = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    const float xv = to_float(x[i]);
+    // windows oy with oy*s - pad <= yy < oy*s - pad + k
+    const int oy_lo = max(0, (yy + pad - k + s) / s), oy_hi = min(OH - 1, (yy + pad) / s);
+    const int ox_lo = max(0, (xx + pad - k + s) / s), ox_hi = min(OW - 1, (xx + pad) / s);
+    float g = 0.f;
+    for (int oy = oy_lo; oy <= oy_hi; ++oy)
+      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+        const long long o = ((static_cast<long long>(n) * OH + oy) * OW + ox) * C + c;
+        if (is_max) {
+          if (to_float(y[o]) == xv) g += to_float(dy[o]);
+        } else {
+          g += to_float(dy[o]);
+        }
+      }
+    if (!is_max) g *= 1.f / (k * k);
+    dx[i] = from_float<T>(g);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LRN across channels, NHWC.  norm = knorm + (alpha/n) * sum_{c' in [c-n/2, c+n/2]} x^2; y = x * norm^-beta.
+// Backward: dx = dy*norm^-beta - (2*beta*alpha/n) * x * sum_{c'} dy*x*norm^(-beta-1)... evaluated at c'.
+// Reference: LRNLayer, src/worker/layer.cc:356-378; window clipping tensor_expr_ext.h:929-934.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void lrn_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, float* __restrict__ norm,
+                               long long pixels, int C, int lsize, float alpha, float beta, float knorm) {
+  const long long total = pixels * C;
+  const int half = lsize / 2;
+  const float salpha = alpha / lsize;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    const long long base = i - c;
+    float s = 0.f;
+    for (int cc = max(0, c - half); cc <= min(C - 1, c + half); ++cc) {
+      const float v = to_float(x[base + cc]);
+      s += v * v;
+    }
+    const float nm = knorm + salpha * s;
+    norm[i] = nm;
+    y[i] = from_float<T>(to_float(x[i]) * __powf(nm, -beta));
+  }
+}
+
+template <typename T>
+__global__ void lrn_bwd_kernel(const T* __restrict__ x, const float* __restrict__ norm,
+                               const T* __restrict__ dy, T* __restrict__ dx, long long pixels, int C,
+                               int lsize, float alpha, float beta) {
+  const long long total = pixels * C;
+  const int half = lsize / 2;
+  const float coef = 2.f * beta * alpha / lsize;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % C);
+    const long long base = i - c;
+    float s = 0.f;
+    for (int cc = max(0, c - half); cc <= min(C - 1, c + half); ++cc) {
+      const float nm = norm[base + cc];
+      s += to_float(dy[base + cc]) * to_float(x[base + cc]) * __powf(nm, -beta - 1.f);
+    }
+    const float g = to_float(dy[i]) * __powf(norm[i], -beta) - coef * to_float(x[i]) * s;
+    dx[i] = from_float<T>(g);
+  }
+}
+
+static inline int grid_for(long long n, int threads) {
+  long long b = (n + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * 16;
+  if (b > cap) b = cap;
+  return static_cast<int>(b < 1 ? 1 : b);
+}
+
+}  // namespace sg
+
+using namespace sg;
+
+extern "C" int sg_softmax_loss(const float* logits, long long ldl, const int* labels, int rows, int dim,
+                               int topk, float scale, float* prob, long long ldp, void* grad,
+                               long long ldg, int grad_bf16, float* metric, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0) return 0;
+  SG_REQUIRE(dim > 0 && topk > 0, "sg_softmax_loss: dim and topk must be positive");
+  const int threads = 256, wpb = threads / 32;
+  int blocks = (rows + wpb - 1) / wpb;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  if (grad_bf16)
+    softmax_loss_kernel<__nv_bfloat16><<<blocks, threads, 0, s>>>(logits, ldl, labels, rows, dim, topk, scale, prob, ldp,
+                                                                   (__nv_bfloat16*)grad, ldg, metric);
+  else
+    softmax_loss_kernel<float><<<blocks, threads, 0, s>>>(logits, ldl, labels, rows, dim, topk, scale, prob, ldp,
+                                                           (float*)grad, ldg, metric);
+  SG_CHECK_LAUNCH("softmax_loss");
+  return 0;
+}
+
+extern "C" int sg_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int k,
+                           int stride, int pad, int is_max, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(N) * OH * OW * C;
+  if (total <= 0) return 0;
+  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_fwd: bad window");
+  if (is_bf16)
+    pool_fwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  else
+    pool_fwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (float*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  SG_CHECK_LAUNCH("pool_fwd");
+  return 0;
+}
+
+extern "C" int sg_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W,
+                           int C, int OH, int OW, int k, int stride, int pad, int is_max, int is_bf16,
+                           void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(N) * H * W * C;
+  if (total <= 0) return 0;
+  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_bwd: bad window");
+  if (is_bf16)
+    pool_bwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  else
+    pool_bwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (const float*)y, (const float*)dy, (float*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  SG_CHECK_LAUNCH("pool_bwd");
+  return 0;
+}
+
+extern "C" int sg_lrn_fwd(const void* x, void* y, float* norm, long long pixels, int C, int lsize,
+                          float alpha, float beta, float knorm, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = pixels * C;
+  if (total <= 0) return 0;
+  SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_fwd: local size must be odd and positive");
+  if (is_bf16)
+    lrn_fwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, norm, pixels, C, lsize, alpha, beta, knorm);
+  else
+    lrn_fwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (float*)y, norm, pixels, C, lsize, alpha, beta, knorm);
+  SG_CHECK_LAUNCH("lrn_fwd");
+  return 0;
+}
+
+extern "C" int sg_lrn_bwd(const void* x, const float* norm, const void* dy, void* dx, long long pixels,
+                          int C, int lsize, float alpha, float beta, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const long long total = pixels * C;
+  if (total <= 0) return 0;
+  SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_bwd: local size must be odd and positive");
+  if (is_bf16)
+    lrn_bwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, norm, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, pixels, C, lsize, alpha, beta);
+  else
+    lrn_bwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, norm, (const float*)dy, (float*)dx, pixels, C, lsize, alpha, beta);
+  SG_CHECK_LAUNCH("lrn_bwd");
+  return 0;
+}

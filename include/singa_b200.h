@@ -54,6 +54,100 @@ typedef struct SgGemmEpilogue {
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
                  long long ldb, int M, int N, int K, const SgGemmEpilogue* ep, void* stream);
 
+/* Test hook: force the N-tile width (64/128/256) of sg_gemm_bf16; 0 restores the heuristic. */
+int sg_gemm_set_tile(int bn);
+
+/* ------------------------------------------------------------------------------------------------
+ * Element-wise family (reference: every mshadow expression lowers to MapPlanKernel,
+ * include/mshadow/cuda/tensor_gpu-inl.cuh:56-92).  is_bf16 selects bf16 vs fp32 element type.
+ * ---------------------------------------------------------------------------------------------- */
+/* ReLU / scaled tanh forward and backward-from-output (src/worker/layer.cc:556-569,688-701). */
+int sg_act_fwd(const void* x, void* y, long long n, int act, int is_bf16, void* stream);
+int sg_act_bwd(const void* dy, const void* y, void* dx, long long n, int act, int is_bf16, void* stream);
+/* Dropout: y = x * (philox(seed', i) < pkeep) / pkeep.  Backward is the same call on dy (layer.cc:142-160).
+ * seed_dev (optional, device memory) is mixed into the seed at run time so that a captured CUDA graph
+ * draws a new mask per replay. */
+int sg_dropout(const void* x, void* y, long long n, float pkeep, unsigned long long seed,
+               const unsigned long long* seed_dev, int is_bf16, void* stream);
+/* out[c] (+)= sum_r x[r][c]  — bias gradients (sum_rows / sumall_except_dim, layer.cc:107,206). */
+int sg_colsum(const void* x, long long ld, int rows, int cols, float* out, int accumulate, int is_bf16,
+              void* stream);
+/* fp32 [rows][lds] -> bf16 [rows][ldd] (padding columns zeroed), optional conv-weight column permutation
+ * (c,ky,kx) -> (ky,kx,c) given perm_c = C, perm_kk = k*k. */
+int sg_cast_pack(const float* src, long long lds, void* dst, long long ldd, int rows, int cols,
+                 int perm_c, int perm_kk, void* stream);
+int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
+/* bf16 [rows][lds] -> bf16 [rows][ldd], padding columns zeroed (re-striding to a TMA-legal leading dimension). */
+int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, void* stream);
+/* Per image [rows][cols] -> [cols][rows] (NCHW <-> NHWC). */
+int sg_transpose_planes(const void* src, int src_bf16, void* dst, int dst_bf16, int batch, int rows,
+                        int cols, void* stream);
+/* out[0] = sum |x|  (Blob::asum_data, src/utils/blob.cc:251-255; the caller divides by count). */
+int sg_asum(const void* x, long long n, float* out, int is_bf16, void* stream);
+/* Philox fills for Param::Init (src/utils/param.cc:89-127): kind 0 uniform[a,b)*scale, 1 gaussian(a,b)*scale. */
+int sg_fill_random(float* dst, long long n, int kind, float a, float b, float scale,
+                   unsigned long long seed, void* stream);
+/* Parsers (src/worker/layer.cc:382-448, 573-624): uint8 records -> normalised activations. */
+int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, float norm_b, int dst_bf16,
+                   void* stream);
+int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H, int W,
+                 int crop, const int* off_h, const int* off_w, const int* mirror, float scale,
+                 int dst_bf16, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Softmax loss forward+backward in one pass (src/worker/layer.cc:718-764).
+ *   metric[0] += scale * mean(-log max(p_label, FLT_MIN)),  metric[1] += scale * top-k accuracy
+ *   grad = (p - onehot) * scale / rows   (grad, prob and metric are each optional)
+ * ---------------------------------------------------------------------------------------------- */
+int sg_softmax_loss(const float* logits, long long ldl, const int* labels, int rows, int dim, int topk,
+                    float scale, float* prob, long long ldp, void* grad, long long ldg, int grad_bf16,
+                    float* metric, void* stream);
+
+/* Pooling (MAX / AVE) and across-channel LRN on channels-last activations
+ * (src/worker/layer.cc:476-540 and 331-378; mshadow pool/unpool/chpool). */
+int sg_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int k, int stride,
+                int pad, int is_max, int is_bf16, void* stream);
+int sg_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C,
+                int OH, int OW, int k, int stride, int pad, int is_max, int is_bf16, void* stream);
+int sg_lrn_fwd(const void* x, void* y, float* norm, long long pixels, int C, int lsize, float alpha,
+               float beta, float knorm, int is_bf16, void* stream);
+int sg_lrn_bwd(const void* x, const float* norm, const void* dy, void* dx, long long pixels, int C,
+               int lsize, float alpha, float beta, int is_bf16, void* stream);
+
+/* Convolution lowering (src/worker/layer.cc:63-123): bf16 NHWC patches -> col[pixels][ld] with column
+ * (ky*k+kx)*C + c, and the gather-form inverse for the data gradient (optionally fused with the
+ * activation gradient of the layer below; aux = that layer's output, bf16 NHWC). */
+int sg_im2col_nhwc(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH, int OW,
+                   int k, int stride, int pad, void* stream);
+int sg_col2im_nhwc(const void* dcol, long long ld, void* dx, int N, int H, int W, int C, int OH, int OW,
+                   int k, int stride, int pad, int grad_act, const void* aux, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Updaters over the flat parameter arena (src/utils/updater.cc:54-182) and PS exchange rules
+ * (src/utils/param.cc:130-284).  Arena offsets are multiples of SG_ARENA_CHUNK elements; chunk_param maps a
+ * chunk to its parameter index (or -1 for padding); lr_mult / wd_mult are indexed by parameter.
+ * ---------------------------------------------------------------------------------------------- */
+#define SG_ARENA_CHUNK 1024
+enum { SG_UPD_SGD = 0, SG_UPD_NESTEROV = 1, SG_UPD_ADAGRAD = 2, SG_UPD_RMSPROP = 3, SG_UPD_ADADELTA = 4 };
+typedef struct SgUpdater {
+  int kind;
+  float lr;            /* LR(step), before the per-parameter multiplier */
+  float momentum;
+  float weight_decay;
+  float delta;
+  float rho;
+  float grad_scale;
+  const float* lr_dev; /* optional device scalar overriding `lr` (lets a captured CUDA graph follow the LR schedule) */
+} SgUpdater;
+int sg_update_arena(float* w, const float* g, float* h, float* u, void* w16, const int* chunk_param,
+                    const float* lr_mult, const float* wd_mult, long long first_chunk,
+                    long long nchunks, const SgUpdater* up, void* stream);
+/* EASGD: d = (w - server) * alpha; server += d (atomic); w -= d.  `server` may be peer memory. */
+int sg_easgd_sync(float* w, float* server, long long n, float alpha, void* w16, void* stream);
+/* RandomSync on the shared-seed subset {i : philox(seed,i) < ratio}. */
+int sg_randomsync(float* w, float* snap, float* server, long long n, float ratio,
+                  unsigned long long seed, void* w16, unsigned long long* nselected, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

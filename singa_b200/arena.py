@@ -1,0 +1,110 @@
+"""Flat parameter arena: one contiguous fp32 buffer each for value / gradient / history (/ update /
+snapshot) of ALL parameters of a net plus a bf16 mirror of the values, with every parameter starting on a
+1024-element boundary.
+
+Why: (1) one fused multi-tensor updater launch per step (or per layer) instead of one per parameter;
+(2) a "server shard" of the B200 parameter server is simply a chunk range of this arena on some GPU, so the
+fused push/pull kernels address it with plain offsets through peer memory; (3) the bf16 mirror is written by
+the updater in the same pass, so the GEMMs never need a separate cast kernel.
+Reference counterpart: ParamManager's single flat Param buffer, src/utils/param_manager.cc:40-69.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import torch
+
+from .device import ctx
+from .param import Param
+
+CHUNK = 1024
+
+
+def _round_up(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
+class ParamArena:
+    def __init__(self, params: Sequence[Param], *, with_update: bool = False, with_snapshot: bool = False,
+                 with_history: bool = True, device=None, allocator=None):
+        self.device = device or ctx().device
+        self.params: List[Param] = [p for p in params if p.is_owner]
+        self.offsets: Dict[int, int] = {}
+        off = 0
+        for p in self.params:
+            self.offsets[id(p)] = off
+            off += _round_up(p.size, CHUNK)
+        self.total = max(off, CHUNK)
+        self.nchunks = self.total // CHUNK
+        alloc = allocator or (lambda n, dt: torch.zeros(n, dtype=dt, device=self.device))
+        self.data = alloc(self.total, torch.float32)
+        self.grad = alloc(self.total, torch.float32)
+        self.history = alloc(self.total, torch.float32) if with_history else None
+        self.update = alloc(self.total, torch.float32) if with_update else None
+        self.snapshot = alloc(self.total, torch.float32) if with_snapshot else None
+        self.use16 = self.device.type == "cuda" and ctx().is_native
+        self.data16 = alloc(self.total, torch.bfloat16) if self.use16 else None
+        chunk_param = torch.full((self.nchunks,), -1, dtype=torch.int32)
+        lr_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
+        wd_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
+        for i, p in enumerate(self.params):
+            o = self.offsets[id(p)]
+            chunk_param[o // CHUNK:(o + _round_up(p.size, CHUNK)) // CHUNK] = i
+            lr_mult[i] = p.learning_rate_multiplier
+            wd_mult[i] = p.weight_decay_multiplier
+        self.chunk_param = chunk_param.to(self.device)
+        self.lr_mult = lr_mult.to(self.device)
+        self.wd_mult = wd_mult.to(self.device)
+        self.adopt()
+
+    def adopt(self) -> None:
+        """Re-point every owner parameter's blobs into the arena (existing values are preserved)."""
+        for p in self.params:
+            o, n = self.offsets[id(p)], p.size
+            p.arena_offset = o
+
+            def view(buf, old):
+                v = buf[o:o + n].view(p.shape)
+                if old is not None and old.data_ptr() != v.data_ptr():
+                    v.copy_(old.to(v.device))
+                return v
+
+            p.data = view(self.data, p.data)
+            p.grad = view(self.grad, p.grad)
+            if self.history is not None:
+                p.history = view(self.history, p.history)
+            if self.update is not None:
+                p.update = view(self.update, p.update)
+            if self.snapshot is not None:
+                p.snapshot = view(self.snapshot, p.snapshot)
+        self.sync_mirror()
+
+    def view16(self, p: Param) -> torch.Tensor:
+        o = self.offsets[id(p if p.is_owner else p.owner)]
+        return self.data16[o:o + p.size].view(p.shape)
+
+    def sync_mirror(self) -> None:
+        """data16 <- data for the whole arena, then refresh every packed operand."""
+        if self.data16 is not None:
+            from .ops import kernels as K
+            K.convert(self.data, self.data16)
+        for p in self.params:
+            if p.pack16 is not None:
+                p.pack16()
+
+    def chunk_range(self, params: Sequence[Param]) -> Tuple[int, int]:
+        """(first_chunk, nchunks) covering ``params`` (must be adjacent in the arena, e.g. one layer)."""
+        owners = [p if p.is_owner else p.owner for p in params]
+        owners = [p for p in owners if id(p) in self.offsets]
+        if not owners:
+            return 0, 0
+        lo = min(self.offsets[id(p)] for p in owners)
+        hi = max(self.offsets[id(p)] + _round_up(p.size, CHUNK) for p in owners)
+        return lo // CHUNK, (hi - lo) // CHUNK
+
+    def param_index(self, p: Param) -> int:
+        return self.params.index(p if p.is_owner else p.owner)
+
+    @property
+    def nbytes(self) -> int:
+        return self.total * 4

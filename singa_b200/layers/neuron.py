@@ -1,0 +1,647 @@
+"""Compute layers: Convolution, InnerProduct, Pooling, LRN, ReLU, Tanh, Dropout, SoftmaxLoss.
+
+Reference: include/worker/layer.h:28-291, src/worker/layer.cc (citations per class).  Every layer has two
+implementations selected once at setup: the native sm_100a path (tcgen05 GEMM + fused epilogues, bf16
+channels-last activations) and the plain-PyTorch fp32 path of ``ops/reference.py`` (CPU oracle / library
+baseline).  Forward/backward only launch kernels on pre-allocated buffers, so a whole training step can be
+captured in a CUDA graph.
+
+Fusions decided by ``NeuralNet.fuse_activations`` (natural fusion boundaries of SURVEY §2.5):
+  * ``fused_act``      — a ReLU/Tanh that is the sole consumer of a conv / inner-product layer runs in that
+                         layer's GEMM epilogue; the activation layer becomes an alias.
+  * ``src_grad_act``   — when the source of a conv / inner-product layer is an activation layer, the data-gradient
+                         GEMM (or col2im) multiplies by act'(y) in its epilogue and writes straight into the
+                         activation's source gradient; the activation layer's backward is skipped.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from ..device import ctx, pad8, step_state
+from ..ops import reference as R
+from ..ops.gemm import ACT_NONE, ACT_RELU, ACT_STANH
+from ..param import param_factory
+from ..proto import schema as S
+from .base import Layer, alloc_act
+
+
+def _K():
+    from ..ops import kernels
+    return kernels
+
+
+class _Workspace:
+    """One growing device scratch buffer shared by layers whose scratch use never overlaps in time
+    (conv data-gradient column buffers, padded gradient copies)."""
+
+    def __init__(self):
+        self.buf: Optional[torch.Tensor] = None
+
+    def reserve(self, nbytes: int) -> None:
+        if self.buf is None or self.buf.numel() < nbytes:
+            self.buf = torch.empty(nbytes, dtype=torch.uint8, device=ctx().device)
+
+    def view(self, shape, dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= s
+        nbytes = n * torch.tensor([], dtype=dtype).element_size()
+        assert self.buf is not None and self.buf.numel() >= nbytes, "workspace not reserved"
+        return self.buf[:nbytes].view(dtype).view(shape)
+
+
+workspace = _Workspace()
+
+
+class NeuronLayer(Layer):
+    """Shared fusion plumbing."""
+
+    def __init__(self):
+        super().__init__()
+        self.fused_act = ACT_NONE          # activation applied in this layer's forward epilogue
+        self.src_grad_act = ACT_NONE       # activation gradient applied in this layer's dgrad epilogue
+        self.src_grad_target: Optional[Layer] = None   # layer whose grad the dgrad writes (skips the act layer)
+
+    def _src_grad(self):
+        """(tensor to write the data gradient into, aux activation output or None)."""
+        src = self.srclayers[0]
+        if self.src_grad_act != ACT_NONE:
+            return self.src_grad_target.grad_for(src), src.data_for(self)
+        return src.grad_for(self), None
+
+    def _need_src_grad(self) -> bool:
+        src = self.srclayers[0]
+        if src.is_datalayer or src.is_parserlayer:
+            return False
+        return src.grad_for(self) is not None or self.src_grad_act != ACT_NONE
+
+
+# ================================================================================================
+# InnerProduct
+# ================================================================================================
+class InnerProductLayer(NeuronLayer):
+    """data = src . W + b with W {vdim, hdim}  (src/worker/layer.cc:162-213)."""
+    type_id = "kInnerProduct"
+
+    def connection_type(self, k):
+        return S.kOneToAll
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        src_shape = self.srclayers[0].shape(self)
+        self.batchsize = src_shape[0]
+        self.vdim = 1
+        for s in src_shape[1:]:
+            self.vdim *= s
+        self.hdim = int(self.proto.inner_product_param.num_output)
+        if self.forced_shape is not None:   # one partition of a layer-partitioned layer
+            self.hdim = self.forced_shape[1]
+            self.proto.inner_product_param.num_output = self.hdim
+        self.bias_term = self.proto.inner_product_param.bias_term
+        self.feeds_loss = any(d.is_losslayer for d in self.dstlayers)
+        self.shape_ = [self.batchsize, self.hdim]
+        native = ctx().is_native
+        self.data = alloc_act(self.shape_, torch.float32 if (self.feeds_loss and native) else None)
+        self.grad = alloc_act(self.shape_)
+        if not hasattr(self, "weight"):
+            protos = list(self.proto.param)
+            while len(protos) < 2:
+                protos.append(S.ParamProto())
+            self.weight = param_factory.create("Param")
+            self.bias = param_factory.create("Param")
+            if not protos[0].name:
+                protos[0].name = "weight"
+            if not protos[1].name:
+                protos[1].name = "bias"
+            # fan_in: the reference passes vdim*hdim (layer.cc:174, survey §2.8 item 4); the intent is vdim
+            self.weight.setup(protos[0], [self.vdim, self.hdim], self.vdim)
+            self.bias.setup(protos[1], [self.hdim], 0)
+        self.src4d = len(src_shape) == 4 and src_shape[1] > 1 and src_shape[2] * src_shape[3] > 1
+        if native:
+            self._setup_native(src_shape)
+
+    def _setup_native(self, src_shape):
+        dev = ctx().device
+        # flatten in the reference's (c,h,w) order: channels-last 4-D sources go through a transpose kernel;
+        # a source whose row stride is not TMA-legal (multiple of 8) is re-strided into x_flat as well
+        self.x_flat = None
+        self.dx_flat = None
+        if self.src4d or self.vdim % 8 != 0:
+            self.x_flat = alloc_act([self.batchsize, self.vdim])
+            self.dx_flat = alloc_act([self.batchsize, self.vdim])
+        # weight operand: the arena's bf16 mirror when hdim is a multiple of 8, else a padded packed copy
+        if self.hdim % 8 != 0:
+            packed = torch.zeros(self.vdim, pad8(self.hdim), dtype=torch.bfloat16, device=dev)
+            self.weight.data16 = packed[:, :self.hdim]
+
+            def pack(w=self.weight, dst=packed):
+                _K().cast_pack(w.data, self.hdim, dst, dst.stride(0), self.vdim, self.hdim)
+            self.weight.pack16 = pack
+
+    def get_params(self):
+        return [self.weight, self.bias] if self.bias_term else [self.weight]
+
+    def _flat2d(self, t):
+        """2-D [batch, vdim] alias of ``t`` when its memory order already is the reference's flatten order."""
+        if t.dim() == 2:
+            return t
+        v = t.reshape(self.batchsize, self.vdim)
+        assert v.data_ptr() == t.data_ptr(), f"{self.name}: unexpected copy while flattening"
+        return v
+
+    def _x2d(self):
+        src = self.srclayers[0].data_for(self)
+        if not ctx().is_native:
+            return src.reshape(self.batchsize, self.vdim).float()
+        K = _K()
+        if self.src4d:
+            n, c, h, w = src.shape
+            if self.vdim % 8 == 0:
+                K.transpose_planes(src, self.x_flat, n, h * w, c)      # NHWC -> (c,h,w) order
+            else:
+                self.x_flat.copy_(src.reshape(self.batchsize, self.vdim))
+            return self.x_flat
+        x = self._flat2d(src)
+        if x.stride(0) % 8 != 0:
+            K.copy2d_bf16(x, x.stride(0), self.x_flat, self.x_flat.stride(0), self.batchsize, self.vdim)
+            return self.x_flat
+        return x
+
+    def _w16(self):
+        w = self.weight if self.weight.is_owner else self.weight.owner
+        return w.data16
+
+    def compute_feature(self, training):
+        x = self._x2d()
+        if ctx().is_native:
+            K = _K()
+            w16 = self._w16()
+            out32 = self.data if self.data.dtype == torch.float32 else None
+            out16 = self.data if self.data.dtype == torch.bfloat16 else None
+            K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, out32=out32,
+                   out16=out16, bias=self.bias.data if self.bias_term else None, act=self.fused_act)
+            self._x_saved = x
+        else:
+            y = R.ip_fwd(x, self.weight.data, self.bias.data if self.bias_term else None)
+            if self.fused_act == ACT_RELU:
+                y = R.relu_fwd(y)
+            elif self.fused_act == ACT_STANH:
+                y = R.stanh_fwd(y)
+            self.data.copy_(y)
+            self._x_saved = x
+
+    def compute_gradient(self):
+        dy = self.grad
+        x = self._x_saved
+        need_dx = self._need_src_grad()
+        if ctx().is_native:
+            K = _K()
+            accumulate = getattr(self, "_accumulate_wgrad", False)
+            if self.bias_term:
+                K.colsum(dy, self.batchsize, self.hdim, dy.stride(0), self.bias.grad, accumulate=accumulate)
+            # dW[vdim][hdim] = X^T dY : A = X stored [K=batch][M=vdim], B = dY stored [K=batch][N=hdim]
+            K.gemm(x, dy, self.vdim, self.hdim, self.batchsize, a_mn=True, b_mn=True,
+                   out32=self.weight.grad, accumulate=accumulate)
+            if need_dx:
+                dst, aux = self._src_grad()
+                w16 = self._w16()
+                if self.src4d:
+                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=self.dx_flat)
+                    n, c, h, w = self.srclayers[0].shape(self)
+                    if self.vdim % 8 == 0:
+                        K.transpose_planes(self.dx_flat, dst, n, c, h * w)   # (c,h,w) -> NHWC
+                    else:
+                        dst.copy_(self.dx_flat.reshape(dst.shape))
+                    if aux is not None:
+                        K.act_bwd(dst, aux, dst, self.src_grad_act)
+                else:
+                    d2 = self._flat2d(dst)
+                    a2 = self._flat2d(aux) if aux is not None else None
+                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=d2,
+                           grad_act=self.src_grad_act, aux=a2)
+        else:
+            dx, dw, db = R.ip_bwd(x, self.weight.data, dy.float(), need_dx)
+            self.weight.grad.copy_(dw)
+            if self.bias_term:
+                self.bias.grad.copy_(db)
+            if need_dx:
+                dst, aux = self._src_grad()
+                if aux is not None:
+                    a = aux.reshape(self.batchsize, self.vdim).float()
+                    dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
+                dst.copy_(dx.view(dst.shape))
+
+
+# ================================================================================================
+# Convolution
+# ================================================================================================
+class ConvolutionLayer(NeuronLayer):
+    """weight {F, C*k*k}, bias {F}; out = (H + 2p - k)/s + 1  (src/worker/layer.cc:18-123).
+
+    Native path: ONE batched GEMM over all images, D[pixels][F] = col[pixels][k*k*C] . W16[F][k*k*C]^T with
+    bias(+ReLU) in the epilogue, writing channels-last output directly; wgrad and dgrad are GEMMs too."""
+    type_id = "kConvolution"
+
+    def connection_type(self, k):
+        return S.kOneToAll
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        cp = self.proto.convolution_param
+        self.kernel, self.pad, self.stride = int(cp.kernel), int(cp.pad), int(cp.stride)
+        assert self.kernel > 0, "Filter size cannot be zero."
+        self.num_filters = int(cp.num_filters)
+        if self.forced_shape is not None:
+            self.num_filters = self.forced_shape[1]
+            cp.num_filters = self.num_filters
+        self.bias_term = cp.bias_term
+        ss = self.srclayers[0].shape(self)
+        assert len(ss) > 2, f"{self.name}: convolution needs an image source, got shape {ss}"
+        self.width, self.height = ss[-1], ss[-2]
+        self.channels = ss[-3] if len(ss) > 3 else 1
+        self.batchsize = ss[0]
+        self.conv_height = (self.height + 2 * self.pad - self.kernel) // self.stride + 1
+        self.conv_width = (self.width + 2 * self.pad - self.kernel) // self.stride + 1
+        self.col_height = self.channels * self.kernel * self.kernel
+        self.col_width = self.conv_height * self.conv_width
+        self._alloc([self.batchsize, self.num_filters, self.conv_height, self.conv_width])
+        if not hasattr(self, "weight"):
+            protos = list(self.proto.param)
+            while len(protos) < 2:
+                protos.append(S.ParamProto())
+            if not protos[0].name:
+                protos[0].name = "weight"
+            if not protos[1].name:
+                protos[1].name = "bias"
+            self.weight = param_factory.create("Param")
+            self.bias = param_factory.create("Param")
+            self.weight.setup(protos[0], [self.num_filters, self.col_height], self.col_height)
+            self.bias.setup(protos[1], [self.num_filters], 0)
+        if ctx().is_native:
+            self._setup_native()
+
+    def _setup_native(self):
+        dev = ctx().device
+        F_, K_ = self.num_filters, self.col_height
+        self.P = self.batchsize * self.col_width
+        self.Kpad = pad8(K_)
+        self.Fpad = pad8(F_)
+        self.pointwise = self.kernel == 1 and self.stride == 1 and self.pad == 0 and self.channels % 8 == 0
+        # per-layer column buffer kept from forward to backward (HBM is plentiful; no recompute)
+        self.col = None if self.pointwise else torch.zeros(self.P, self.Kpad, dtype=torch.bfloat16, device=dev)
+        # bf16 weights repacked to (ky,kx,c) column order to match the channels-last patches
+        self.w16_packed = torch.zeros(F_, self.Kpad, dtype=torch.bfloat16, device=dev)
+        self.weight.data16 = self.w16_packed[:, :K_]
+        kk = self.kernel * self.kernel
+
+        def pack(w=self.weight, dst=self.w16_packed):
+            _K().cast_pack(w.data, K_, dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
+        self.weight.pack16 = pack
+        # scratch shared across layers: dcol [P][Kpad] and (if F % 8 != 0) a padded copy of dy [P][Fpad]
+        self.ws_bytes = self.P * self.Kpad * 2 + (self.P * self.Fpad * 2 if F_ % 8 else 0)
+        workspace.reserve(self.ws_bytes)
+
+    def get_params(self):
+        return [self.weight, self.bias] if self.bias_term else [self.weight]
+
+    def _w16(self):
+        w = self.weight if self.weight.is_owner else self.weight.owner
+        return w.data16
+
+    def _src_nhwc(self):
+        src = self.srclayers[0].data_for(self)
+        if src.dim() == 3:
+            return src   # {N,H,W}: C == 1, contiguous == channels-last
+        return src
+
+    def compute_feature(self, training):
+        src = self._src_nhwc()
+        if ctx().is_native:
+            K = _K()
+            N, H, W, C = self.batchsize, self.height, self.width, self.channels
+            if self.pointwise:
+                col, ld = src.permute(0, 2, 3, 1).reshape(self.P, C), C
+            else:
+                K.im2col_nhwc(src, self.col, self.Kpad, N, H, W, C, self.conv_height, self.conv_width,
+                              self.kernel, self.stride, self.pad)
+                col = self.col[:, :self.col_height]
+            y2d = self.data.permute(0, 2, 3, 1).reshape(self.P, self.num_filters)   # view of NHWC storage
+            assert y2d.data_ptr() == self.data.data_ptr()
+            K.gemm(col, self._w16(), self.P, self.num_filters, self.col_height,
+                   out16=y2d, bias=self.bias.data if self.bias_term else None, act=self.fused_act)
+            self._col_saved = col
+        else:
+            x = src.float()
+            if x.dim() == 3:
+                x = x.unsqueeze(1)
+            y = R.conv_fwd(x, self.weight.data, self.bias.data if self.bias_term else None, self.kernel,
+                           self.stride, self.pad)
+            if self.fused_act == ACT_RELU:
+                y = R.relu_fwd(y)
+            elif self.fused_act == ACT_STANH:
+                y = R.stanh_fwd(y)
+            self.data.copy_(y)
+            self._x_saved = x
+
+    def compute_gradient(self):
+        need_dx = self._need_src_grad()
+        if ctx().is_native:
+            K = _K()
+            F_, K_, P = self.num_filters, self.col_height, self.P
+            dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
+            accumulate = getattr(self, "_accumulate_wgrad", False)
+            if self.bias_term:
+                K.colsum(dy2d, P, F_, F_, self.bias.grad, accumulate=accumulate)
+            if F_ % 8:
+                dyp = workspace.view((P, self.Fpad), torch.bfloat16)
+                K.copy2d_bf16(dy2d, F_, dyp, self.Fpad, P, F_)
+                dy_op = dyp[:, :F_]
+                ws_off = P * self.Fpad * 2
+            else:
+                dy_op, ws_off = dy2d, 0
+            col = self._col_saved
+            kk = self.kernel * self.kernel
+            # dW[F][K] = dY^T col : A = dY stored [K=P][M=F], B = col stored [K=P][N=K_]; columns come out in
+            # (ky,kx,c) order and are stored in the reference's (c,ky,kx) order by the epilogue permutation
+            K.gemm(dy_op, col, F_, K_, P, a_mn=True, b_mn=True, out32=self.weight.grad, accumulate=accumulate,
+                   perm=(self.channels, kk) if kk > 1 and self.channels > 1 else None)
+            if need_dx:
+                dst, aux = self._src_grad()
+                N, H, W, C = self.batchsize, self.height, self.width, self.channels
+                if self.pointwise:
+                    d2 = dst.permute(0, 2, 3, 1).reshape(P, C)
+                    a2 = aux.permute(0, 2, 3, 1).reshape(P, C) if aux is not None else None
+                    K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=d2,
+                           grad_act=self.src_grad_act, aux=a2)
+                else:
+                    dcol = workspace.buf[ws_off:ws_off + P * self.Kpad * 2].view(torch.bfloat16).view(P, self.Kpad)
+                    # dcol[P][K] = dY[P][F] . W16[F][K] : B(n=K idx, k=F idx) stored [K=F][N=K_]
+                    K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=dcol[:, :K_])
+                    K.col2im_nhwc(dcol, self.Kpad, dst, N, H, W, C, self.conv_height, self.conv_width,
+                                  self.kernel, self.stride, self.pad, self.src_grad_act, aux)
+        else:
+            dx, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
+                                    self.stride, self.pad, need_dx)
+            self.weight.grad.copy_(dw)
+            if self.bias_term:
+                self.bias.grad.copy_(db)
+            if need_dx:
+                dst, aux = self._src_grad()
+                if aux is not None:
+                    a = aux.float().view(dx.shape)
+                    dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
+                dst.copy_(dx.view(dst.shape))
+
+
+# ================================================================================================
+# Activations
+# ================================================================================================
+class ActivationLayer(NeuronLayer):
+    act = ACT_NONE
+
+    def __init__(self):
+        super().__init__()
+        self.fwd_fused = False    # computed by the producer's epilogue
+        self.bwd_fused = False    # computed by the consumer's dgrad epilogue
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        src = self.srclayers[0]
+        self.shape_ = src.shape(self)
+        self.data = alloc_act(self.shape_)
+        self.grad = alloc_act(self.shape_)
+
+    def alias_to_source(self):
+        """Forward fused into the producer: this layer's output IS the producer's output buffer, and the
+        gradient w.r.t. the pre-activation is computed in place in the producer's gradient buffer."""
+        src = self.srclayers[0]
+        self.data = src.data_for(self)
+        self.grad = src.grad_for(self)
+        self.fwd_fused = True
+
+    def compute_feature(self, training):
+        if self.fwd_fused:
+            return
+        x = self.srclayers[0].data_for(self)
+        if ctx().is_native:
+            _K().act_fwd(x, self.data, self.act)
+        else:
+            self.data.copy_(R.relu_fwd(x) if self.act == ACT_RELU else R.stanh_fwd(x))
+
+    def compute_gradient(self):
+        if self.bwd_fused:
+            return
+        dst = self.srclayers[0].grad_for(self)
+        if dst is None:
+            return
+        if ctx().is_native:
+            _K().act_bwd(self.grad, self.data, dst, self.act)   # in place when grad aliases dst
+        else:
+            g, y = self.grad.float(), self.data.float()
+            dst.copy_(R.relu_bwd(g, y) if self.act == ACT_RELU else R.stanh_bwd(g, y))
+
+
+class ReLULayer(ActivationLayer):
+    """max(x, 0); ``negative_slope`` is accepted and, as in the reference, unused (layer.cc:544-569)."""
+    type_id = "kReLU"
+    act = ACT_RELU
+
+
+class TanhLayer(ActivationLayer):
+    """1.7159047 tanh(0.66666667 x) — the reference hard-codes the scales (layer.cc:675-701)."""
+    type_id = "kTanh"
+    act = ACT_STANH
+
+
+class DropoutLayer(NeuronLayer):
+    """Training: y = x * mask / pkeep with a counter-RNG mask regenerated in backward (no mask tensor);
+    test: identity (the reference applies the mask at test time too — survey §2.8 item 5 — not kept)."""
+    type_id = "kDropout"
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        self.pkeep = 1.0 - self.proto.dropout_param.dropout_ratio
+        self._alloc(self.srclayers[0].shape(self))
+        self.seed_base = (hash(self.name) & 0xFFFFFF) << 20
+        self.step_seed = 0
+        self._training = False
+
+    def set_step(self, step: int) -> None:
+        self.step_seed = self.seed_base + step
+
+    def compute_feature(self, training):
+        x = self.srclayers[0].data_for(self)
+        self._training = training
+        if not training:
+            self.data.copy_(x)
+            return
+        if ctx().is_native:
+            _K().dropout(x, self.data, self.pkeep, self.seed_base, step_state()["step"])
+        else:
+            m = R.dropout_mask(self.seed_base + int(step_state()['host_step'][0]), x.numel(), self.pkeep, x.device).view(x.shape)
+            self._mask = m
+            self.data.copy_(x.float() * m)
+
+    def compute_gradient(self):
+        dst = self.srclayers[0].grad_for(self)
+        if dst is None:
+            return
+        if not self._training:
+            dst.copy_(self.grad)
+        elif ctx().is_native:
+            _K().dropout(self.grad, dst, self.pkeep, self.seed_base, step_state()["step"])
+        else:
+            dst.copy_(self.grad.float() * self._mask)
+
+
+# ================================================================================================
+# Pooling / LRN
+# ================================================================================================
+class PoolingLayer(NeuronLayer):
+    """MAX / AVE over k x k windows, stride s, output size in ceil form with clipped windows; AVE divides by
+    k^2 (src/worker/layer.cc:476-540).  Padding is honoured (the reference reads ``pad_`` uninitialised)."""
+    type_id = "kPooling"
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        pp = self.proto.pooling_param
+        self.kernel, self.stride, self.pad = int(pp.kernel), int(pp.stride), int(pp.pad)
+        assert self.pad < self.kernel
+        self.is_max = pp.pool == S.enum_value("PoolingProto.PoolMethod", "MAX")
+        ss = self.srclayers[0].shape(self)
+        assert len(ss) > 2
+        self.width, self.height = ss[-1], ss[-2]
+        self.channels = ss[-3] if len(ss) > 3 else 1
+        self.batchsize = ss[0]
+        self.pooled_height = R.pool_out_size(self.height, self.kernel, self.stride, self.pad)
+        self.pooled_width = R.pool_out_size(self.width, self.kernel, self.stride, self.pad)
+        self._alloc([self.batchsize, self.channels, self.pooled_height, self.pooled_width])
+
+    def compute_feature(self, training):
+        x = self.srclayers[0].data_for(self)
+        if ctx().is_native:
+            _K().pool_fwd(x, self.data, self.batchsize, self.height, self.width, self.channels,
+                          self.pooled_height, self.pooled_width, self.kernel, self.stride, self.pad, self.is_max)
+        else:
+            x4 = x.float().view(self.batchsize, self.channels, self.height, self.width)
+            self.data.copy_(R.pool_fwd(x4, self.kernel, self.stride, self.pad, self.is_max))
+
+    def compute_gradient(self):
+        src = self.srclayers[0]
+        dst = src.grad_for(self)
+        if dst is None:
+            return
+        x = src.data_for(self)
+        if ctx().is_native:
+            _K().pool_bwd(x, self.data, self.grad, dst, self.batchsize, self.height, self.width, self.channels,
+                          self.pooled_height, self.pooled_width, self.kernel, self.stride, self.pad, self.is_max)
+        else:
+            x4 = x.float().view(self.batchsize, self.channels, self.height, self.width)
+            dst.copy_(R.pool_bwd(x4, self.data.float(), self.grad.float(), self.kernel, self.stride, self.pad,
+                                 self.is_max).view(dst.shape))
+
+
+class LRNLayer(NeuronLayer):
+    """Across-channel local response normalisation (src/worker/layer.cc:331-378).  WITHIN_CHANNEL is declared in
+    the schema but, as in the reference, not implemented."""
+    type_id = "kLRN"
+
+    def setup(self):
+        assert len(self.srclayers) == 1
+        lp = self.proto.lrn_param
+        self.lsize = int(lp.local_size)
+        assert self.lsize % 2 == 1, "LRN only supports odd values for Localvol"
+        if lp.norm_region != S.enum_value("LRNProto.NormRegion", "ACROSS_CHANNELS"):
+            raise NotImplementedError("LRN WITHIN_CHANNEL is not implemented (neither is it in the reference)")
+        self.alpha, self.beta, self.knorm = lp.alpha, lp.beta, lp.knorm
+        ss = self.srclayers[0].shape(self)
+        assert len(ss) == 4
+        self.batchsize, self.channels, self.height, self.width = ss
+        self._alloc(ss)
+        self.norm = alloc_act(ss, torch.float32)
+
+    def compute_feature(self, training):
+        x = self.srclayers[0].data_for(self)
+        if ctx().is_native:
+            _K().lrn_fwd(x, self.data, self.norm, self.batchsize * self.height * self.width, self.channels,
+                         self.lsize, self.alpha, self.beta, self.knorm)
+        else:
+            y, nm = R.lrn_fwd(x.float(), self.lsize, self.alpha, self.beta, self.knorm)
+            self.data.copy_(y)
+            self.norm.copy_(nm)
+
+    def compute_gradient(self):
+        src = self.srclayers[0]
+        dst = src.grad_for(self)
+        if dst is None:
+            return
+        x = src.data_for(self)
+        if ctx().is_native:
+            _K().lrn_bwd(x, self.norm, self.grad, dst, self.batchsize * self.height * self.width,
+                         self.channels, self.lsize, self.alpha, self.beta)
+        else:
+            dst.copy_(R.lrn_bwd(x.float(), self.norm, self.grad.float(), self.lsize, self.alpha, self.beta))
+
+
+# ================================================================================================
+# Loss
+# ================================================================================================
+class LossLayer(NeuronLayer):
+    is_losslayer = True
+
+    def __init__(self):
+        super().__init__()
+        self.metric: Optional[torch.Tensor] = None
+
+
+class SoftmaxLossLayer(LossLayer):
+    """Softmax + NLL + top-k accuracy; metric = scale * [mean loss, accuracy]; gradient (p - onehot) scale / N
+    written straight into the logits layer's gradient buffer in the forward pass
+    (src/worker/layer.cc:703-764)."""
+    type_id = "kSoftmaxLoss"
+
+    @property
+    def partition_type(self):
+        pt = self.proto.partition_type if self.proto.HasField("partition_type") else S.kNone
+        return S.kNone if pt == S.kLayerPartition else pt   # include/worker/layer.h:216-221
+
+    def connection_type(self, k):
+        return S.kOneToAll
+
+    def setup(self):
+        assert len(self.srclayers) == 2, f"{self.name}: softmax loss needs (logits, label) sources"
+        ss = self.srclayers[0].shape(self)
+        self.batchsize = ss[0]
+        self.dim = 1
+        for s in ss[1:]:
+            self.dim *= s
+        self.topk = int(self.proto.softmaxloss_param.topk)
+        self.scale = float(self.proto.softmaxloss_param.scale)
+        self.shape_ = [self.batchsize, self.dim]
+        self.data = alloc_act(self.shape_, torch.float32)   # probabilities
+        self.grad = None
+        self.metric = torch.zeros(2, dtype=torch.float32, device=ctx().device)
+
+    def compute_feature(self, training):
+        logits = self.srclayers[0].data_for(self)
+        labels = self.srclayers[1].data_for(self)
+        # ``metric`` ACCUMULATES over steps on the device (Performance divides by its step counter and zeroes
+        # it at the end of a display window), so no host round trip or memset sits in the step.
+        if ctx().is_native:
+            g = self.srclayers[0].grad_for(self) if training else None
+            l2 = logits if logits.dim() == 2 else logits.view(self.batchsize, self.dim)
+            _K().softmax_loss(l2, l2.stride(0), labels, self.batchsize, self.dim, self.topk, self.scale,
+                              self.data, g, g.stride(0) if g is not None else 0, self.metric)
+        else:
+            m, g = R.softmax_loss(logits.float().view(self.batchsize, self.dim), labels, self.topk, self.scale)
+            self.metric.add_(m)
+            self._g = g
+
+    def compute_gradient(self):
+        if ctx().is_native:
+            return   # gradient already written by the fused forward kernel
+        dst = self.srclayers[0].grad_for(self)
+        if dst is not None:
+            dst.copy_(self._g.view(dst.shape))

@@ -1,12 +1,43 @@
-"""argtypes for the non-GEMM entry points (kept next to include/singa_b200.h, one block per section)."""
+"""ctypes signatures of the non-GEMM entry points, in the order of include/singa_b200.h."""
 import ctypes as C
 
-vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong
+
+
+class Updater(C.Structure):
+    _fields_ = [("kind", i32), ("lr", f32), ("momentum", f32), ("weight_decay", f32), ("delta", f32),
+                ("rho", f32), ("grad_scale", f32), ("lr_dev", vp)]
+
+
+SIGNATURES = {
+    "sg_act_fwd": [vp, vp, i64, i32, i32, vp],
+    "sg_act_bwd": [vp, vp, vp, i64, i32, i32, vp],
+    "sg_dropout": [vp, vp, i64, f32, u64, vp, i32, vp],
+    "sg_colsum": [vp, i64, i32, i32, vp, i32, i32, vp],
+    "sg_cast_pack": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
+    "sg_convert": [vp, i32, vp, i32, i64, vp],
+    "sg_copy2d_bf16": [vp, i64, vp, i64, i32, i32, vp],
+    "sg_transpose_planes": [vp, i32, vp, i32, i32, i32, i32, vp],
+    "sg_asum": [vp, i64, vp, i32, vp],
+    "sg_fill_random": [vp, i64, i32, f32, f32, f32, u64, vp],
+    "sg_mnist_parse": [vp, vp, i64, f32, f32, i32, vp],
+    "sg_rgb_parse": [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, f32, i32, vp],
+    "sg_softmax_loss": [vp, i64, vp, i32, i32, i32, f32, vp, i64, vp, i64, i32, vp, vp],
+    "sg_pool_fwd": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "sg_pool_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "sg_lrn_fwd": [vp, vp, vp, i64, i32, i32, f32, f32, f32, i32, vp],
+    "sg_lrn_bwd": [vp, vp, vp, vp, i64, i32, i32, f32, f32, i32, vp],
+    "sg_im2col_nhwc": [vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "sg_col2im_nhwc": [vp, i64, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp],
+    "sg_update_arena": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.POINTER(Updater), vp],
+    "sg_easgd_sync": [vp, vp, i64, f32, vp, vp],
+    "sg_randomsync": [vp, vp, vp, i64, f32, u64, vp, vp, vp],
+}
 
 
 def declare_all(lib):
-    def d(name, *args, res=C.c_int):
+    for name, args in SIGNATURES.items():
         if hasattr(lib, name):
             fn = getattr(lib, name)
             fn.argtypes = list(args)
-            fn.restype = res
+            fn.restype = C.c_int

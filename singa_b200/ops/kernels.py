@@ -1,0 +1,136 @@
+"""Thin Python wrappers over the native sm_100a kernels (one function per entry point of
+``include/singa_b200.h``).  They take CUDA torch tensors, launch on the current torch stream and write their
+outputs in place.  4-D activations are channels-last (N,H,W,C contiguous)."""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import native
+from ._decl import Updater
+from .gemm import ACT_NONE, ACT_RELU, ACT_STANH, gemm  # noqa: F401  (re-exported)
+
+
+def _lib():
+    return native.require()
+
+
+def _bf(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return 1
+    assert t.dtype == torch.float32, t.dtype
+    return 0
+
+
+def _call(name: str, *args):
+    rc = getattr(_lib(), name)(*args, native.stream_ptr())
+    native.check(rc, name)
+    native.count_launch()
+
+
+def act_fwd(x, y, act):
+    _call("sg_act_fwd", x.data_ptr(), y.data_ptr(), x.numel(), act, _bf(x))
+
+
+def act_bwd(dy, y, dx, act):
+    _call("sg_act_bwd", dy.data_ptr(), y.data_ptr(), dx.data_ptr(), dy.numel(), act, _bf(dy))
+
+
+def dropout(x, y, pkeep: float, seed: int, seed_dev=None):
+    _call("sg_dropout", x.data_ptr(), y.data_ptr(), x.numel(), float(pkeep), seed & (2**64 - 1),
+          native.ptr(seed_dev), _bf(x))
+
+
+def colsum(x, rows, cols, ld, out, accumulate=False):
+    _call("sg_colsum", x.data_ptr(), ld, rows, cols, out.data_ptr(), 1 if accumulate else 0, _bf(x))
+
+
+def cast_pack(src, lds, dst, ldd, rows, cols, perm=(0, 0)):
+    _call("sg_cast_pack", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols, perm[0], perm[1])
+
+
+def convert(src, dst):
+    _call("sg_convert", src.data_ptr(), _bf(src), dst.data_ptr(), _bf(dst), src.numel())
+
+
+def copy2d_bf16(src, lds, dst, ldd, rows, cols):
+    _call("sg_copy2d_bf16", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols)
+
+
+def transpose_planes(src, dst, batch, rows, cols):
+    _call("sg_transpose_planes", src.data_ptr(), _bf(src), dst.data_ptr(), _bf(dst), batch, rows, cols)
+
+
+def asum(x, out):
+    _call("sg_asum", x.data_ptr(), x.numel(), out.data_ptr(), _bf(x))
+
+
+def fill_random(dst, kind: int, a: float, b: float, scale: float, seed: int):
+    _call("sg_fill_random", dst.data_ptr(), dst.numel(), kind, float(a), float(b), float(scale),
+          seed & (2**64 - 1))
+
+
+def mnist_parse(src_u8, dst, norm_a, norm_b):
+    _call("sg_mnist_parse", src_u8.data_ptr(), dst.data_ptr(), src_u8.numel(), float(norm_a), float(norm_b),
+          _bf(dst))
+
+
+def rgb_parse(src_u8, mean, dst, batch, C, H, W, crop, off_h, off_w, mirror, scale):
+    _call("sg_rgb_parse", src_u8.data_ptr(), native.ptr(mean), dst.data_ptr(), batch, C, H, W, crop,
+          native.ptr(off_h), native.ptr(off_w), native.ptr(mirror), float(scale), _bf(dst))
+
+
+def softmax_loss(logits, ldl, labels, rows, dim, topk, scale, prob, grad, ldg, metric):
+    _call("sg_softmax_loss", logits.data_ptr(), ldl, labels.data_ptr(), rows, dim, topk, float(scale),
+          native.ptr(prob), prob.stride(0) if prob is not None else 0, native.ptr(grad), ldg,
+          _bf(grad) if grad is not None else 0, native.ptr(metric))
+
+
+def pool_fwd(x, y, N, H, W, C, OH, OW, k, s, pad, is_max):
+    _call("sg_pool_fwd", x.data_ptr(), y.data_ptr(), N, H, W, C, OH, OW, k, s, pad, 1 if is_max else 0, _bf(x))
+
+
+def pool_bwd(x, y, dy, dx, N, H, W, C, OH, OW, k, s, pad, is_max):
+    _call("sg_pool_bwd", x.data_ptr(), y.data_ptr(), dy.data_ptr(), dx.data_ptr(), N, H, W, C, OH, OW, k, s,
+          pad, 1 if is_max else 0, _bf(x))
+
+
+def lrn_fwd(x, y, norm, pixels, C, lsize, alpha, beta, knorm):
+    _call("sg_lrn_fwd", x.data_ptr(), y.data_ptr(), norm.data_ptr(), pixels, C, lsize, float(alpha),
+          float(beta), float(knorm), _bf(x))
+
+
+def lrn_bwd(x, norm, dy, dx, pixels, C, lsize, alpha, beta):
+    _call("sg_lrn_bwd", x.data_ptr(), norm.data_ptr(), dy.data_ptr(), dx.data_ptr(), pixels, C, lsize,
+          float(alpha), float(beta), _bf(x))
+
+
+def im2col_nhwc(x, col, ld, N, H, W, C, OH, OW, k, s, pad):
+    _call("sg_im2col_nhwc", x.data_ptr(), col.data_ptr(), ld, N, H, W, C, OH, OW, k, s, pad)
+
+
+def col2im_nhwc(dcol, ld, dx, N, H, W, C, OH, OW, k, s, pad, grad_act=ACT_NONE, aux=None):
+    _call("sg_col2im_nhwc", dcol.data_ptr(), ld, dx.data_ptr(), N, H, W, C, OH, OW, k, s, pad, grad_act,
+          native.ptr(aux))
+
+
+UPD_SGD, UPD_NESTEROV, UPD_ADAGRAD, UPD_RMSPROP, UPD_ADADELTA = range(5)
+ARENA_CHUNK = 1024
+
+
+def update_arena(w, g, h, u, w16, chunk_param, lr_mult, wd_mult, first_chunk, nchunks, *, kind, lr,
+                 momentum=0.0, weight_decay=0.0, delta=1e-7, rho=0.9, grad_scale=1.0, lr_dev=None):
+    up = Updater(kind, lr, momentum, weight_decay, delta, rho, grad_scale, native.ptr(lr_dev))
+    _call("sg_update_arena", w.data_ptr(), g.data_ptr(), native.ptr(h), native.ptr(u), native.ptr(w16),
+          chunk_param.data_ptr(), lr_mult.data_ptr(), wd_mult.data_ptr(), first_chunk, nchunks,
+          ctypes.byref(up))
+
+
+def easgd_sync(w, server, alpha, w16=None):
+    _call("sg_easgd_sync", w.data_ptr(), server.data_ptr(), w.numel(), float(alpha), native.ptr(w16))
+
+
+def randomsync(w, snap, server, ratio, seed, w16=None, nselected=None):
+    _call("sg_randomsync", w.data_ptr(), snap.data_ptr(), server.data_ptr(), w.numel(), float(ratio),
+          seed & (2**64 - 1), native.ptr(w16), native.ptr(nselected))

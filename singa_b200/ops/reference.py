@@ -1,0 +1,276 @@
+"""Plain-PyTorch fp32 restatement of every layer / updater / init rule of the reference.
+
+This module is (a) the CPU execution path (BASELINE config 1, CI without a GPU), (b) the oracle that the
+native kernels are tested against, and (c) on a GPU, the cuBLAS/cuDNN "library baseline" backend.
+All functions take/return logical NCHW tensors and never touch the native library.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+STANH_A, STANH_B = 1.7159047, 0.66666667
+FLT_MIN = 1.17549435e-38
+
+
+# ------------------------------------------------------------------------------------------- activations
+def relu_fwd(x):
+    return torch.clamp_min(x, 0)
+
+
+def relu_bwd(dy, y):
+    return dy * (y > 0).to(dy.dtype)
+
+
+def stanh_fwd(x):
+    """1.7159047 * tanh(0.66666667 x)  (include/mshadow/cxxnet_op.h:77-81)."""
+    return STANH_A * torch.tanh(STANH_B * x)
+
+
+def stanh_bwd(dy, y):
+    """dy * (A*B - B/A * y^2)  (cxxnet_op.h:83-87)."""
+    return dy * (STANH_A * STANH_B - (STANH_B / STANH_A) * y * y)
+
+
+# ------------------------------------------------------------------------------------------- philox
+def philox_uniform(seed: int, n: int, device="cpu") -> torch.Tensor:
+    """n uniforms in [0,1): element e uses counter e//4, lane e%4 — bit-identical to csrc/philox.cuh."""
+    n4 = (n + 3) // 4
+    idx = torch.arange(n4, dtype=torch.int64, device=device)
+    M32 = 0xFFFFFFFF
+    c = [idx & M32, (idx >> 32) & M32, torch.zeros_like(idx), torch.zeros_like(idx)]
+    k0, k1 = seed & M32, (seed >> 32) & M32
+    M0, M1, W0, W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
+
+    def mulhilo(a: int, b: torch.Tensor):
+        # 32x32 -> 64 without overflowing int64: split b into 16-bit halves
+        b_lo, b_hi = b & 0xFFFF, b >> 16
+        p_lo = a * b_lo                      # < 2^48
+        p_hi = a * b_hi                      # < 2^48
+        lo = (p_lo + ((p_hi & 0xFFFF) << 16))
+        carry = lo >> 32
+        hi = (p_hi >> 16) + carry
+        return hi & M32, lo & M32
+
+    for _ in range(10):
+        hi0, lo0 = mulhilo(M0, c[0])
+        hi1, lo1 = mulhilo(M1, c[2])
+        c = [(hi1 ^ c[1] ^ k0) & M32, lo1, (hi0 ^ c[3] ^ k1) & M32, lo0]
+        k0 = (k0 + W0) & M32
+        k1 = (k1 + W1) & M32
+    u = torch.stack([(ci >> 8).to(torch.float32) * (1.0 / 16777216.0) for ci in c], dim=1).reshape(-1)
+    return u[:n]
+
+
+def dropout_mask(seed: int, n: int, pkeep: float, device="cpu") -> torch.Tensor:
+    return (philox_uniform(seed, n, device) < pkeep).to(torch.float32) / pkeep
+
+
+# ------------------------------------------------------------------------------------------- pooling
+def pool_out_size(h: int, k: int, s: int, pad: int = 0) -> int:
+    """ceil((h + 2p - k)/s) + 1 with the last window required to start inside the padded image
+    (the reference's ceil form, src/worker/layer.cc:498-501, made consistent with the window clipping of
+    include/mshadow/tensor_expr_ext.h:790-811 — the ceil/floor mismatch of the survey's §2.8 is not kept)."""
+    o = int(math.ceil((h + 2 * pad - k) / s)) + 1
+    if pad > 0 and (o - 1) * s >= h + pad:
+        o -= 1
+    return max(o, 1)
+
+
+def _windows(x, k, s, pad, oh, ow, fill):
+    """[N,C,oh,ow,k*k] view of clipped windows (out-of-image taps = fill)."""
+    n, c, h, w = x.shape
+    need_h = (oh - 1) * s + k
+    need_w = (ow - 1) * s + k
+    xp = F.pad(x, (pad, max(0, need_w - w - pad), pad, max(0, need_h - h - pad)), value=fill)
+    cols = F.unfold(xp, kernel_size=k, stride=s)          # [N, C*k*k, L]
+    L = cols.shape[-1]
+    full_ow = (xp.shape[-1] - k) // s + 1
+    cols = cols.view(n, c, k * k, L // full_ow, full_ow)[:, :, :, :oh, :ow]
+    return cols.permute(0, 1, 3, 4, 2)
+
+
+def pool_fwd(x, k, s, pad, is_max):
+    n, c, h, w = x.shape
+    oh, ow = pool_out_size(h, k, s, pad), pool_out_size(w, k, s, pad)
+    if is_max:
+        return _windows(x, k, s, pad, oh, ow, float("-inf")).amax(dim=-1)
+    return _windows(x, k, s, pad, oh, ow, 0.0).sum(dim=-1) / (k * k)
+
+
+def pool_bwd(x, y, dy, k, s, pad, is_max):
+    """MAX: gradient goes to EVERY input equal to the window max (mshadow unpool, tensor_expr_ext.h:819-848);
+    AVE: dy / k^2 to every tap."""
+    n, c, h, w = x.shape
+    oh, ow = y.shape[2], y.shape[3]
+    dx = torch.zeros_like(x)
+    for ky in range(k):
+        for kx in range(k):
+            # taps: input (oy*s - pad + ky, ox*s - pad + kx)
+            iy = torch.arange(oh, device=x.device) * s - pad + ky
+            ix = torch.arange(ow, device=x.device) * s - pad + kx
+            vy = (iy >= 0) & (iy < h)
+            vx = (ix >= 0) & (ix < w)
+            if not vy.any() or not vx.any():
+                continue
+            iyv, ixv = iy[vy], ix[vx]
+            g = dy[:, :, vy][:, :, :, vx]
+            if is_max:
+                xs = x[:, :, iyv][:, :, :, ixv]
+                ys = y[:, :, vy][:, :, :, vx]
+                g = g * (xs == ys).to(g.dtype)
+            else:
+                g = g / (k * k)
+            dx[:, :, iyv[:, None], ixv[None, :]] += g
+    return dx
+
+
+# ------------------------------------------------------------------------------------------- LRN
+def _chwindow_sum(t, lsize):
+    half = lsize // 2
+    c = t.shape[1]
+    tp = F.pad(t, (0, 0, 0, 0, half, half))
+    out = torch.zeros_like(t)
+    for d in range(lsize):
+        out = out + tp[:, d:d + c]
+    return out
+
+
+def lrn_fwd(x, lsize, alpha, beta, knorm):
+    norm = knorm + (alpha / lsize) * _chwindow_sum(x * x, lsize)
+    return x * norm.pow(-beta), norm
+
+
+def lrn_bwd(x, norm, dy, lsize, alpha, beta):
+    t = dy * x * norm.pow(-beta - 1.0)
+    return dy * norm.pow(-beta) - (2.0 * beta * alpha / lsize) * x * _chwindow_sum(t, lsize)
+
+
+# ------------------------------------------------------------------------------------------- conv / inner product
+def conv_fwd(x, weight, bias, k, s, pad):
+    """weight {F, C*k*k} with column (c*k + ky)*k + kx  (SURVEY A.1)."""
+    f = weight.shape[0]
+    c = x.shape[1]
+    y = F.conv2d(x, weight.view(f, c, k, k), bias, stride=s, padding=pad)
+    return y
+
+
+def conv_bwd(x, weight, dy, k, s, pad, need_dx=True):
+    f = weight.shape[0]
+    c = x.shape[1]
+    w4 = weight.view(f, c, k, k)
+    db = dy.sum(dim=(0, 2, 3))
+    dw = torch.nn.grad.conv2d_weight(x, w4.shape, dy, stride=s, padding=pad).reshape(f, -1)
+    dx = torch.nn.grad.conv2d_input(x.shape, w4, dy, stride=s, padding=pad) if need_dx else None
+    return dx, dw, db
+
+
+def ip_fwd(x2d, weight, bias):
+    """weight {vdim, hdim}: y = x W + b  (src/worker/layer.cc:186-196)."""
+    y = x2d @ weight
+    return y + bias if bias is not None else y
+
+
+def ip_bwd(x2d, weight, dy, need_dx=True):
+    db = dy.sum(dim=0)
+    dw = x2d.t() @ dy
+    dx = dy @ weight.t() if need_dx else None
+    return dx, dw, db
+
+
+# ------------------------------------------------------------------------------------------- softmax loss
+def softmax_loss(logits, labels, topk=1, scale=1.0):
+    """returns (metric[2], grad): metric = scale*[mean NLL, top-k accuracy], grad=(p-onehot)*scale/N."""
+    n, dim = logits.shape
+    p = torch.softmax(logits.float(), dim=1)
+    lab = labels.long().clamp(0, dim - 1)
+    pl = p.gather(1, lab[:, None]).squeeze(1)
+    loss = -torch.log(torch.clamp_min(pl, FLT_MIN)).mean()
+    xl = logits.float().gather(1, lab[:, None])
+    rank = (logits.float() > xl).sum(dim=1)
+    acc = (rank < topk).float().mean()
+    grad = p.clone()
+    grad[torch.arange(n, device=logits.device), lab] -= 1.0
+    grad = grad * (scale / n)
+    return torch.stack([loss * scale, acc * scale]), grad
+
+
+# ------------------------------------------------------------------------------------------- LR schedules / updaters
+def learning_rate(up, step: int) -> float:
+    """UpdaterProto -> LR(step)  (src/utils/updater.cc:11-51)."""
+    from ..proto import schema as S
+    base = up.base_learning_rate
+    m = up.learning_rate_change_method
+    name = S.enum_name("UpdaterProto.ChangeProto", m)
+    freq = up.learning_rate_change_frequency
+    if name == "kFixed":
+        return base
+    if name == "kLinear":
+        r = step * 1.0 / freq
+        return (1.0 - r) * base + r * up.final_learning_rate
+    if name == "kExponential":
+        return base / math.pow(2, step * 1.0 / freq)
+    if name == "kInverse_t":
+        return base / (1.0 + step * 1.0 / up.final_learning_rate)
+    if name == "kInverse":
+        return base * math.pow(1.0 + up.gamma * step, -up.pow)
+    if name == "kStep":
+        return base * math.pow(up.gamma, step // freq)
+    raise ValueError(f"unknown learning-rate change method {m}")
+
+
+def update_ref(kind: str, w, g, h, u, *, lr, momentum=0.0, wd=0.0, delta=1e-7, rho=0.9, grad_scale=1.0):
+    """In-place update of fp32 tensors; same math as csrc/updaters.cu::update_one."""
+    sg = g * grad_scale
+    if kind == "kSGD":
+        gg = sg + wd * w if wd > 0 else sg
+        if momentum > 0:
+            h.mul_(momentum).add_(gg, alpha=lr)
+            w.sub_(h)
+        else:
+            w.sub_(gg, alpha=lr)
+    elif kind == "kNesterov":
+        gg = sg + wd * w if wd > 0 else sg
+        hold = h.clone()
+        h.mul_(momentum).add_(gg, alpha=lr)
+        w.sub_(h * (1 + momentum) - hold * momentum)
+    elif kind == "kAdaGrad":
+        h.add_(sg * sg)
+        gg = sg + wd * w if wd > 0 else sg
+        w.sub_(lr * gg / torch.sqrt(h + delta))
+    elif kind == "kRMSProp":
+        h.mul_(rho).add_(sg * sg, alpha=1 - rho)
+        gg = sg + wd * w if wd > 0 else sg
+        w.sub_(lr * gg / torch.sqrt(h + delta))
+    elif kind == "kAdaDelta":
+        gg = sg + wd * w if wd > 0 else sg
+        h.mul_(rho).add_(gg * gg, alpha=1 - rho)
+        t = gg * torch.sqrt(u + delta) / torch.sqrt(h + delta)
+        u.mul_(rho).add_(t * t, alpha=1 - rho)
+        w.sub_(t)
+    else:
+        raise ValueError(kind)
+
+
+# ------------------------------------------------------------------------------------------- sync rules
+def easgd_ref(w, s, alpha):
+    """d = (w - s) alpha; s += d; w -= d  (src/utils/param.cc:244-284)."""
+    d = (w - s) * alpha
+    s.add_(d)
+    w.sub_(d)
+
+
+def randomsync_ref(w, snap, s, ratio, seed):
+    """Shared-seed subset exchange (src/utils/param.cc:130-228) on {i: philox(seed,i) < ratio}."""
+    n = w.numel()
+    sel = torch.ones(n, dtype=torch.bool, device=w.device) if ratio >= 1 else \
+        (philox_uniform(seed, n, w.device) < ratio)
+    wf, sf, snf = w.view(-1), s.view(-1), snap.view(-1)
+    delta = wf[sel] - snf[sel]
+    old = sf[sel].clone()
+    sf[sel] += delta
+    wf[sel] += old - snf[sel]
+    snf[sel] = wf[sel]
+    return int(sel.sum())

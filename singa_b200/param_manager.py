@@ -1,0 +1,148 @@
+"""ParamManager: the worker-side owner of the parameters — arena creation, initialisation, the updater, and
+the exchange with the parameter servers.
+
+Reference: include/utils/param_manager.h:38-127, src/utils/param_manager.cc:9-235 (Stack A), whose call
+points are kept: ``update_param`` right after a layer's backward, ``wait_update`` right before a layer's next
+forward (the layer-granular overlap hooks of src/worker/worker.cc:249-253,290-292).
+
+Exchange backends:
+  * ``local``  — no servers: the fused arena updater runs once per step.
+  * ``zmq``    — Stack A over the ZeroMQ Router (kPut / kGet / kSync / kStop): Elastic or RandomSync every
+                 ``sync_frequency`` steps; CPU plumbing config and cross-host control.
+  * ``nccl``   — synchronous data parallel with NCCL reduce-scatter -> shard update -> all-gather
+                 (the library baseline).
+  * ``fused``  — the B200 product path: reduce-scatter + updater + broadcast in ONE kernel over NVSwitch peer
+                 memory with device-side version counters (singa_b200/parallel/fused_ps.py).
+"""
+from __future__ import annotations
+
+import time
+from typing import Dict, List, Optional
+
+import torch
+
+from .arena import ParamArena
+from .cluster import Cluster
+from .device import ctx, set_step_state, step_state
+from .param import Param, kGet, kPut, kStop, kSync
+from .updater import create_updater
+
+
+class ParamManager:
+    def __init__(self, net, updater_proto, cluster: Optional[Cluster] = None, backend: Optional[str] = None,
+                 seed: int = 0):
+        self.net = net
+        self.cluster = cluster
+        self.updater_proto = updater_proto
+        self.updater = create_updater(updater_proto)
+        self.seed = seed
+        ngroups = cluster.ngroups if cluster else 1
+        nservers = cluster.nservers if cluster else 0
+        self.moving_rate = updater_proto.moving_rate / max(ngroups, 1)
+        self.sync_frequency = max(1, updater_proto.sync_frequency)
+        self.warmup_steps = updater_proto.warmup_steps
+        self.nservers = nservers
+        self.sample_ratio = 1.0
+        self.param_type = updater_proto.param_type
+        self.hogwild = (cluster.nthreads_per_procs == 1 if cluster else True) or updater_proto.hogwild
+        owners = [p for p in net.params if p.is_owner]
+        self.arena = ParamArena(owners, with_update=self.updater.needs_update,
+                                with_snapshot=(self.param_type == "RandomSync" and nservers > 0))
+        self.paramid2version: Dict[int, int] = {p.id: 0 for p in net.params}
+        self.layer_ranges = {}
+        for layer in net.layers:
+            ps = layer.get_params()
+            if ps:
+                self.layer_ranges[layer.name] = self.arena.chunk_range(ps)
+        self._param_layers = [l for l in net.layers if l.get_params()]
+        self._first_param_layer = self._param_layers[0] if self._param_layers else None
+        if backend is None:
+            backend = "local" if nservers == 0 else "zmq"
+        self.backend_name = backend
+        self.backend = None
+        if backend == "zmq":
+            from .parallel.zmq_ps import ZmqExchange
+            self.backend = ZmqExchange(self)
+        elif backend == "nccl":
+            from .parallel.nccl_ps import NcclExchange
+            self.backend = NcclExchange(self)
+        elif backend == "fused":
+            from .parallel.fused_ps import FusedExchange
+            self.backend = FusedExchange(self)
+        elif backend != "local":
+            raise ValueError(f"unknown exchange backend {backend!r}")
+        self.use_device_lr = ctx().is_native
+
+    # -- reference API -----------------------------------------------------------------------------
+    def init_params(self) -> None:
+        for p in self.arena.params:
+            p.init(self.seed)
+        self.arena.sync_mirror()
+
+    def sync_config(self, compute_time: float) -> None:
+        """RandomSync sizing: ratio = bandwidth * nservers / (modelMB * nworkers / compute_time), <= 1
+        (src/utils/param_manager.cc:88-96)."""
+        if self.cluster is None or self.nservers == 0:
+            return
+        model_mb = self.arena.nbytes / (1024.0 * 1024.0)
+        nworkers = max(1, self.cluster.nworkers)
+        throughput = model_mb * nworkers / max(compute_time, 1e-9)
+        self.sample_ratio = min(1.0, self.cluster.bandwidth * self.nservers / max(throughput, 1e-9))
+
+    def sync_now(self, step: int) -> bool:
+        return self.nservers > 0 and (step + 1) % self.sync_frequency == 0 and step > self.warmup_steps
+
+    def send_params_to_servers(self) -> None:
+        if self.backend is not None:
+            self.backend.put_all()
+
+    def get_params_from_servers(self) -> None:
+        if self.backend is not None:
+            self.backend.get_all()
+
+    def begin_step(self, step: int) -> None:
+        """Publish LR(step) / step to device memory (keeps a captured graph valid across steps)."""
+        self.lr = self.updater.learning_rate(step)
+        if self.use_device_lr:
+            set_step_state(step, self.lr)
+
+    def update_param(self, layer, step: int) -> None:
+        """Called right after ``layer``'s backward."""
+        if self.backend is not None and self.backend.handles_update:
+            self.backend.update_layer(layer, step)
+            return
+        # local update: one fused launch over the whole arena once the last gradient (the first layer in
+        # forward order) is ready
+        if layer is self._first_param_layer:
+            self._update_range(0, self.arena.nchunks, step)
+            for p in self.net.params:
+                self.paramid2version[p.id] = step + 1
+            if self.backend is not None and self.sync_now(step):
+                self.backend.sync_all(step)
+
+    def _update_range(self, first_chunk: int, nchunks: int, step: int, grad_scale: float = 1.0) -> None:
+        if self.arena.use16:
+            from .ops import kernels as K
+            from .updater import _KIND_ID
+            u = self.updater
+            K.update_arena(self.arena.data, self.arena.grad, self.arena.history, self.arena.update,
+                           self.arena.data16, self.arena.chunk_param, self.arena.lr_mult, self.arena.wd_mult,
+                           first_chunk, nchunks, kind=_KIND_ID[u.kind], lr=getattr(self, "lr", 0.0),
+                           momentum=u.momentum, weight_decay=u.weight_decay, delta=u.delta, rho=u.rho,
+                           grad_scale=grad_scale, lr_dev=step_state()["lr"] if self.use_device_lr else None)
+            lo, hi = first_chunk * 1024, (first_chunk + nchunks) * 1024
+            for p in self.arena.params:
+                if p.pack16 is not None and lo <= self.arena.offsets[id(p)] < hi:
+                    p.pack16()
+        else:
+            self.updater.update_arena(step, self.arena, first_chunk, nchunks, grad_scale)
+
+    def wait_update(self, layer, step: int) -> None:
+        """Called right before ``layer``'s forward: block until its parameters are fresh enough."""
+        if self.backend is not None:
+            self.backend.wait_layer(layer, step)
+
+    def finish(self) -> None:
+        if self.backend is not None:
+            self.backend.close()
+            self.backend = None

@@ -1,0 +1,400 @@
+"""Worker / Executor / Performance — the training runtime.
+
+Reference: include/worker/worker.h:37-213, src/worker/worker.cc:14-388.  The step structure is the
+reference's (optional validation/test -> TrainOneBatch -> metrics -> display), with the per-layer
+``wait_update`` / ``update_param`` hooks around forward / backward.  B200 specifics:
+
+* data is staged from pinned host memory by the parser layers while the previous step computes;
+* forward + backward + the fused arena update of one step are captured ONCE in a CUDA graph and replayed
+  (the MNIST-scale models are launch-latency bound); LR and step live in device memory so the graph follows
+  the schedule;
+* phase timers use CUDA events on the compute stream, metrics stay on the device until a display step.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import threading
+import time
+from typing import List, Optional
+
+import torch
+
+from .cluster import Cluster
+from .device import ctx
+from .neuralnet import NeuralNet, registry_param
+from .param import Param
+from .param_manager import ParamManager
+from .proto import schema as S
+
+log = logging.getLogger("singa")
+
+
+def _sync():
+    if ctx().device.type == "cuda":
+        torch.cuda.synchronize()
+
+
+class Performance:
+    """Averages every loss layer's metric blob over the display window and prints
+    ``Output from <layer> layer 0 : <loss>\\t1 : <precision>`` (src/worker/worker.cc:350-386).  The sums are
+    accumulated on the device by the loss kernel itself; the host reads them only in ``to_string``."""
+
+    def __init__(self, net: NeuralNet):
+        self.net = net
+        self.names = [l.name for l in net.losslayers]
+        self.counter = 0
+        self.reset()
+
+    def update(self) -> None:
+        self.counter += 1
+
+    def reset(self) -> None:
+        for l in self.net.losslayers:
+            l.metric.zero_()
+        self.counter = 0
+
+    def values(self) -> List[List[float]]:
+        c = max(self.counter, 1)
+        return [[float(v) / c for v in l.metric.detach().cpu().tolist()] for l in self.net.losslayers]
+
+    def to_string(self) -> str:
+        out = ""
+        for name, m in zip(self.names, self.values()):
+            out += f"Output from {name} layer " + "".join(f"{j} : {v:.6f}\t" for j, v in enumerate(m)) + "\n"
+        return out
+
+
+class Executor:
+    def __init__(self, local_threadid: int, model, cluster: Optional[Cluster], pm: ParamManager,
+                 train_net: NeuralNet, test_net: Optional[NeuralNet] = None,
+                 validation_net: Optional[NeuralNet] = None, use_graph: Optional[bool] = None):
+        self.local_threadid = local_threadid
+        self.model = model
+        self.cluster = cluster
+        self.pm = pm
+        self.train_net, self.test_net, self.validation_net = train_net, test_net, validation_net
+        self.step = 0
+        self.ticks = 0
+        self.t_forward = self.t_backward = self.t_sync_data = self.t_sync_param = 0.0
+        self._events: List[tuple] = []
+        self._prefetch_thread: Optional[threading.Thread] = None
+        self._copy_stream = torch.cuda.Stream() if ctx().device.type == "cuda" else None
+        env = os.environ.get("SINGA_B200_CUDA_GRAPH")
+        if use_graph is None:
+            use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local",)
+        self.use_graph = use_graph
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_warmup = 3
+        self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
+        from .parallel.bridge import BridgeTransport
+        self.bridge = BridgeTransport(cluster, local_threadid) if self._has_bridges else None
+
+    # -- locality ------------------------------------------------------------------------------------
+    def _is_local(self, layer) -> bool:
+        if self.cluster is None or not self._has_bridges:
+            return True
+        return self.bridge.is_local(layer)
+
+    # -- schedule predicates (include/worker/worker.h:118-158) -----------------------------------------
+    def _every(self, step, freq, after) -> bool:
+        return freq > 0 and step >= after and (step - after) % freq == 0
+
+    def display_now(self, step) -> bool:
+        return self._every(step, self.model.display_frequency, self.model.display_after_steps)
+
+    def display_debug_info(self, step) -> bool:
+        return self.display_now(step) and self.model.debug and self._group0()
+
+    def stop_now(self, step) -> bool:
+        return step >= self.model.train_steps
+
+    def _group0(self) -> bool:
+        return self.cluster is None or self.cluster.groupid == 0
+
+    def test_now(self, step) -> bool:
+        return self._group0() and self.test_net is not None and \
+            self._every(step, self.model.test_frequency, self.model.test_after_steps)
+
+    def validate_now(self, step) -> bool:
+        return self._group0() and self.validation_net is not None and \
+            self._every(step, self.model.validation_frequency, self.model.validation_after_steps)
+
+    def checkpoint_now(self, step) -> bool:
+        return self._group0() and step > 0 and \
+            self._every(step, self.model.checkpoint_frequency, self.model.checkpoint_after_steps)
+
+    # -- data --------------------------------------------------------------------------------------------
+    def setup(self) -> None:
+        """Stage the first batch (and start prefetching) — Executor::Setup, src/worker/worker.cc:123-156."""
+        self._prefetch(self.train_net, True)
+
+    def _prefetch(self, net: NeuralNet, training: bool) -> None:
+        for d in net.datalayers:
+            if self._is_local(d):
+                d.prefetching(training)
+        for p in net.parserlayers:
+            if self._is_local(p):
+                p.prefetching(training, self._copy_stream)
+
+    def _start_prefetch(self, net, training) -> None:
+        if not self.model.prefetch:
+            return
+        t = threading.Thread(target=self._prefetch, args=(net, training), daemon=True)
+        t.start()
+        self._prefetch_thread = t
+
+    def _join_prefetch(self) -> None:
+        if self._prefetch_thread is not None:
+            self._prefetch_thread.join()
+            self._prefetch_thread = None
+
+    def _feed(self, net: NeuralNet, training: bool) -> None:
+        """Make the staged batch current (parse kernels), then start staging the next one."""
+        self._join_prefetch()
+        if not self.model.prefetch:
+            for d in net.datalayers:
+                if self._is_local(d):
+                    d.compute_feature(training)
+        for p in net.parserlayers:
+            if self._is_local(p):
+                p.compute_feature(training)
+        self._start_prefetch(net, training)
+
+    # -- forward / backward (src/worker/worker.cc:240-302) ---------------------------------------------
+    def forward(self, net: NeuralNet, step: int, training: bool, skip_inputs: bool = False) -> None:
+        for layer in net.layers:
+            if not self._is_local(layer):
+                continue
+            if layer.is_datalayer or layer.is_parserlayer:
+                if not skip_inputs and layer.is_parserlayer:
+                    layer.compute_feature(training)
+                continue
+            if layer.is_bridgedstlayer:
+                self.bridge.recv_data(layer)
+            if training:
+                for _p in layer.get_params():
+                    self.pm.wait_update(layer, step)
+                    break
+            layer.compute_feature(training)
+            if layer.is_bridgesrclayer:
+                self.bridge.send_data(layer)
+        if training and self.display_debug_info(step):
+            log.error("\n" + net.debug_info())
+
+    def backward(self, net: NeuralNet, step: int) -> None:
+        for layer in reversed(net.layers):
+            if not self._is_local(layer) or layer.is_datalayer or layer.is_parserlayer:
+                continue
+            if layer.is_bridgesrclayer:
+                self.bridge.recv_grad(layer)
+            layer.compute_gradient()
+            if layer.get_params():
+                self.pm.update_param(layer, step)
+            if layer.is_bridgedstlayer:
+                self.bridge.send_grad(layer)
+
+    # -- one training step --------------------------------------------------------------------------------
+    def train_one_batch(self, step: int) -> None:
+        self.pm.begin_step(step)
+        self._feed(self.train_net, True)
+        cuda = ctx().device.type == "cuda"
+        if self.use_graph and not self._has_bridges:
+            if self._graph is None and self.ticks > self._graph_warmup:
+                self._capture(step)
+            if self._graph is not None:
+                self._graph.replay()
+                return
+        if cuda:
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record()
+        t0 = time.monotonic()
+        self.forward(self.train_net, step, True, skip_inputs=True)
+        if cuda:
+            e1.record()
+        t1 = time.monotonic()
+        self.backward(self.train_net, step)
+        if cuda:
+            e2.record()
+            self._events.append((e0, e1, e2))
+        else:
+            self.t_forward += (t1 - t0) * 1e3
+            self.t_backward += (time.monotonic() - t1) * 1e3
+
+    def _capture(self, step: int) -> None:
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.forward(self.train_net, step, True, skip_inputs=True)
+            self.backward(self.train_net, step)
+        self._graph = g
+        # capture does not execute: the replay in train_one_batch performs this step's work
+
+    def timer_info(self) -> str:
+        """``Total / forward / backward`` milliseconds per iteration (include/worker/worker.h:91-114)."""
+        if self._events:
+            _sync()
+            for e0, e1, e2 in self._events:
+                self.t_forward += e0.elapsed_time(e1)
+                self.t_backward += e1.elapsed_time(e2)
+            self._events.clear()
+        ticks = max(self.ticks, 1)
+        tf, tb = self.t_forward / ticks, self.t_backward / ticks
+        s = "Total\t%6.2f\tforward\t%6.2f\tbackward\t%6.2f\t" % (tf + tb, tf, tb)
+        s += "worker_gen_sync\t%6.2f\tworker_handle_sync\t%6.2f\n" % (Param.worker_gen_sync / ticks,
+                                                                      Param.worker_handle_sync / ticks)
+        Param.worker_gen_sync = Param.worker_handle_sync = 0.0
+        self.t_forward = self.t_backward = self.t_sync_data = self.t_sync_param = 0.0
+        self.ticks = 0
+        return s
+
+    def run_one_batch(self, step: int, perf: Optional[Performance] = None) -> None:
+        self.ticks += 1
+        if self.validate_now(step):
+            log.error("Validation at step %d", step)
+            self.test(self.validation_net, self.model.validation_steps, perf is not None)
+        if self.test_now(step):
+            log.error("Test at step %d", step)
+            self.test(self.test_net, self.model.test_steps, perf is not None)
+        self.train_one_batch(step)
+        if perf is not None:
+            perf.update()
+            if self.display_now(step):
+                log.error("Training at step %d", step)
+                log.error("\t%s", perf.to_string())
+                perf.reset()
+                log.error("\t%s", self.timer_info())
+
+    def test(self, net: NeuralNet, nsteps: int, disperf: bool = True) -> Optional[List[List[float]]]:
+        """Forward-only passes over ``nsteps`` batches with their own staging (worker.cc:318-348)."""
+        if net is None or nsteps <= 0:
+            return None
+        self._join_prefetch()
+        perf = Performance(net)
+        for b in range(nsteps):
+            for d in net.datalayers:
+                d.compute_feature(False)
+            self.forward(net, b, False)
+            perf.update()
+        vals = perf.values()
+        if disperf:
+            log.error("\t%s", perf.to_string())
+        # training prefetch may have been consumed by nothing: restage for the train net
+        return vals
+
+    def run(self, perf: Optional[Performance], start_step: int = 0, on_step=None) -> int:
+        step = start_step
+        while not self.stop_now(step):
+            self.run_one_batch(step, perf)
+            if on_step is not None:
+                on_step(step)
+            step += 1
+        self.step = step
+        self._join_prefetch()
+        return step
+
+
+class Worker:
+    """``Worker(cluster).start(model)`` — build the phase nets, parameters and executors, warm up, exchange
+    the initial parameters with the servers and train (src/worker/worker.cc:14-106)."""
+
+    def __init__(self, cluster: Optional[Cluster] = None, backend: Optional[str] = None, seed: int = 0,
+                 use_graph: Optional[bool] = None):
+        self.cluster = cluster
+        self.backend = backend
+        self.seed = seed
+        self.use_graph = use_graph
+        self.train_net = self.test_net = self.validation_net = None
+        self.pm: Optional[ParamManager] = None
+        self.executor: Optional[Executor] = None
+        self.perf: Optional[Performance] = None
+        self.model = None
+        self.start_step = 0
+
+    # phase filtering by LayerProto.exclude (worker.cc:69-95)
+    def setup_neuralnet(self, model, phase: int) -> Optional[NeuralNet]:
+        proto = S.NetProto()
+        proto.partition_type = model.neuralnet.partition_type
+        for lp in model.neuralnet.layer:
+            if phase in list(lp.exclude):
+                continue
+            proto.layer.add().CopyFrom(lp)
+        if not any(l.type in ("kShardData", "kLMDBData") for l in proto.layer):
+            return None
+        gsize = self.cluster.nthreads_per_group if self.cluster is not None else 1
+        partitioned = proto.partition_type != S.kNone or any(
+            l.HasField("partition_type") and l.partition_type != S.kNone for l in proto.layer) or \
+            any(l.locationid != 0 for l in proto.layer)
+        return NeuralNet(proto, gsize if partitioned else 1)
+
+    def build(self, model) -> None:
+        self.model = model
+        registry_param(model.updater.param_type)
+        self.train_net = self.setup_neuralnet(model, S.kTrain)
+        assert self.train_net is not None, "the model has no training data layer"
+        has_test = model.test_steps > 0 and model.test_frequency > 0
+        has_val = model.validation_steps > 0 and model.validation_frequency > 0
+        if has_test:
+            self.test_net = self.setup_neuralnet(model, S.kTest)
+            if self.test_net is not None:
+                self.test_net.share_weights(self.train_net)
+        if has_val:
+            self.validation_net = self.setup_neuralnet(model, S.kValidation)
+            if self.validation_net is not None:
+                self.validation_net.share_weights(self.train_net)
+        self.pm = ParamManager(self.train_net, model.updater, self.cluster, self.backend, self.seed)
+        for net in (self.test_net, self.validation_net):
+            if net is not None:
+                net.share_weights(self.train_net)   # re-alias after the arena re-pointed the blobs
+        self.pm.init_params()
+        self.executor = Executor(0, model, self.cluster, self.pm, self.train_net, self.test_net,
+                                 self.validation_net, self.use_graph)
+        self.perf = Performance(self.train_net)
+
+    def resume(self) -> int:
+        """Load the latest Param-proto checkpoint (if the model names one or the workspace holds one) and
+        return the step to continue from — ``Worker::Resume`` is an empty TODO in the reference
+        (src/worker/worker.cc:65-67)."""
+        from . import checkpoint
+        path = self.model.checkpoint if self.model.HasField("checkpoint") else None
+        if path is None and self.cluster is not None:
+            path = checkpoint.latest(self.cluster.checkpoint_folder)
+        if path and os.path.exists(path):
+            step = checkpoint.load(path, self.train_net, self.pm)
+            log.error("Resumed from %s at step %d", path, step)
+            return step
+        return int(self.model.step)
+
+    def start(self, model) -> int:
+        log.error("Worker on %s is starting...", self.cluster.hostname if self.cluster else "localhost")
+        self.build(model)
+        ex, pm = self.executor, self.pm
+        self.start_step = self.resume()
+        ex.setup()
+        # warm-up: time the compute to size RandomSync messages (worker.cc:41-48)
+        warm = 0
+        if pm.nservers > 0 and self.start_step == 0:
+            warm = min(model.updater.warmup_steps, model.train_steps)
+            _sync()
+            t0 = time.monotonic()
+            for step in range(warm):
+                ex.run_one_batch(step, self.perf)
+            _sync()
+            if warm:
+                pm.sync_config((time.monotonic() - t0) / warm)
+            if self.cluster.groupid == 0:
+                pm.send_params_to_servers()
+            else:
+                pm.get_params_from_servers()
+        start = max(self.start_step, warm)
+        step = ex.run(self.perf, start, on_step=self._maybe_checkpoint)
+        _sync()
+        pm.finish()
+        return step
+
+    def _maybe_checkpoint(self, step: int) -> None:
+        if self.executor.checkpoint_now(step + 1) and self.cluster is not None:
+            from . import checkpoint
+            path = checkpoint.save(self.cluster.checkpoint_folder, self.train_net, self.pm, step + 1,
+                                   self.model.name)
+            log.error("Checkpoint written to %s", path)

@@ -1,0 +1,93 @@
+"""Whole-net checks on the GPU: the native sm_100a path against the plain-PyTorch fp32 path of the same net,
+same parameters, same synthetic batch."""
+import pytest
+import torch
+
+from singa_b200 import device
+from singa_b200.models import configs
+from singa_b200.worker import Worker
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(model, backend, dev):
+    device.set_context(dev, backend)
+    w = Worker(use_graph=False)
+    w.build(model)
+    return w
+
+
+def _one_step(w, update=False):
+    ex = w.executor
+    w.pm.begin_step(0)
+    ex._feed(w.train_net, True)
+    ex.forward(w.train_net, 0, True, skip_inputs=True)
+    if update:
+        ex.backward(w.train_net, 0)
+    else:
+        for layer in reversed(w.train_net.layers):
+            if not (layer.is_datalayer or layer.is_parserlayer):
+                layer.compute_gradient()
+    torch.cuda.synchronize()
+
+
+def _compare(model, rtol_loss=2e-2, grad_cos=0.98):
+    ref = _build(model, "torch", "cuda")
+    nat = _build(model, "native", "cuda")
+    for a, b in zip(nat.train_net.params, ref.train_net.params):
+        a.data.copy_(b.data)
+    nat.pm.arena.sync_mirror()
+    ref.executor.model.prefetch = False
+    nat.executor.model.prefetch = False
+    _one_step(ref)
+    _one_step(nat)
+    lr_, ln_ = ref.train_net.losslayers[0].metric.cpu(), nat.train_net.losslayers[0].metric.cpu()
+    assert abs(float(lr_[0]) - float(ln_[0])) <= rtol_loss * max(1.0, abs(float(lr_[0]))), (lr_, ln_)
+    for a, b in zip(nat.train_net.params, ref.train_net.params):
+        ga, gb = a.grad.float().flatten(), b.grad.float().flatten()
+        cos = torch.nn.functional.cosine_similarity(ga, gb, dim=0)
+        assert float(cos) > grad_cos, f"param {a.id} {a.name} {a.shape}: cosine {float(cos)}"
+        rel = float((ga - gb).norm() / (gb.norm() + 1e-12))
+        assert rel < 0.15, f"param {a.id} {a.name}: relative grad error {rel}"
+    device.reset_context()
+
+
+def test_mnist_mlp_native_vs_torch():
+    _compare(configs.mnist_mlp(batch=256, hidden=(512, 256, 128)))
+
+
+def test_lenet_native_vs_torch():
+    _compare(configs.lenet(batch=32))
+
+
+def test_cifar_convnet_native_vs_torch():
+    m = configs.cifar10_convnet(batch=16)
+    for l in m.neuralnet.layer:       # larger init so gradients are not all ~0 in bf16
+        for p in l.param:
+            if p.name == "weight":
+                p.std = 0.05
+    _compare(m, grad_cos=0.95)
+
+
+def test_training_reduces_loss_native_graph():
+    """A few hundred captured-graph steps on the synthetic MNIST-shaped data must reduce the loss."""
+    device.set_context("cuda", "native")
+    m = configs.mnist_mlp(batch=500, train_steps=150, hidden=(512, 256))
+    m.display_frequency = 0
+    m.updater.base_learning_rate = 0.05
+    w = Worker(use_graph=True)
+    w.build(m)
+    ex = w.executor
+    ex.setup()
+    losses = []
+    for step in range(150):
+        ex.ticks += 1
+        ex.train_one_batch(step)
+        if step % 50 == 49 or step == 0:
+            torch.cuda.synchronize()
+            mt = w.train_net.losslayers[0].metric
+            losses.append(float(mt[0].item()) / (1 if step == 0 else 49 if len(losses) == 1 else 50))
+            mt.zero_()
+    assert ex._graph is not None, "the step was not captured in a CUDA graph"
+    assert losses[-1] < losses[0] * 0.7, losses
+    device.reset_context()
