@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""Headline benchmark: training throughput (images/sec) of the reference's flagship job — the examples/mnist
+MLP (784-2500-2000-1500-1000-500-10, tanh, batch 1000 per worker group, SGD) — on N B200 GPUs of one node,
+one worker group (= one process) per GPU, synchronous push/pull through the sharded parameter server.
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 200 --warmup 20
+    python bench.py --impl reference ...     # the unmodified reference (unavailable offline: see DESIGN.md)
+
+Prints ONE JSON line on rank 0 (contract in the task statement).  Two measurements:
+  * ``value``      device-timed (CUDA events, max over ranks): K steps of parse + forward + backward + fused
+                   update (+ push/pull for N > 1) with the uint8 batches already staged on the device;
+  * ``e2e.value``  the same K steps through the public API (Executor.train_one_batch) with, EVERY step, the
+                   batch assembled in pinned host memory, copied host->device, and the loss read back.
+Other configs of BASELINE.json: ``--config {mnist_mlp,lenet,cifar10,alexnet,wide_mlp}``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--config", default="mnist_mlp")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the config's own)")
+    ap.add_argument("--push-pull", default=os.environ.get("SINGA_B200_PUSH_PULL", "fused"),
+                    choices=["fused", "nccl"])
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons during the timed region (profiling recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001 - nvidia-smi missing: report empty clocks
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args):
+    """The reference cannot be installed or built here: it has no setup.py/pyproject.toml (pip: "Neither
+    'setup.py' nor 'pyproject.toml' found") and `make singa` needs protoc, glog, gflags, czmq, lmdb, OpenCV,
+    cblas, none of which exist on the box (no network).  Recorded in DESIGN.md."""
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    why = "reference is a C++/Makefile project (no setup.py/pyproject.toml; make needs protoc, glog, gflags, " \
+          "czmq, lmdb, OpenCV, cblas - absent offline); baseline/_ref is empty"
+    if os.path.isdir(ref) and os.listdir(ref):
+        why = "baseline/_ref exists but holds no runnable reference entry point"
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} needs WORLD_SIZE={args.gpus} (launch with torch.distributed.run); "
+                         f"got WORLD_SIZE={world}")
+    assert torch.cuda.is_available(), "bench.py needs a GPU"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from singa_b200 import device
+    from singa_b200.cluster import Cluster
+    from singa_b200.models import configs
+    from singa_b200.ops import native
+    from singa_b200.proto import schema as S
+    from singa_b200.worker import Worker
+
+    backend_kind = "torch" if args.impl == "torch" else "native"
+    device.set_context(f"cuda:{local_rank}", backend_kind)
+
+    kw = {}
+    if args.batch:
+        kw["batch"] = args.batch
+    model = configs.CONFIGS[args.config](**kw)
+    model.display_frequency = 0
+    model.test_frequency = 0
+    model.train_steps = 1 << 30
+    model.prefetch = False          # bench drives the staging explicitly (see the two timed regions)
+
+    cluster = None
+    exchange = None
+    if world > 1:
+        cp = S.ClusterProto()
+        cp.nworkers, cp.nservers = world, world        # one server shard co-located with every worker group
+        cp.workspace = os.environ.get("SINGA_B200_WORKSPACE", "/tmp/singa_b200_bench")
+        cp.synchronous = True
+        cp.push_pull = args.push_pull
+        Cluster.reset()
+        cluster = Cluster.get(cp, "", rank)
+        exchange = args.push_pull
+    w = Worker(cluster, backend=exchange, use_graph=not args.no_graph)
+    w.build(model)
+    ex, net = w.executor, w.train_net
+    data_layer = net.datalayers[0]
+    per_gpu_batch = data_layer.batchsize
+    loss_layer = net.losslayers[0]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------------------------------------------------------- device-timed region
+    # batches staged on the device up front; each step: parse kernels + fwd + bwd + update (+ push/pull)
+    def stage_all():
+        data_layer.compute_feature(True)
+        for p in net.parserlayers:
+            p.prefetching(True)
+            p.compute_feature(True)
+
+    def step_device(step):
+        ex.ticks += 1
+        w.pm.begin_step(step)
+        for p in net.parserlayers:      # re-parse the device-resident staged batch (no host traffic)
+            p.reparse(True)
+        ex._run_compute(step)
+
+    stage_all()
+    step = 0
+    for _ in range(max(args.warmup, 3)):
+        step_device(step); step += 1
+    barrier()
+    ws_bytes = w.pm.arena.total * (4 + 4 + 2) + sum(
+        l.data.numel() * l.data.element_size() for l in net.layers if l.data is not None and l.data.is_cuda)
+    flush = None
+    if ws_bytes < L2_BYTES:
+        flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device="cuda")
+    sampler = ClockSampler(local_rank)
+    launches0 = native.launch_count
+    if rank == 0:
+        sampler.start()
+    barrier()
+    if flush is None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            step_device(step); step += 1
+        e1.record()
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+    else:
+        evs = []
+        for _ in range(args.steps):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); step_device(step); step += 1; b.record()
+            evs.append((a, b))
+        barrier()
+        ms_total = sum(a.elapsed_time(b) for a, b in evs)
+    clocks = sampler.stop() if rank == 0 else None
+    eager_launches = native.launch_count - launches0
+    graph_launches = ex.graph_kernel_count * args.steps if ex._graph is not None else 0
+    gpu_launches = eager_launches + graph_launches
+
+    # ---------------------------------------------------------------- end-to-end region (public API)
+    h2d = sum(p.h2d_bytes for p in net.parserlayers)
+    d2h = loss_layer.metric.numel() * loss_layer.metric.element_size()
+    model.prefetch = True
+    ex.setup()                         # stage batch 0, start the prefetch thread
+    for _ in range(3):
+        ex.ticks += 1
+        ex.train_one_batch(step); step += 1
+        loss_layer.metric.cpu()
+    barrier()
+    t0 = time.perf_counter()
+    last = None
+    for _ in range(args.steps):
+        ex.ticks += 1
+        ex.train_one_batch(step); step += 1      # pinned host batch -> H2D -> parse -> fwd/bwd/update
+        last = loss_layer.metric.cpu()           # D2H read of the step's result (forces completion)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    ex._join_prefetch()
+
+    # ---------------------------------------------------------------- reduce over ranks, report
+    t = torch.tensor([ms_total, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    global_batch = per_gpu_batch * world
+    value = global_batch * args.steps / (ms_total / 1e3)
+    e2e_value = global_batch * args.steps / (e2e_ms / 1e3)
+    if rank == 0:
+        out = {
+            "metric": "images/sec (device-timed, max over ranks)",
+            "value": round(value, 1),
+            "unit": "images/s",
+            "n_gpus": world,
+            "steps": args.steps,
+            "warmup": max(args.warmup, 3),
+            "ms_per_step": round(ms_total / args.steps, 4),
+            "higher_is_better": True,
+            "scaling": "weak",
+            "vs_baseline": None,
+            "dtype": "bf16" if backend_kind == "native" else "fp32",
+            "data": "synthetic",
+            "impl": args.impl,
+            "config": {
+                "model": {"mnist_mlp": "examples/mnist MLP 784-2500-2000-1500-1000-500-10 tanh"}.get(
+                    args.config, args.config),
+                "global_batch": global_batch,
+                "per_gpu_batch": per_gpu_batch,
+                "seq_len": None,
+                "parallelism": f"dp{world} (1 worker group + 1 server shard per GPU, sync push/pull: "
+                               f"{exchange or 'local'})",
+                "precision": "bf16 operands, fp32 accumulate, fp32 master weights + optimizer state",
+                "cuda_graph": ex._graph is not None,
+                "l2": ("per-step working set %.0f MB > 126 MB L2 (no flush needed)" % (ws_bytes / 2**20))
+                      if flush is None else "L2 flushed (252 MB write) between timed steps, per-step events",
+            },
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "final_loss_sum_window": [round(float(x), 4) for x in last.tolist()] if last is not None else None},
+            "gpu_launches": gpu_launches,
+        }
+        print(json.dumps(out))
+    w.pm.finish()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -77,6 +77,8 @@ class ParamArena:
                 p.update = view(self.update, p.update)
             if self.snapshot is not None:
                 p.snapshot = view(self.snapshot, p.snapshot)
+            if self.data16 is not None and p.pack16 is None:
+                p.data16 = self.data16[o:o + n].view(p.shape)   # GEMM operand = the arena's bf16 mirror
         self.sync_mirror()
 
     def view16(self, p: Param) -> torch.Tensor:

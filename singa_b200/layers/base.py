@@ -46,6 +46,7 @@ class Layer:
         self.shape_: List[int] = []
         self.forced_shape: Optional[List[int]] = None   # set when instantiated as one partition of a layer
         self.net = None                                  # back-pointer set by NeuralNet
+        self.native = ctx().is_native                    # backend is fixed when the layer is created
 
     # -- construction ----------------------------------------------------------------------------
     def init(self, proto) -> None:

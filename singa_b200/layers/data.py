@@ -242,10 +242,15 @@ class ParserLayer(Layer):
             else:
                 slot = self.stage_ready
             self.stage_ready = -1
+        self.last_slot = slot
         ev = self.stage_events[slot]
         if ev is not None and ctx().device.type == "cuda":
             torch.cuda.current_stream().wait_event(ev)
         self.parse(self.staging[slot], training)
+
+    def reparse(self, training: bool) -> None:
+        """Parse the most recently consumed staged batch again (device-resident input, no host traffic)."""
+        self.parse(self.staging[self.last_slot], training)
 
     @property
     def h2d_bytes(self) -> int:
@@ -272,7 +277,7 @@ class MnistImageLayer(ParserLayer):
         return self._data_layer().pixels
 
     def parse(self, staged, training):
-        if ctx().is_native:
+        if self.native:
             from ..ops import kernels as K
             K.mnist_parse(staged, self.data, self.norm_a, self.norm_b)
         else:
@@ -321,7 +326,7 @@ class RGBImageLayer(ParserLayer):
                                          dtype=torch.int32))
         else:
             self.mir.zero_()
-        if ctx().is_native:
+        if self.native:
             from ..ops import kernels as K
             K.rgb_parse(staged, None, self.data, n, self.C, self.H, self.W, crop, self.off_h, self.off_w,
                         self.mir, self.scale)

@@ -102,7 +102,7 @@ class InnerProductLayer(NeuronLayer):
         self.bias_term = self.proto.inner_product_param.bias_term
         self.feeds_loss = any(d.is_losslayer for d in self.dstlayers)
         self.shape_ = [self.batchsize, self.hdim]
-        native = ctx().is_native
+        native = self.native
         self.data = alloc_act(self.shape_, torch.float32 if (self.feeds_loss and native) else None)
         self.grad = alloc_act(self.shape_)
         if not hasattr(self, "weight"):
@@ -153,7 +153,7 @@ class InnerProductLayer(NeuronLayer):
 
     def _x2d(self):
         src = self.srclayers[0].data_for(self)
-        if not ctx().is_native:
+        if not self.native:
             return src.reshape(self.batchsize, self.vdim).float()
         K = _K()
         if self.src4d:
@@ -175,7 +175,7 @@ class InnerProductLayer(NeuronLayer):
 
     def compute_feature(self, training):
         x = self._x2d()
-        if ctx().is_native:
+        if self.native:
             K = _K()
             w16 = self._w16()
             out32 = self.data if self.data.dtype == torch.float32 else None
@@ -196,7 +196,7 @@ class InnerProductLayer(NeuronLayer):
         dy = self.grad
         x = self._x_saved
         need_dx = self._need_src_grad()
-        if ctx().is_native:
+        if self.native:
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
             if self.bias_term:
@@ -279,7 +279,7 @@ class ConvolutionLayer(NeuronLayer):
             self.bias = param_factory.create("Param")
             self.weight.setup(protos[0], [self.num_filters, self.col_height], self.col_height)
             self.bias.setup(protos[1], [self.num_filters], 0)
-        if ctx().is_native:
+        if self.native:
             self._setup_native()
 
     def _setup_native(self):
@@ -318,7 +318,7 @@ class ConvolutionLayer(NeuronLayer):
 
     def compute_feature(self, training):
         src = self._src_nhwc()
-        if ctx().is_native:
+        if self.native:
             K = _K()
             N, H, W, C = self.batchsize, self.height, self.width, self.channels
             if self.pointwise:
@@ -347,7 +347,7 @@ class ConvolutionLayer(NeuronLayer):
 
     def compute_gradient(self):
         need_dx = self._need_src_grad()
-        if ctx().is_native:
+        if self.native:
             K = _K()
             F_, K_, P = self.num_filters, self.col_height, self.P
             dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
@@ -425,7 +425,7 @@ class ActivationLayer(NeuronLayer):
         if self.fwd_fused:
             return
         x = self.srclayers[0].data_for(self)
-        if ctx().is_native:
+        if self.native:
             _K().act_fwd(x, self.data, self.act)
         else:
             self.data.copy_(R.relu_fwd(x) if self.act == ACT_RELU else R.stanh_fwd(x))
@@ -436,7 +436,7 @@ class ActivationLayer(NeuronLayer):
         dst = self.srclayers[0].grad_for(self)
         if dst is None:
             return
-        if ctx().is_native:
+        if self.native:
             _K().act_bwd(self.grad, self.data, dst, self.act)   # in place when grad aliases dst
         else:
             g, y = self.grad.float(), self.data.float()
@@ -477,7 +477,7 @@ class DropoutLayer(NeuronLayer):
         if not training:
             self.data.copy_(x)
             return
-        if ctx().is_native:
+        if self.native:
             _K().dropout(x, self.data, self.pkeep, self.seed_base, step_state()["step"])
         else:
             m = R.dropout_mask(self.seed_base + int(step_state()['host_step'][0]), x.numel(), self.pkeep, x.device).view(x.shape)
@@ -490,7 +490,7 @@ class DropoutLayer(NeuronLayer):
             return
         if not self._training:
             dst.copy_(self.grad)
-        elif ctx().is_native:
+        elif self.native:
             _K().dropout(self.grad, dst, self.pkeep, self.seed_base, step_state()["step"])
         else:
             dst.copy_(self.grad.float() * self._mask)
@@ -521,7 +521,7 @@ class PoolingLayer(NeuronLayer):
 
     def compute_feature(self, training):
         x = self.srclayers[0].data_for(self)
-        if ctx().is_native:
+        if self.native:
             _K().pool_fwd(x, self.data, self.batchsize, self.height, self.width, self.channels,
                           self.pooled_height, self.pooled_width, self.kernel, self.stride, self.pad, self.is_max)
         else:
@@ -534,7 +534,7 @@ class PoolingLayer(NeuronLayer):
         if dst is None:
             return
         x = src.data_for(self)
-        if ctx().is_native:
+        if self.native:
             _K().pool_bwd(x, self.data, self.grad, dst, self.batchsize, self.height, self.width, self.channels,
                           self.pooled_height, self.pooled_width, self.kernel, self.stride, self.pad, self.is_max)
         else:
@@ -564,7 +564,7 @@ class LRNLayer(NeuronLayer):
 
     def compute_feature(self, training):
         x = self.srclayers[0].data_for(self)
-        if ctx().is_native:
+        if self.native:
             _K().lrn_fwd(x, self.data, self.norm, self.batchsize * self.height * self.width, self.channels,
                          self.lsize, self.alpha, self.beta, self.knorm)
         else:
@@ -578,7 +578,7 @@ class LRNLayer(NeuronLayer):
         if dst is None:
             return
         x = src.data_for(self)
-        if ctx().is_native:
+        if self.native:
             _K().lrn_bwd(x, self.norm, self.grad, dst, self.batchsize * self.height * self.width,
                          self.channels, self.lsize, self.alpha, self.beta)
         else:
@@ -629,7 +629,7 @@ class SoftmaxLossLayer(LossLayer):
         labels = self.srclayers[1].data_for(self)
         # ``metric`` ACCUMULATES over steps on the device (Performance divides by its step counter and zeroes
         # it at the end of a display window), so no host round trip or memset sits in the step.
-        if ctx().is_native:
+        if self.native:
             g = self.srclayers[0].grad_for(self) if training else None
             l2 = logits if logits.dim() == 2 else logits.view(self.batchsize, self.dim)
             _K().softmax_loss(l2, l2.stride(0), labels, self.batchsize, self.dim, self.topk, self.scale,
@@ -640,7 +640,7 @@ class SoftmaxLossLayer(LossLayer):
             self._g = g
 
     def compute_gradient(self):
-        if ctx().is_native:
+        if self.native:
             return   # gradient already written by the fused forward kernel
         dst = self.srclayers[0].grad_for(self)
         if dst is not None:

@@ -86,6 +86,7 @@ class Executor:
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
+        self.graph_kernel_count = 0
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
         from .parallel.bridge import BridgeTransport
         self.bridge = BridgeTransport(cluster, local_threadid) if self._has_bridges else None
@@ -198,6 +199,11 @@ class Executor:
     def train_one_batch(self, step: int) -> None:
         self.pm.begin_step(step)
         self._feed(self.train_net, True)
+        self._run_compute(step)
+
+    def _run_compute(self, step: int) -> None:
+        """forward + backward (+ per-layer parameter update / push) of one step on the already-parsed batch;
+        replayed from a CUDA graph once captured."""
         cuda = ctx().device.type == "cuda"
         if self.use_graph and not self._has_bridges:
             if self._graph is None and self.ticks > self._graph_warmup:
@@ -217,18 +223,24 @@ class Executor:
         if cuda:
             e2.record()
             self._events.append((e0, e1, e2))
+            if len(self._events) > 4096:
+                self._events = self._events[-1024:]
         else:
             self.t_forward += (t1 - t0) * 1e3
             self.t_backward += (time.monotonic() - t1) * 1e3
 
     def _capture(self, step: int) -> None:
+        from .ops import native
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
+        n0 = native.launch_count
         with torch.cuda.graph(g):
             self.forward(self.train_net, step, True, skip_inputs=True)
             self.backward(self.train_net, step)
+        self.graph_kernel_count = native.launch_count - n0
+        native.launch_count = n0          # capture records launches, it does not execute them
         self._graph = g
-        # capture does not execute: the replay in train_one_batch performs this step's work
+        # the replay in _run_compute performs this step's work
 
     def timer_info(self) -> str:
         """``Total / forward / backward`` milliseconds per iteration (include/worker/worker.h:91-114)."""

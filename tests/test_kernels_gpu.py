@@ -112,7 +112,7 @@ def test_parsers():
     px = torch.randint(0, 256, (n, 784), device=DEV, dtype=torch.uint8)
     out = torch.empty(n, 28, 28, device=DEV, dtype=torch.bfloat16)
     K().mnist_parse(px, out, 127.5, 1.0)
-    torch.testing.assert_close(out.float().view(n, -1), (px.float() / 127.5 - 1.0).to(torch.bfloat16).float())
+    torch.testing.assert_close(out.float().view(n, -1), px.float() / 127.5 - 1.0, rtol=1e-2, atol=1e-2)
     C, H, W, crop = 3, 32, 32, 24
     img = torch.randint(0, 256, (n, C, H, W), device=DEV, dtype=torch.uint8)
     oh = torch.randint(0, H - crop + 1, (n,), device=DEV, dtype=torch.int32)
@@ -130,7 +130,7 @@ def test_parsers():
 @pytest.mark.parametrize("rows,dim,topk", [(1000, 10, 1), (256, 1000, 5), (33, 7, 2)])
 def test_softmax_loss(rows, dim, topk):
     ld = (dim + 3) // 4 * 4
-    logits = torch.randn(rows, ld, device=DEV)[:, :dim] * 3
+    logits = (torch.randn(rows, ld, device=DEV) * 3)[:, :dim]
     labels = torch.randint(0, dim, (rows,), device=DEV, dtype=torch.int32)
     ldg = (dim + 7) // 8 * 8
     grad = torch.zeros(rows, ldg, device=DEV, dtype=torch.bfloat16)[:, :dim]
