@@ -403,19 +403,34 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
   return launch_gemm<BN, true, true>(ta, tb, p, s);
 }
 
-// Tile-width heuristic: widest N tile that still gives every SM at least one tile; the small MNIST-MLP
-// layers are occupancy bound, the 4096/16384-wide layers want the 128x256 tile.
-static int pick_bn(int M, int N) {
+// Tile-width choice from a small cost model (cycles).  Measured on B200: this kernel is bound by the
+// L2 -> shared-memory path (about 6300 B/cycle for the whole chip, i.e. ~42 B/cycle/SM with every SM pulling),
+// not by the tensor pipe, so wide tiles (fewer bytes per flop) win even when they leave SMs idle:
+//   per k-block:  mma = max(2*BN, 128 + BN) cycles   (tensor pipe vs. smem operand reads at 128 B/cycle)
+//                 l2  = (16 KB + BN*128 B) / min(64, 6300 / active CTAs)
+//   total = waves * (num_kb * max(mma, l2) + fixed per-tile overhead)
+static int pick_bn(int M, int N, int K) {
   const int sms = num_sms();
   const long long m_tiles = (M + BM - 1) / BM;
+  const long long num_kb = (K + BK - 1) / BK;
   const int cands[3] = {256, 128, 64};
+  double best = 1e30;
+  int best_bn = 64;
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
-    if (N < bn && i < 2) continue;
+    if (bn > 64 && N <= bn / 2) continue;   // more than half of the tile would be padding
     const long long tiles = m_tiles * ((N + bn - 1) / bn);
-    if (tiles >= sms || i == 2) return bn;
+    const long long active = tiles < sms ? tiles : sms;
+    const long long waves = (tiles + sms - 1) / sms;
+    const double mma = (2.0 * bn > 128.0 + bn) ? 2.0 * bn : 128.0 + bn;
+    double bw = 6300.0 / static_cast<double>(active);
+    if (bw > 64.0) bw = 64.0;
+    const double l2 = (16384.0 + bn * 128.0) / bw;
+    const double per_tile = num_kb * (mma > l2 ? mma : l2) + 2500.0 + 6.0 * bn;
+    const double total = waves * per_tile;
+    if (total < best) { best = total; best_bn = bn; }
   }
-  return 64;
+  return best_bn;
 }
 
 int g_force_bn = 0;  // test hook (sg_gemm_set_tile)
@@ -439,7 +454,7 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   SG_REQUIRE(ep != nullptr && (ep->d32 != nullptr || ep->d16 != nullptr),
              "sg_gemm_bf16: epilogue needs an output");
   SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm_bf16: grad_act needs aux");
-  const int bn = g_force_bn ? g_force_bn : pick_bn(M, N);
+  const int bn = g_force_bn ? g_force_bn : pick_bn(M, N, K);
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn_major) rc = make_tmap_bf16(&ta, A, K, M, lda, BK, BM);

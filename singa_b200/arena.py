@@ -30,10 +30,20 @@ class ParamArena:
         self.device = device or ctx().device
         self.params: List[Param] = [p for p in params if p.is_owner]
         self.offsets: Dict[int, int] = {}
+        self.slot: Dict[int, int] = {}      # elements occupied in the arena (>= p.size when rows are padded)
+        self.use16 = self.device.type == "cuda" and ctx().is_native
         off = 0
         for p in self.params:
             self.offsets[id(p)] = off
-            off += _round_up(p.size, CHUNK)
+            # a 2-D GEMM weight whose row length is not a multiple of 8 is stored with a padded row stride so
+            # that the bf16 mirror is directly TMA-legal (padding stays zero: its gradient is never written)
+            p.ld = p.shape[-1] if p.shape else 1
+            if self.use16 and getattr(p, "want_padded_ld", False) and len(p.shape) == 2 and p.shape[1] % 8:
+                p.ld = (p.shape[1] + 7) // 8 * 8
+                self.slot[id(p)] = p.shape[0] * p.ld
+            else:
+                self.slot[id(p)] = p.size
+            off += _round_up(self.slot[id(p)], CHUNK)
         self.total = max(off, CHUNK)
         self.nchunks = self.total // CHUNK
         alloc = allocator or (lambda n, dt: torch.zeros(n, dtype=dt, device=self.device))
@@ -42,14 +52,13 @@ class ParamArena:
         self.history = alloc(self.total, torch.float32) if with_history else None
         self.update = alloc(self.total, torch.float32) if with_update else None
         self.snapshot = alloc(self.total, torch.float32) if with_snapshot else None
-        self.use16 = self.device.type == "cuda" and ctx().is_native
         self.data16 = alloc(self.total, torch.bfloat16) if self.use16 else None
         chunk_param = torch.full((self.nchunks,), -1, dtype=torch.int32)
         lr_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
         wd_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
         for i, p in enumerate(self.params):
             o = self.offsets[id(p)]
-            chunk_param[o // CHUNK:(o + _round_up(p.size, CHUNK)) // CHUNK] = i
+            chunk_param[o // CHUNK:(o + _round_up(self.slot[id(p)], CHUNK)) // CHUNK] = i
             lr_mult[i] = p.learning_rate_multiplier
             wd_mult[i] = p.weight_decay_multiplier
         self.chunk_param = chunk_param.to(self.device)
@@ -60,11 +69,17 @@ class ParamArena:
     def adopt(self) -> None:
         """Re-point every owner parameter's blobs into the arena (existing values are preserved)."""
         for p in self.params:
-            o, n = self.offsets[id(p)], p.size
+            o, n = self.offsets[id(p)], self.slot[id(p)]
             p.arena_offset = o
+            padded = n != p.size
+
+            def shaped(buf):
+                if padded:
+                    return buf[o:o + n].view(p.shape[0], p.ld)[:, :p.shape[1]]
+                return buf[o:o + n].view(p.shape)
 
             def view(buf, old):
-                v = buf[o:o + n].view(p.shape)
+                v = shaped(buf)
                 if old is not None and old.data_ptr() != v.data_ptr():
                     v.copy_(old.to(v.device))
                 return v
@@ -78,12 +93,11 @@ class ParamArena:
             if self.snapshot is not None:
                 p.snapshot = view(self.snapshot, p.snapshot)
             if self.data16 is not None and p.pack16 is None:
-                p.data16 = self.data16[o:o + n].view(p.shape)   # GEMM operand = the arena's bf16 mirror
+                p.data16 = shaped(self.data16)   # GEMM operand = the arena's bf16 mirror
         self.sync_mirror()
 
     def view16(self, p: Param) -> torch.Tensor:
-        o = self.offsets[id(p if p.is_owner else p.owner)]
-        return self.data16[o:o + p.size].view(p.shape)
+        return (p if p.is_owner else p.owner).data16
 
     def sync_mirror(self) -> None:
         """data16 <- data for the whole arena, then refresh every packed operand."""
@@ -101,7 +115,7 @@ class ParamArena:
         if not owners:
             return 0, 0
         lo = min(self.offsets[id(p)] for p in owners)
-        hi = max(self.offsets[id(p)] + _round_up(p.size, CHUNK) for p in owners)
+        hi = max(self.offsets[id(p)] + _round_up(self.slot[id(p)], CHUNK) for p in owners)
         return lo // CHUNK, (hi - lo) // CHUNK
 
     def param_index(self, p: Param) -> int:

@@ -131,14 +131,9 @@ class InnerProductLayer(NeuronLayer):
         if self.src4d or self.vdim % 8 != 0:
             self.x_flat = alloc_act([self.batchsize, self.vdim])
             self.dx_flat = alloc_act([self.batchsize, self.vdim])
-        # weight operand: the arena's bf16 mirror when hdim is a multiple of 8, else a padded packed copy
-        if self.hdim % 8 != 0:
-            packed = torch.zeros(self.vdim, pad8(self.hdim), dtype=torch.bfloat16, device=dev)
-            self.weight.data16 = packed[:, :self.hdim]
-
-            def pack(w=self.weight, dst=packed):
-                _K().cast_pack(w.data, self.hdim, dst, dst.stride(0), self.vdim, self.hdim)
-            self.weight.pack16 = pack
+        # weight operand = the arena's bf16 mirror; when hdim is not a multiple of 8 the arena stores the rows
+        # with a padded stride (ParamArena honours want_padded_ld) so the mirror is TMA-legal as is
+        self.weight.want_padded_ld = True
 
     def get_params(self):
         return [self.weight, self.bias] if self.bias_term else [self.weight]
@@ -192,10 +187,15 @@ class InnerProductLayer(NeuronLayer):
             self.data.copy_(y)
             self._x_saved = x
 
+    split_backward = True
+
     def compute_gradient(self):
-        dy = self.grad
-        x = self._x_saved
-        need_dx = self._need_src_grad()
+        self.compute_param_gradient()
+        self.compute_data_gradient()
+
+    def compute_param_gradient(self):
+        """db = sum_rows(dY), dW = X^T dY (independent of the data gradient: may run on a side stream)."""
+        dy, x = self.grad, self._x_saved
         if self.native:
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
@@ -204,34 +204,41 @@ class InnerProductLayer(NeuronLayer):
             # dW[vdim][hdim] = X^T dY : A = X stored [K=batch][M=vdim], B = dY stored [K=batch][N=hdim]
             K.gemm(x, dy, self.vdim, self.hdim, self.batchsize, a_mn=True, b_mn=True,
                    out32=self.weight.grad, accumulate=accumulate)
-            if need_dx:
-                dst, aux = self._src_grad()
-                w16 = self._w16()
-                if self.src4d:
-                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=self.dx_flat)
-                    n, c, h, w = self.srclayers[0].shape(self)
-                    if self.vdim % 8 == 0:
-                        K.transpose_planes(self.dx_flat, dst, n, c, h * w)   # (c,h,w) -> NHWC
-                    else:
-                        dst.copy_(self.dx_flat.reshape(dst.shape))
-                    if aux is not None:
-                        K.act_bwd(dst, aux, dst, self.src_grad_act)
-                else:
-                    d2 = self._flat2d(dst)
-                    a2 = self._flat2d(aux) if aux is not None else None
-                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=d2,
-                           grad_act=self.src_grad_act, aux=a2)
         else:
-            dx, dw, db = R.ip_bwd(x, self.weight.data, dy.float(), need_dx)
+            _, dw, db = R.ip_bwd(x, self.weight.data, dy.float(), False)
             self.weight.grad.copy_(dw)
             if self.bias_term:
                 self.bias.grad.copy_(db)
-            if need_dx:
-                dst, aux = self._src_grad()
+
+    def compute_data_gradient(self):
+        """dX = dY W^T (times act'(x) when the source activation's backward is fused here)."""
+        if not self._need_src_grad():
+            return
+        dy = self.grad
+        dst, aux = self._src_grad()
+        if self.native:
+            K = _K()
+            w16 = self._w16()
+            if self.src4d:
+                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=self.dx_flat)
+                n, c, h, w = self.srclayers[0].shape(self)
+                if self.vdim % 8 == 0:
+                    K.transpose_planes(self.dx_flat, dst, n, c, h * w)   # (c,h,w) -> NHWC
+                else:
+                    dst.copy_(self.dx_flat.reshape(dst.shape))
                 if aux is not None:
-                    a = aux.reshape(self.batchsize, self.vdim).float()
-                    dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
-                dst.copy_(dx.view(dst.shape))
+                    K.act_bwd(dst, aux, dst, self.src_grad_act)
+            else:
+                d2 = self._flat2d(dst)
+                a2 = self._flat2d(aux) if aux is not None else None
+                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=d2,
+                       grad_act=self.src_grad_act, aux=a2)
+        else:
+            dx = dy.float() @ self.weight.data.t()
+            if aux is not None:
+                a = aux.reshape(self.batchsize, self.vdim).float()
+                dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
+            dst.copy_(dx.view(dst.shape))
 
 
 # ================================================================================================
@@ -299,9 +306,12 @@ class ConvolutionLayer(NeuronLayer):
         def pack(w=self.weight, dst=self.w16_packed):
             _K().cast_pack(w.data, K_, dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
         self.weight.pack16 = pack
-        # scratch shared across layers: dcol [P][Kpad] and (if F % 8 != 0) a padded copy of dy [P][Fpad]
-        self.ws_bytes = self.P * self.Kpad * 2 + (self.P * self.Fpad * 2 if F_ % 8 else 0)
+        # scratch: dcol [P][Kpad] in the workspace shared by all conv layers (used and consumed within one
+        # data-gradient step); a padded copy of dy [P][Fpad] per layer when F % 8 != 0 (read by both gradient GEMMs)
+        self.ws_bytes = self.P * self.Kpad * 2
         workspace.reserve(self.ws_bytes)
+        self.dy_pad = torch.zeros(self.P, self.Fpad, dtype=torch.bfloat16, device=dev) if F_ % 8 else None
+        self._dy_op = None
 
     def get_params(self):
         return [self.weight, self.bias] if self.bias_term else [self.weight]
@@ -345,54 +355,69 @@ class ConvolutionLayer(NeuronLayer):
             self.data.copy_(y)
             self._x_saved = x
 
+    split_backward = True
+
     def compute_gradient(self):
-        need_dx = self._need_src_grad()
+        self.compute_param_gradient()
+        self.compute_data_gradient()
+
+    def _dy_operand(self):
+        """dY as a [P][F] bf16 matrix with a TMA-legal row stride (padded copy in the workspace if F % 8)."""
+        K = _K()
+        F_, P = self.num_filters, self.P
+        dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
+        if F_ % 8:
+            dyp = self.dy_pad
+            K.copy2d_bf16(dy2d, F_, dyp, self.Fpad, P, F_)
+            return dy2d, dyp[:, :F_]
+        return dy2d, dy2d
+
+    def compute_param_gradient(self):
         if self.native:
             K = _K()
             F_, K_, P = self.num_filters, self.col_height, self.P
-            dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
             accumulate = getattr(self, "_accumulate_wgrad", False)
+            dy2d, dy_op = self._dy_operand()
+            self._dy_op = dy_op
             if self.bias_term:
                 K.colsum(dy2d, P, F_, F_, self.bias.grad, accumulate=accumulate)
-            if F_ % 8:
-                dyp = workspace.view((P, self.Fpad), torch.bfloat16)
-                K.copy2d_bf16(dy2d, F_, dyp, self.Fpad, P, F_)
-                dy_op = dyp[:, :F_]
-                ws_off = P * self.Fpad * 2
-            else:
-                dy_op, ws_off = dy2d, 0
-            col = self._col_saved
             kk = self.kernel * self.kernel
             # dW[F][K] = dY^T col : A = dY stored [K=P][M=F], B = col stored [K=P][N=K_]; columns come out in
             # (ky,kx,c) order and are stored in the reference's (c,ky,kx) order by the epilogue permutation
-            K.gemm(dy_op, col, F_, K_, P, a_mn=True, b_mn=True, out32=self.weight.grad, accumulate=accumulate,
-                   perm=(self.channels, kk) if kk > 1 and self.channels > 1 else None)
-            if need_dx:
-                dst, aux = self._src_grad()
-                N, H, W, C = self.batchsize, self.height, self.width, self.channels
-                if self.pointwise:
-                    d2 = dst.permute(0, 2, 3, 1).reshape(P, C)
-                    a2 = aux.permute(0, 2, 3, 1).reshape(P, C) if aux is not None else None
-                    K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=d2,
-                           grad_act=self.src_grad_act, aux=a2)
-                else:
-                    dcol = workspace.buf[ws_off:ws_off + P * self.Kpad * 2].view(torch.bfloat16).view(P, self.Kpad)
-                    # dcol[P][K] = dY[P][F] . W16[F][K] : B(n=K idx, k=F idx) stored [K=F][N=K_]
-                    K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=dcol[:, :K_])
-                    K.col2im_nhwc(dcol, self.Kpad, dst, N, H, W, C, self.conv_height, self.conv_width,
-                                  self.kernel, self.stride, self.pad, self.src_grad_act, aux)
+            K.gemm(dy_op, self._col_saved, F_, K_, P, a_mn=True, b_mn=True, out32=self.weight.grad,
+                   accumulate=accumulate, perm=(self.channels, kk) if kk > 1 and self.channels > 1 else None)
         else:
-            dx, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
-                                    self.stride, self.pad, need_dx)
+            self._dx_ref, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
+                                              self.stride, self.pad, self._need_src_grad())
             self.weight.grad.copy_(dw)
             if self.bias_term:
                 self.bias.grad.copy_(db)
-            if need_dx:
-                dst, aux = self._src_grad()
-                if aux is not None:
-                    a = aux.float().view(dx.shape)
-                    dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
-                dst.copy_(dx.view(dst.shape))
+
+    def compute_data_gradient(self):
+        if not self._need_src_grad():
+            return
+        dst, aux = self._src_grad()
+        if self.native:
+            K = _K()
+            F_, K_, P = self.num_filters, self.col_height, self.P
+            N, H, W, C = self.batchsize, self.height, self.width, self.channels
+            dy_op = self._dy_operand()[1] if not hasattr(self, "_dy_op") or self._dy_op is None else self._dy_op
+            if self.pointwise:
+                d2 = dst.permute(0, 2, 3, 1).reshape(P, C)
+                a2 = aux.permute(0, 2, 3, 1).reshape(P, C) if aux is not None else None
+                K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=d2, grad_act=self.src_grad_act, aux=a2)
+            else:
+                dcol = workspace.view((P, self.Kpad), torch.bfloat16)
+                # dcol[P][K] = dY[P][F] . W16[F][K] : B(n=K idx, k=F idx) stored [K=F][N=K_]
+                K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=dcol[:, :K_])
+                K.col2im_nhwc(dcol, self.Kpad, dst, N, H, W, C, self.conv_height, self.conv_width,
+                              self.kernel, self.stride, self.pad, self.src_grad_act, aux)
+        else:
+            dx = self._dx_ref
+            if aux is not None:
+                a = aux.float().view(dx.shape)
+                dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
+            dst.copy_(dx.view(dst.shape))
 
 
 # ================================================================================================

@@ -117,8 +117,13 @@ class Param:
             raise ValueError(f"unknown init method {p.init_method}")
         if self.data.is_cuda and ctx().is_native:
             from .ops import kernels as K
-            flat = self.data.view(-1)
-            K.fill_random(flat, kind, a, b, scale, seed * 1000003 + (self.id if self.id >= 0 else 0) + 12345)
+            sd = seed * 1000003 + (self.id if self.id >= 0 else 0) + 12345
+            if self.data.is_contiguous():
+                K.fill_random(self.data.view(-1), kind, a, b, scale, sd)
+            else:   # padded row stride in the arena: fill a dense temporary, copy the logical part
+                tmp = torch.empty(self.shape, dtype=torch.float32, device=self.data.device)
+                K.fill_random(tmp.view(-1), kind, a, b, scale, sd)
+                self.data.copy_(tmp)
         else:
             g = torch.Generator(device="cpu")
             g.manual_seed(seed * 1000003 + (self.id if self.id >= 0 else 0) + 12345)

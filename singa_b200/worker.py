@@ -86,6 +86,9 @@ class Executor:
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
+        nside = int(os.environ.get("SINGA_B200_SIDE_STREAMS", "2"))
+        self._side_streams = [torch.cuda.Stream() for _ in range(nside)] \
+            if (ctx().is_native and nside > 0) else None
         self.graph_kernel_count = 0
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
         from .parallel.bridge import BridgeTransport
@@ -184,13 +187,32 @@ class Executor:
             log.error("\n" + net.debug_info())
 
     def backward(self, net: NeuralNet, step: int) -> None:
+        """Reverse-topological walk.  On the native path a layer's parameter gradient (wgrad GEMM + bias
+        reduction) is independent of its data gradient, so it is issued on a side stream and the data
+        gradient — the critical path to the layers below — continues on the main stream; the parameter
+        update joins the side streams.  Small GEMMs that cannot fill 148 SMs alone then overlap."""
+        split = self._side_streams is not None and self.pm.backend_name == "local"
+        main = torch.cuda.current_stream() if split else None
+        k = 0
         for layer in reversed(net.layers):
             if not self._is_local(layer) or layer.is_datalayer or layer.is_parserlayer:
                 continue
             if layer.is_bridgesrclayer:
                 self.bridge.recv_grad(layer)
-            layer.compute_gradient()
-            if layer.get_params():
+            has_params = bool(layer.get_params())
+            if split and has_params and getattr(layer, "split_backward", False):
+                side = self._side_streams[k % len(self._side_streams)]
+                k += 1
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    layer.compute_param_gradient()
+                layer.compute_data_gradient()
+                if layer is self.pm._first_param_layer:
+                    for s_ in self._side_streams:
+                        main.wait_stream(s_)
+            else:
+                layer.compute_gradient()
+            if has_params:
                 self.pm.update_param(layer, step)
             if layer.is_bridgedstlayer:
                 self.bridge.send_grad(layer)
