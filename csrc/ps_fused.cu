@@ -1,0 +1,265 @@
+// Parameter-server data plane over NVSwitch peer memory: the gradient push (reduce-scatter into the owner
+// shard + the server Updater + broadcast of the fresh weights) as ONE kernel, plus the device-side flag
+// protocol that replaces the reference's ZeroMQ kSync / WaitUpdate messages
+// (src/utils/param_manager.cc:163-234, src/server/server.cc:18-43, src/server/pm_server.cc:262-294).
+//
+// Layout: every rank holds a full-size gradient arena, bf16 weight mirror and flag block, all allocated with
+// cudaMalloc and exported through CUDA IPC, so a kernel on rank s can ld/st any rank's copy.  The arena is cut
+// into `world` contiguous chunk ranges; rank s is the SERVER for range s (fp32 master weights + optimizer
+// state live only there).
+//
+// One push launch on the owner of chunks [first_chunk, first_chunk + nchunks):
+//   1. acquire-spin until every rank's `ready` flag for this layer reaches the step value (its gradients are
+//      complete and it no longer reads the bf16 weights of this layer),
+//   2. g = (sum over ranks of peer-loaded gradients) * grad_scale        [reduce-scatter, NVLink reads]
+//   3. apply the Updater to the local fp32 master weights / history      [server update, in registers]
+//   4. store the new weights as bf16 into EVERY rank's mirror            [all-gather by broadcast, NVLink writes]
+//   5. the last CTA to finish (global arrival counter = scratch) release-stores the new version into every
+//      rank's `version` flag, which is what the consumer GEMM's producer warp / the wait kernel acquires.
+// Memory ordering: data stores -> __threadfence_system() -> counter; last CTA: fence -> st.release.sys flags.
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "../include/singa_b200.h"
+#include "common.h"
+
+namespace sg {
+
+constexpr int CHUNK = 1024;
+constexpr int MAX_WORLD = SG_PS_MAX_WORLD;
+
+struct PushParams {
+  const float* grad[MAX_WORLD];
+  __nv_bfloat16* w16[MAX_WORLD];
+  const unsigned long long* ready[MAX_WORLD];
+  unsigned long long* version[MAX_WORLD];
+  int world;
+  float* w; float* h; float* u;
+  const int* chunk_param; const float* lr_mult; const float* wd_mult;
+  long long first_chunk, nchunks;
+  int kind; float lr, momentum, wd, delta, rho, grad_scale; const float* lr_dev;
+  const long long* step_dev; long long value_add;   // flag value = *step_dev + value_add (or value_add alone)
+  unsigned int* counter;                             // scratch: CTA arrival counter, zero between launches
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Bounded spin: a peer that never arrives becomes a trap (host-visible error), not a hung GPU.
+__device__ __forceinline__ void wait_flag_ge(const unsigned long long* p, unsigned long long target) {
+  if (ld_acquire_sys(p) >= target) return;
+  const long long t0 = clock64();
+  while (ld_acquire_sys(p) < target) {
+    __nanosleep(200);
+    if (clock64() - t0 > 60000000000LL) __trap();   // ~30 s
+  }
+}
+
+__device__ __forceinline__ void upd(int kind, float lr, float wd, float momentum, float delta, float rho,
+                                    float& w, float g, float& h, float& u) {
+  switch (kind) {
+    case SG_UPD_SGD: {
+      if (wd > 0.f) g += wd * w;
+      if (momentum > 0.f) { h = momentum * h + lr * g; w -= h; } else w -= lr * g;
+      break;
+    }
+    case SG_UPD_NESTEROV: {
+      if (wd > 0.f) g += wd * w;
+      const float hold = h;
+      h = momentum * h + lr * g;
+      w -= h * (1.f + momentum) - hold * momentum;
+      break;
+    }
+    case SG_UPD_ADAGRAD: {
+      h += g * g;
+      if (wd > 0.f) g += wd * w;
+      w -= lr * g * rsqrtf(h + delta);
+      break;
+    }
+    case SG_UPD_RMSPROP: {
+      h = rho * h + (1.f - rho) * g * g;
+      if (wd > 0.f) g += wd * w;
+      w -= lr * g * rsqrtf(h + delta);
+      break;
+    }
+    case SG_UPD_ADADELTA: {
+      if (wd > 0.f) g += wd * w;
+      h = rho * h + (1.f - rho) * g * g;
+      const float t = g * sqrtf(u + delta) * rsqrtf(h + delta);
+      u = rho * u + (1.f - rho) * t * t;
+      w -= t;
+      break;
+    }
+    default: break;
+  }
+}
+
+__global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p) {
+  const unsigned long long target =
+      static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  // 1. wait for every rank's gradients of this layer
+  if (threadIdx.x < p.world && p.ready[threadIdx.x] != nullptr) wait_flag_ge(p.ready[threadIdx.x], target);
+  __syncthreads();
+
+  const float base_lr = p.lr_dev ? __ldg(p.lr_dev) : p.lr;
+  const bool need_h = p.kind != SG_UPD_SGD || p.momentum > 0.f;
+  const bool need_u = p.kind == SG_UPD_ADADELTA;
+  for (long long c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
+    const long long chunk = p.first_chunk + c;
+    const int pid = p.chunk_param[chunk];
+    if (pid < 0) continue;
+    const float lr = base_lr * p.lr_mult[pid];
+    const float wd = p.wd * p.wd_mult[pid];
+    const long long i = chunk * CHUNK + threadIdx.x * 4;
+    // 2. reduce the peers' gradients (128-bit loads; remote ranks go over NVLink)
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < MAX_WORLD; ++r) {
+      if (r < p.world) {
+        const float4 t = *reinterpret_cast<const float4*>(p.grad[r] + i);
+        g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+      }
+    }
+    g.x *= p.grad_scale; g.y *= p.grad_scale; g.z *= p.grad_scale; g.w *= p.grad_scale;
+    // 3. server update on the local master copy
+    float4 wv = *reinterpret_cast<const float4*>(p.w + i);
+    float4 hv = make_float4(0.f, 0.f, 0.f, 0.f), uv = hv;
+    if (need_h) hv = *reinterpret_cast<const float4*>(p.h + i);
+    if (need_u) uv = *reinterpret_cast<const float4*>(p.u + i);
+    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.x, g.x, hv.x, uv.x);
+    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.y, g.y, hv.y, uv.y);
+    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.z, g.z, hv.z, uv.z);
+    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.w, g.w, hv.w, uv.w);
+    *reinterpret_cast<float4*>(p.w + i) = wv;
+    if (need_h) *reinterpret_cast<float4*>(p.h + i) = hv;
+    if (need_u) *reinterpret_cast<float4*>(p.u + i) = uv;
+    // 4. broadcast the fresh bf16 weights into every rank's mirror
+    const __nv_bfloat162 a = __floats2bfloat162_rn(wv.x, wv.y), b = __floats2bfloat162_rn(wv.z, wv.w);
+    uint2 o;
+    o.x = *reinterpret_cast<const uint32_t*>(&a);
+    o.y = *reinterpret_cast<const uint32_t*>(&b);
+#pragma unroll
+    for (int r = 0; r < MAX_WORLD; ++r)
+      if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+  }
+  // 5. publish: last CTA to arrive bumps the version flag on every rank
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int done = atomicAdd(p.counter, 1u) + 1u;
+    if (done == gridDim.x) {
+      *p.counter = 0u;   // scratch must read zero at the next launch
+      __threadfence_system();
+      for (int r = 0; r < p.world; ++r)
+        if (p.version[r] != nullptr) st_release_sys(p.version[r], target);
+    }
+  }
+}
+
+__global__ void ps_flag_set_kernel(unsigned long long* flag, const long long* step_dev, long long value_add) {
+  __threadfence_system();
+  st_release_sys(flag, static_cast<unsigned long long>((step_dev ? *step_dev : 0) + value_add));
+}
+
+struct WaitParams {
+  const unsigned long long* flags[SG_PS_MAX_WAIT];
+  int n;
+  const long long* step_dev;
+  long long value_add;
+};
+__global__ void ps_flag_wait_kernel(const WaitParams p) {
+  const unsigned long long target =
+      static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  if (threadIdx.x < p.n) wait_flag_ge(p.flags[threadIdx.x], target);
+}
+
+}  // namespace sg
+
+using namespace sg;
+
+extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SG_REQUIRE(a != nullptr, "sg_ps_push_update: null args");
+  if (a->nchunks <= 0) return 0;
+  SG_REQUIRE(a->world >= 1 && a->world <= MAX_WORLD, "sg_ps_push_update: world %d out of range [1,%d]", a->world, MAX_WORLD);
+  SG_REQUIRE(a->counter != nullptr, "sg_ps_push_update: needs a zeroed arrival counter (scratch)");
+  SG_REQUIRE(a->up.kind >= SG_UPD_SGD && a->up.kind <= SG_UPD_ADADELTA, "sg_ps_push_update: unknown updater");
+  const bool need_h = a->up.kind != SG_UPD_SGD || a->up.momentum > 0.f;
+  SG_REQUIRE(!need_h || a->h != nullptr, "sg_ps_push_update: updater needs a history buffer");
+  SG_REQUIRE(a->up.kind != SG_UPD_ADADELTA || a->u != nullptr, "sg_ps_push_update: AdaDelta needs an update buffer");
+  PushParams p;
+  for (int r = 0; r < MAX_WORLD; ++r) {
+    p.grad[r] = r < a->world ? a->grad[r] : nullptr;
+    p.w16[r] = r < a->world ? reinterpret_cast<__nv_bfloat16*>(a->w16[r]) : nullptr;
+    p.ready[r] = r < a->world ? a->ready[r] : nullptr;
+    p.version[r] = r < a->world ? a->version[r] : nullptr;
+    SG_REQUIRE(r >= a->world || (p.grad[r] != nullptr && p.w16[r] != nullptr), "sg_ps_push_update: null peer pointer for rank %d", r);
+  }
+  p.world = a->world;
+  p.w = a->w; p.h = a->h; p.u = a->u;
+  p.chunk_param = a->chunk_param; p.lr_mult = a->lr_mult; p.wd_mult = a->wd_mult;
+  p.first_chunk = a->first_chunk; p.nchunks = a->nchunks;
+  p.kind = a->up.kind; p.lr = a->up.lr; p.momentum = a->up.momentum; p.wd = a->up.weight_decay;
+  p.delta = a->up.delta; p.rho = a->up.rho; p.grad_scale = a->up.grad_scale; p.lr_dev = a->up.lr_dev;
+  p.step_dev = a->step_dev; p.value_add = a->value_add;
+  p.counter = a->counter;
+  long long grid = a->nchunks;
+  const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward
+  if (grid > cap) grid = cap;
+  ps_push_update_kernel<<<static_cast<unsigned>(grid), 256, 0, s>>>(p);
+  SG_CHECK_LAUNCH("ps_push_update");
+  return 0;
+}
+
+extern "C" int sg_ps_flag_set(unsigned long long* flag, const long long* step_dev, long long value_add,
+                              void* stream) {
+  ps_flag_set_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flag, step_dev, value_add);
+  SG_CHECK_LAUNCH("ps_flag_set");
+  return 0;
+}
+
+extern "C" int sg_ps_flag_wait(const unsigned long long* const* flags, int n, const long long* step_dev,
+                               long long value_add, void* stream) {
+  SG_REQUIRE(n >= 0 && n <= SG_PS_MAX_WAIT, "sg_ps_flag_wait: at most %d flags per call", SG_PS_MAX_WAIT);
+  if (n == 0) return 0;
+  WaitParams p;
+  for (int i = 0; i < SG_PS_MAX_WAIT; ++i) p.flags[i] = i < n ? flags[i] : nullptr;
+  p.n = n; p.step_dev = step_dev; p.value_add = value_add;
+  ps_flag_wait_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
+  SG_CHECK_LAUNCH("ps_flag_wait");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// CUDA IPC helpers: arenas that peers can map (cudaMalloc + cudaIpc*; 64-byte opaque handles travel over the
+// control plane).
+// ------------------------------------------------------------------------------------------------
+extern "C" int sg_ipc_alloc(long long bytes, void** out) {
+  SG_REQUIRE(bytes > 0 && out != nullptr, "sg_ipc_alloc: bad arguments");
+  if (check_cuda(cudaMalloc(out, static_cast<size_t>(bytes)), "cudaMalloc(ipc arena)")) return 1;
+  if (check_cuda(cudaMemset(*out, 0, static_cast<size_t>(bytes)), "cudaMemset(ipc arena)")) return 1;
+  return 0;
+}
+extern "C" int sg_ipc_free(void* p) {
+  if (p == nullptr) return 0;
+  return check_cuda(cudaFree(p), "cudaFree(ipc arena)");
+}
+extern "C" int sg_ipc_get_handle(void* p, void* handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  return check_cuda(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle64), p), "cudaIpcGetMemHandle");
+}
+extern "C" int sg_ipc_open_handle(const void* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  return check_cuda(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+}
+extern "C" int sg_ipc_close_handle(void* p) {
+  if (p == nullptr) return 0;
+  return check_cuda(cudaIpcCloseMemHandle(p), "cudaIpcCloseMemHandle");
+}

@@ -148,6 +148,41 @@ int sg_easgd_sync(float* w, float* server, long long n, float alpha, void* w16, 
 int sg_randomsync(float* w, float* snap, float* server, long long n, float ratio,
                   unsigned long long seed, void* w16, unsigned long long* nselected, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Parameter-server data plane over NVSwitch peer memory (gradient push = reduce-scatter + server Updater +
+ * weight broadcast in ONE kernel; device-side version flags instead of kSync / WaitUpdate messages:
+ * src/utils/param_manager.cc:163-234, src/server/server.cc:18-43, src/server/pm_server.cc:262-294).
+ * All pointers in the per-rank arrays are device pointers valid on the calling GPU (local or IPC-mapped peer
+ * memory).  Flag value = (*step_dev if given else 0) + value_add.
+ * ---------------------------------------------------------------------------------------------- */
+#define SG_PS_MAX_WORLD 8
+#define SG_PS_MAX_WAIT 32
+typedef struct SgPsPush {
+  int world;
+  const float* grad[SG_PS_MAX_WORLD];               /* every rank's gradient arena base */
+  void* w16[SG_PS_MAX_WORLD];                       /* every rank's bf16 weight mirror base */
+  const unsigned long long* ready[SG_PS_MAX_WORLD]; /* rank r's "gradients of this layer are ready" flag (or NULL) */
+  unsigned long long* version[SG_PS_MAX_WORLD];     /* rank r's version slot for (layer, this owner) (or NULL) */
+  float* w; float* h; float* u;                     /* local fp32 master / history / update arenas */
+  const int* chunk_param; const float* lr_mult; const float* wd_mult;
+  long long first_chunk, nchunks;                   /* chunk range updated by this launch (owned by this rank) */
+  SgUpdater up;
+  const long long* step_dev; long long value_add;
+  unsigned int* counter;                            /* scratch: 4 bytes of device memory, zero between launches */
+  int max_ctas;                                     /* CTA budget (0 = 64) so backward keeps the SMs */
+} SgPsPush;
+int sg_ps_push_update(const SgPsPush* args, void* stream);
+/* release-store / acquire-wait on 64-bit flags in (peer) device memory */
+int sg_ps_flag_set(unsigned long long* flag, const long long* step_dev, long long value_add, void* stream);
+int sg_ps_flag_wait(const unsigned long long* const* flags, int n, const long long* step_dev,
+                    long long value_add, void* stream);
+/* CUDA-IPC arenas: these (and only these) entry points allocate / free device memory. */
+int sg_ipc_alloc(long long bytes, void** out);
+int sg_ipc_free(void* p);
+int sg_ipc_get_handle(void* p, void* handle64);
+int sg_ipc_open_handle(const void* handle64, void** out);
+int sg_ipc_close_handle(void* p);
+
 #ifdef __cplusplus
 }
 #endif

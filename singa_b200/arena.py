@@ -26,7 +26,7 @@ def _round_up(n: int, m: int) -> int:
 
 class ParamArena:
     def __init__(self, params: Sequence[Param], *, with_update: bool = False, with_snapshot: bool = False,
-                 with_history: bool = True, device=None, allocator=None):
+                 with_history: bool = True, device=None, allocator=None, pad_chunks_to: int = 1):
         self.device = device or ctx().device
         self.params: List[Param] = [p for p in params if p.is_owner]
         self.offsets: Dict[int, int] = {}
@@ -44,15 +44,22 @@ class ParamArena:
             else:
                 self.slot[id(p)] = p.size
             off += _round_up(self.slot[id(p)], CHUNK)
-        self.total = max(off, CHUNK)
+        self.total = _round_up(max(off, CHUNK), CHUNK * max(1, pad_chunks_to))
         self.nchunks = self.total // CHUNK
-        alloc = allocator or (lambda n, dt: torch.zeros(n, dtype=dt, device=self.device))
-        self.data = alloc(self.total, torch.float32)
-        self.grad = alloc(self.total, torch.float32)
-        self.history = alloc(self.total, torch.float32) if with_history else None
-        self.update = alloc(self.total, torch.float32) if with_update else None
-        self.snapshot = alloc(self.total, torch.float32) if with_snapshot else None
-        self.data16 = alloc(self.total, torch.bfloat16) if self.use16 else None
+
+        def default_alloc(name, n, dt):
+            return torch.zeros(n, dtype=dt, device=self.device)
+        # allocator(name, nelems, dtype): lets the fused parameter server place `grad` / `data16` in
+        # peer-mapped (CUDA IPC) memory; may return None to fall back to a plain torch allocation
+        def make(name, dt):
+            t = allocator(name, self.total, dt) if allocator is not None else None
+            return t if t is not None else default_alloc(name, self.total, dt)
+        self.data = make("data", torch.float32)
+        self.grad = make("grad", torch.float32)
+        self.history = make("history", torch.float32) if with_history else None
+        self.update = make("update", torch.float32) if with_update else None
+        self.snapshot = make("snapshot", torch.float32) if with_snapshot else None
+        self.data16 = make("data16", torch.bfloat16) if self.use16 else None
         chunk_param = torch.full((self.nchunks,), -1, dtype=torch.int32)
         lr_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
         wd_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
@@ -65,6 +72,20 @@ class ParamArena:
         self.lr_mult = lr_mult.to(self.device)
         self.wd_mult = wd_mult.to(self.device)
         self.adopt()
+
+    @staticmethod
+    def layout_total(params: Sequence[Param], pad_chunks_to: int = 1) -> int:
+        """Number of arena elements the given owner parameters will occupy (same rules as __init__)."""
+        use16 = ctx().device.type == "cuda" and ctx().is_native
+        off = 0
+        for p in params:
+            if not p.is_owner:
+                continue
+            n = p.size
+            if use16 and getattr(p, "want_padded_ld", False) and len(p.shape) == 2 and p.shape[1] % 8:
+                n = p.shape[0] * ((p.shape[1] + 7) // 8 * 8)
+            off += _round_up(n, CHUNK)
+        return _round_up(max(off, CHUNK), CHUNK * max(1, pad_chunks_to))
 
     def adopt(self) -> None:
         """Re-point every owner parameter's blobs into the arena (existing values are preserved)."""

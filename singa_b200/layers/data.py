@@ -156,10 +156,24 @@ class DataLayer(Layer):
             n = int(np.random.default_rng(1234).integers(0, self.random_skip + 1))
             self.source.skip(n)
             self.random_skip = 0
+        # data parallel worker groups read disjoint records: group g takes batch g of every window of
+        # `ngroups` batches (the reference partitions the record list per worker group offline,
+        # script/load_data.py; here the stride is applied at read time)
+        self.group_id, self.ngroups = 0, 1
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                self.group_id, self.ngroups = dist.get_rank(), dist.get_world_size()
+        except Exception:  # noqa: BLE001
+            pass
+        if self.group_id:
+            self.source.skip(self.group_id * self.batchsize)
 
     def compute_feature(self, training):
         """Read the next batch of records into the pinned host buffers."""
         self.source.next_batch(self._np_pixels, self._np_labels)
+        if self.ngroups > 1:
+            self.source.skip((self.ngroups - 1) * self.batchsize)
 
     prefetching = compute_feature
 

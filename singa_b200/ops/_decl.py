@@ -32,6 +32,14 @@ SIGNATURES = {
     "sg_update_arena": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.POINTER(Updater), vp],
     "sg_easgd_sync": [vp, vp, i64, f32, vp, vp],
     "sg_randomsync": [vp, vp, vp, i64, f32, u64, vp, vp, vp],
+    "sg_ps_push_update": [vp, vp],
+    "sg_ps_flag_set": [vp, vp, i64, vp],
+    "sg_ps_flag_wait": [vp, i32, vp, i64, vp],
+    "sg_ipc_alloc": [i64, vp],
+    "sg_ipc_free": [vp],
+    "sg_ipc_get_handle": [vp, vp],
+    "sg_ipc_open_handle": [vp, vp],
+    "sg_ipc_close_handle": [vp],
 }
 
 

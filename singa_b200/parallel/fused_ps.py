@@ -1,0 +1,164 @@
+"""The B200 parameter server: gradient push and parameter pull as kernels over NVSwitch peer memory.
+
+Every rank is both a worker group and the SERVER for one contiguous chunk range ("shard") of the flat
+parameter arena.  Per layer, right after its backward (the reference's ``UpdateParam`` call site,
+src/worker/worker.cc:290-292):
+
+  1. the worker release-stores its ``ready[layer]`` flag (gradients complete, bf16 weights no longer read);
+  2. the server side — on a separate comm stream, so it overlaps the backward of the layers below — launches
+     ``sg_ps_push_update`` over (layer range ∩ own shard): reduce the peers' gradients through peer loads,
+     apply the Updater to the fp32 master copy, broadcast the new bf16 weights into every rank's mirror,
+     bump ``version[layer][server]`` on every rank.
+
+Right before the layer's next forward (the ``WaitUpdate`` call site, worker.cc:249-253) the worker's compute
+stream acquires the version flags of the shards that intersect the layer — a device-side wait, no host
+message, no host synchronisation.  This is messages M2-M5/M9 of the survey without ZeroMQ.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..device import ctx, step_state
+from ..ops import native
+from ..ops._decl import Updater as CUpdater
+from ..updater import _KIND_ID
+from .symm import SymmetricHeap
+
+MAX_WORLD = 8
+MAX_WAIT = 32
+
+
+class PsPush(ctypes.Structure):
+    _fields_ = [
+        ("world", ctypes.c_int),
+        ("grad", ctypes.c_void_p * MAX_WORLD),
+        ("w16", ctypes.c_void_p * MAX_WORLD),
+        ("ready", ctypes.c_void_p * MAX_WORLD),
+        ("version", ctypes.c_void_p * MAX_WORLD),
+        ("w", ctypes.c_void_p), ("h", ctypes.c_void_p), ("u", ctypes.c_void_p),
+        ("chunk_param", ctypes.c_void_p), ("lr_mult", ctypes.c_void_p), ("wd_mult", ctypes.c_void_p),
+        ("first_chunk", ctypes.c_longlong), ("nchunks", ctypes.c_longlong),
+        ("up", CUpdater),
+        ("step_dev", ctypes.c_void_p), ("value_add", ctypes.c_longlong),
+        ("counter", ctypes.c_void_p),
+        ("max_ctas", ctypes.c_int),
+    ]
+
+
+def shard_bounds(nchunks: int, world: int) -> List[Tuple[int, int]]:
+    per = (nchunks + world - 1) // world
+    return [(min(r * per, nchunks), min((r + 1) * per, nchunks)) for r in range(world)]
+
+
+def symmetric_regions(total_elems: int, nlayers: int, world: int):
+    """Regions of the symmetric heap for an arena of ``total_elems`` elements."""
+    return [("grad", total_elems * 4), ("data16", total_elems * 2),
+            ("ready", max(nlayers, 1) * 8), ("version", max(nlayers, 1) * world * 8)]
+
+
+class FusedExchange:
+    handles_update = True
+
+    def __init__(self, pm, heap: SymmetricHeap):
+        self.pm = pm
+        self.heap = heap
+        self.lib = native.require()
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        assert self.world <= MAX_WORLD, f"fused push/pull supports up to {MAX_WORLD} ranks per node"
+        self.arena = pm.arena
+        self.layers = list(pm._param_layers)
+        self.lidx = {l.name: i for i, l in enumerate(self.layers)}
+        self.shards = shard_bounds(self.arena.nchunks, self.world)
+        self.comm = torch.cuda.Stream()
+        self.counters = torch.zeros(max(len(self.layers), 1), dtype=torch.int32, device=ctx().device)
+        self.step_dev = step_state()["step"]
+        self.lr_dev = step_state()["lr"]
+        # per layer: the chunk range owned by this rank, and the owners whose shards intersect the layer
+        self.mine: Dict[str, Tuple[int, int]] = {}
+        self.owners: Dict[str, List[int]] = {}
+        for l in self.layers:
+            lo, n = pm.layer_ranges[l.name]
+            hi = lo + n
+            s0, s1 = self.shards[self.rank]
+            a, b = max(lo, s0), min(hi, s1)
+            self.mine[l.name] = (a, max(0, b - a))
+            self.owners[l.name] = [r for r, (x, y) in enumerate(self.shards) if max(lo, x) < min(hi, y)]
+        self._wait_arrays = {}
+        for l in self.layers:
+            i = self.lidx[l.name]
+            arr = (ctypes.c_void_p * MAX_WAIT)()
+            owners = self.owners[l.name]
+            assert len(owners) <= MAX_WAIT
+            for k, o in enumerate(owners):
+                arr[k] = heap.ptr("version", self.rank, (i * self.world + o) * 8)
+            self._wait_arrays[l.name] = (arr, len(owners))
+        self.launches = 0
+        if self.world > 1:
+            dist.barrier()
+
+    # -- worker side ---------------------------------------------------------------------------------
+    def update_layer(self, layer, step: int) -> None:
+        i = self.lidx[layer.name]
+        main = torch.cuda.current_stream()
+        native.check(self.lib.sg_ps_flag_set(ctypes.c_void_p(self.heap.ptr("ready", self.rank, i * 8)),
+                                             ctypes.c_void_p(self.step_dev.data_ptr()), 1, main.cuda_stream),
+                     "sg_ps_flag_set")
+        native.count_launch()
+        first, n = self.mine[layer.name]
+        if n <= 0:
+            return
+        # -- server side: my shard of this layer, on the comm stream
+        self.comm.wait_stream(main)
+        a = PsPush()
+        a.world = self.world
+        for r in range(self.world):
+            a.grad[r] = self.heap.ptr("grad", r)
+            a.w16[r] = self.heap.ptr("data16", r)
+            a.ready[r] = self.heap.ptr("ready", r, i * 8)
+            a.version[r] = self.heap.ptr("version", r, (i * self.world + self.rank) * 8)
+        ar, u = self.arena, self.pm.updater
+        a.w = ar.data.data_ptr()
+        a.h = ar.history.data_ptr() if ar.history is not None else None
+        a.u = ar.update.data_ptr() if ar.update is not None else None
+        a.chunk_param, a.lr_mult, a.wd_mult = ar.chunk_param.data_ptr(), ar.lr_mult.data_ptr(), ar.wd_mult.data_ptr()
+        a.first_chunk, a.nchunks = first, n
+        a.up = CUpdater(_KIND_ID[u.kind], getattr(self.pm, "lr", 0.0), u.momentum, u.weight_decay, u.delta,
+                        u.rho, 1.0 / self.world, self.lr_dev.data_ptr())
+        a.step_dev, a.value_add = self.step_dev.data_ptr(), 1
+        a.counter = self.counters[i:i + 1].data_ptr()
+        a.max_ctas = 0
+        native.check(self.lib.sg_ps_push_update(ctypes.byref(a), self.comm.cuda_stream), "sg_ps_push_update")
+        native.count_launch()
+        self.launches += 1
+        for p in layer.get_params():
+            if p.pack16 is not None:   # repacked operands (conv weights) follow the mirror on every rank
+                raise NotImplementedError("fused push/pull with repacked (convolution) weights: use push_pull=nccl")
+
+    def wait_layer(self, layer, step: int) -> None:
+        if layer.name not in self._wait_arrays:
+            return
+        arr, n = self._wait_arrays[layer.name]
+        native.check(self.lib.sg_ps_flag_wait(arr, n, ctypes.c_void_p(self.step_dev.data_ptr()), 0,
+                                              torch.cuda.current_stream().cuda_stream), "sg_ps_flag_wait")
+        native.count_launch()
+
+    # -- reference API no-ops in synchronous mode -----------------------------------------------------------
+    def put_all(self):
+        pass
+
+    def get_all(self):
+        pass
+
+    def sync_all(self, step):
+        pass
+
+    def close(self):
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+        self.heap.close()

@@ -46,8 +46,28 @@ class ParamManager:
         self.param_type = updater_proto.param_type
         self.hogwild = (cluster.nthreads_per_procs == 1 if cluster else True) or updater_proto.hogwild
         owners = [p for p in net.params if p.is_owner]
+        if backend is None:
+            backend = "local" if nservers == 0 else "zmq"
+        import torch.distributed as dist
+        world = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        heap = None
+        allocator = None
+        if backend == "fused":
+            # gradient arena, bf16 mirror and flags live in ONE peer-mapped allocation per rank
+            from .parallel.fused_ps import symmetric_regions
+            from .parallel.symm import SymmetricHeap
+            probe = ParamArena.layout_total(owners, pad_chunks_to=world)
+            nlayers = sum(1 for l in net.layers if l.get_params())
+            heap = SymmetricHeap(symmetric_regions(probe, nlayers, world), dist.get_rank() if world > 1 else 0,
+                                 world, ctx().device)
+
+            def allocator(name, n, dt, heap=heap):
+                if name in ("grad", "data16"):
+                    return heap.tensor(name, dt)
+                return None
         self.arena = ParamArena(owners, with_update=self.updater.needs_update,
-                                with_snapshot=(self.param_type == "RandomSync" and nservers > 0))
+                                with_snapshot=(self.param_type == "RandomSync" and nservers > 0),
+                                allocator=allocator, pad_chunks_to=world if backend in ("fused", "nccl") else 1)
         self.paramid2version: Dict[int, int] = {p.id: 0 for p in net.params}
         self.layer_ranges = {}
         for layer in net.layers:
@@ -56,8 +76,6 @@ class ParamManager:
                 self.layer_ranges[layer.name] = self.arena.chunk_range(ps)
         self._param_layers = [l for l in net.layers if l.get_params()]
         self._first_param_layer = self._param_layers[0] if self._param_layers else None
-        if backend is None:
-            backend = "local" if nservers == 0 else "zmq"
         self.backend_name = backend
         self.backend = None
         if backend == "zmq":
@@ -68,7 +86,7 @@ class ParamManager:
             self.backend = NcclExchange(self)
         elif backend == "fused":
             from .parallel.fused_ps import FusedExchange
-            self.backend = FusedExchange(self)
+            self.backend = FusedExchange(self, heap)
         elif backend != "local":
             raise ValueError(f"unknown exchange backend {backend!r}")
         self.use_device_lr = ctx().is_native

@@ -1,0 +1,83 @@
+"""Fused push kernel on ONE GPU: the ranks are emulated as separate local buffers (every 'peer pointer' is a
+local pointer), flags pre-set so nothing waits — numerics of reduce + update + broadcast + version publish."""
+import ctypes
+
+import pytest
+import torch
+
+from singa_b200.ops import native
+from singa_b200.ops import reference as R
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("kind,kid", [("kSGD", 0), ("kAdaGrad", 2)])
+def test_push_update_emulated(world, kind, kid):
+    from singa_b200.ops._decl import Updater as CUpdater
+    from singa_b200.parallel.fused_ps import PsPush
+    lib = native.require()
+    dev = "cuda"
+    nchunks = 40
+    n = nchunks * 1024
+    grads = [torch.randn(n, device=dev) for _ in range(world)]
+    mirrors = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(world)]
+    ready = torch.full((world,), 5, dtype=torch.int64, device=dev)
+    version = torch.zeros(world, dtype=torch.int64, device=dev)
+    w = torch.randn(n, device=dev)
+    h = torch.rand(n, device=dev)
+    chunk_param = torch.zeros(nchunks, dtype=torch.int32, device=dev)
+    chunk_param[20:] = 1
+    lr_mult = torch.tensor([1.0, 0.5], device=dev)
+    wd_mult = torch.tensor([1.0, 1.0], device=dev)
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    step_dev = torch.tensor([4], dtype=torch.int64, device=dev)
+    wr, hr = w.clone(), h.clone()
+    first, cnt = 8, 25       # only a sub-range is owned by "this server"
+    a = PsPush()
+    a.world = world
+    for r in range(world):
+        a.grad[r] = grads[r].data_ptr()
+        a.w16[r] = mirrors[r].data_ptr()
+        a.ready[r] = ready[r:r + 1].data_ptr()
+        a.version[r] = version[r:r + 1].data_ptr()
+    a.w, a.h, a.u = w.data_ptr(), h.data_ptr(), None
+    a.chunk_param, a.lr_mult, a.wd_mult = chunk_param.data_ptr(), lr_mult.data_ptr(), wd_mult.data_ptr()
+    a.first_chunk, a.nchunks = first, cnt
+    a.up = CUpdater(kid, 0.01, 0.9, 0.001, 1e-7, 0.9, 1.0 / world, None)
+    a.step_dev, a.value_add = step_dev.data_ptr(), 1
+    a.counter = counter.data_ptr()
+    a.max_ctas = 7
+    for _ in range(2):   # two launches: the arrival counter must be back to zero after the first
+        native.check(lib.sg_ps_push_update(ctypes.byref(a), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        g = sum(grads) / world
+        for pid, (lo, hi) in enumerate(((0, 20 * 1024), (20 * 1024, n))):
+            lo2, hi2 = max(lo, first * 1024), min(hi, (first + cnt) * 1024)
+            if lo2 < hi2:
+                R.update_ref(kind, wr[lo2:hi2], g[lo2:hi2], hr[lo2:hi2], None, lr=0.01 * float(lr_mult[pid]),
+                             momentum=0.9, wd=0.001, delta=1e-7, rho=0.9)
+        torch.testing.assert_close(w, wr, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(h, hr, rtol=1e-5, atol=1e-6)
+        lo, hi = first * 1024, (first + cnt) * 1024
+        for m in mirrors:
+            assert torch.equal(m[lo:hi], w[lo:hi].to(torch.bfloat16))
+            assert float(m[:lo].abs().sum()) == 0 and float(m[hi:].abs().sum()) == 0
+        assert int(counter.item()) == 0
+        assert version.tolist() == [5] * world
+
+
+def test_flag_set_wait():
+    lib = native.require()
+    flags = torch.zeros(3, dtype=torch.int64, device="cuda")
+    step = torch.tensor([9], dtype=torch.int64, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    for i in range(3):
+        native.check(lib.sg_ps_flag_set(ctypes.c_void_p(flags[i:i + 1].data_ptr()),
+                                        ctypes.c_void_p(step.data_ptr()), 1, s))
+    arr = (ctypes.c_void_p * 32)()
+    for i in range(3):
+        arr[i] = flags[i:i + 1].data_ptr()
+    native.check(lib.sg_ps_flag_wait(arr, 3, ctypes.c_void_p(step.data_ptr()), 1, s))   # already satisfied
+    torch.cuda.synchronize()
+    assert flags.tolist() == [10, 10, 10]

@@ -1,0 +1,101 @@
+"""Multi-GPU check of the parameter-server data plane (run under torch.distributed.run, 1 process per GPU):
+
+  W ranks x batch B with push_pull in {fused, nccl}  ==  1 process x batch W*B   (same records, same init)
+
+Every rank trains a small MNIST-shaped MLP for a few steps; rank 0 then trains the equivalent single-process
+job and compares the bf16 weight mirrors.  Prints PASS/FAIL lines; exit code 0 only if all pass.
+"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def run(push_pull, world, rank, steps, batch, hidden):
+    from singa_b200 import device
+    from singa_b200.cluster import Cluster
+    from singa_b200.models import configs
+    from singa_b200.proto import schema as S
+    from singa_b200.worker import Worker
+    model = configs.mnist_mlp(batch=batch, hidden=hidden)
+    model.display_frequency = 0
+    model.prefetch = False
+    model.updater.base_learning_rate = 0.02
+    model.updater.momentum = 0.9
+    cluster = None
+    if push_pull is not None:
+        cp = S.ClusterProto()
+        cp.nworkers = cp.nservers = world
+        cp.workspace = "/tmp/singa_b200_check"
+        cp.synchronous = True
+        Cluster.reset()
+        cluster = Cluster.get(cp, "", rank)
+    w = Worker(cluster, backend=push_pull, use_graph=False)
+    w.build(model)
+    ex = w.executor
+    for step in range(steps):
+        ex.ticks += 1
+        ex.train_one_batch(step)
+    torch.cuda.synchronize()
+    if push_pull is not None:
+        dist.barrier()
+    out = {p.name + str(p.id): p.data16.float().clone() for p in w.pm.arena.params if p.data16 is not None}
+    loss = float(w.train_net.losslayers[0].metric[0]) / steps
+    w.pm.finish()
+    return out, loss
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from singa_b200 import device
+    device.set_context(f"cuda:{local}", "native")
+    steps, batch, hidden = 6, 64, (256, 136)
+    ok = True
+    results = {}
+    for pp in ("nccl", "fused"):
+        results[pp] = run(pp, world, rank, steps, batch, hidden)
+        dist.barrier()
+    # every rank must hold identical mirrors
+    for pp, (mir, loss) in results.items():
+        for k, v in mir.items():
+            ref = v.clone()
+            dist.broadcast(ref, 0)
+            same = bool(torch.equal(ref, v))
+            if not same:
+                ok = False
+                print(f"[rank {rank}] FAIL {pp}: mirror {k} differs from rank 0 (max {float((ref - v).abs().max())})")
+    if rank == 0:
+        # single-process reference with batch world*B reading the same records
+        import torch.distributed as d2
+        saved = d2.is_initialized
+        d2.is_initialized = lambda: False     # make the data layer / arena behave as a single process
+        try:
+            ref, ref_loss = run(None, 1, 0, steps, batch * world, hidden)
+        finally:
+            d2.is_initialized = saved
+        for pp, (mir, loss) in results.items():
+            worst = 0.0
+            for k, v in mir.items():
+                rel = float((v - ref[k]).norm() / (ref[k].norm() + 1e-12))
+                worst = max(worst, rel)
+            status = "PASS" if worst < 2e-2 else "FAIL"
+            ok = ok and status == "PASS"
+            print(f"{status} {pp}: world={world} worst relative weight difference vs 1 process x batch "
+                  f"{batch * world}: {worst:.3e}; mean loss {loss:.4f} vs {ref_loss:.4f}")
+        a, b = results["nccl"][0], results["fused"][0]
+        worst = max(float((a[k] - b[k]).abs().max()) for k in a)
+        print(f"INFO fused vs nccl max abs mirror difference: {worst:.3e}")
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
