@@ -287,9 +287,14 @@ def main():
             "gpu_launches": gpu_launches,
         }
         print(json.dumps(out))
-    w.pm.finish()
+    sys.stdout.flush()
     if world > 1:
-        dist.destroy_process_group()
+        # NCCL work captured in CUDA graphs can make destroy_process_group hang; every rank has passed the final
+        # barrier, so leave without the collective teardown
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
+    w.pm.finish()
     return 0
 
 

@@ -52,6 +52,9 @@ struct GemmParams {
   const void* aux; long long ldaux; int aux_bf16;
   int accumulate;
   int perm_c, perm_kk;
+  const unsigned long long* wait_flags[8];
+  int nwait;
+  const unsigned long long* wait_seq;
 };
 
 __device__ __forceinline__ float tanh_fast(float x) {
@@ -128,6 +131,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
+      if (p.nwait > 0) {
+        // fused parameter pull: the weights this GEMM reads are written into this GPU's mirror by the
+        // server shards' push kernels (peer stores over NVLink); acquire their version counters here, then
+        // order the generic-proxy acquire before the async-proxy (TMA) reads
+        const unsigned long long target = *p.wait_seq;
+        for (int i = 0; i < p.nwait; ++i) {
+          const unsigned long long* f = p.wait_flags[i];
+          unsigned long long v;
+          const long long t0 = clock64();
+          do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+            if (v < target && clock64() - t0 > 60000000000LL) __trap();
+          } while (v < target);
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
       uint32_t stage = 0, phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile % m_tiles) * BM;
@@ -470,6 +489,10 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   p.bias = ep->bias; p.act = ep->act; p.grad_act = ep->grad_act;
   p.aux = ep->aux; p.ldaux = ep->ldaux; p.aux_bf16 = ep->aux_bf16;
   p.accumulate = ep->accumulate; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
+  SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 8, "sg_gemm_bf16: at most 8 wait flags");
+  SG_REQUIRE(ep->nwait == 0 || ep->wait_seq != nullptr, "sg_gemm_bf16: wait flags need wait_seq");
+  for (int i = 0; i < 8; ++i) p.wait_flags[i] = i < ep->nwait ? ep->wait_flags[i] : nullptr;
+  p.nwait = ep->nwait; p.wait_seq = ep->wait_seq;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   switch (bn) {
     case 256: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, p, s);

@@ -39,8 +39,10 @@ struct PushParams {
   const int* chunk_param; const float* lr_mult; const float* wd_mult;
   long long first_chunk, nchunks;
   int kind; float lr, momentum, wd, delta, rho, grad_scale; const float* lr_dev;
-  const long long* step_dev; long long value_add;   // flag value = *step_dev + value_add (or value_add alone)
-  unsigned int* counter;                             // scratch: CTA arrival counter, zero between launches
+  const long long* step_dev; long long value_add;   // explicit flag value = *step_dev + value_add (seq == nullptr)
+  unsigned long long* scratch;                       // [0] CTA arrival counter (zero between launches)
+                                                     // [1] launch sequence number (self-counting flag value)
+  int self_count;
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -101,8 +103,12 @@ __device__ __forceinline__ void upd(int kind, float lr, float wd, float momentum
 }
 
 __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p) {
-  const unsigned long long target =
-      static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  // Flag value of this launch.  Self-counting mode (the default of the framework): the n-th launch for a
+  // layer waits for ready >= n and publishes version = n, with n kept in scratch[1] — no dependence on a step
+  // scalar that another stream may already have advanced.
+  const unsigned long long target = p.self_count
+      ? p.scratch[1] + 1ull
+      : static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
   // 1. wait for every rank's gradients of this layer
   if (threadIdx.x < p.world && p.ready[threadIdx.x] != nullptr) wait_flag_ge(p.ready[threadIdx.x], target);
   __syncthreads();
@@ -110,51 +116,71 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
   const float base_lr = p.lr_dev ? __ldg(p.lr_dev) : p.lr;
   const bool need_h = p.kind != SG_UPD_SGD || p.momentum > 0.f;
   const bool need_u = p.kind == SG_UPD_ADADELTA;
-  for (long long c = blockIdx.x; c < p.nchunks; c += gridDim.x) {
-    const long long chunk = p.first_chunk + c;
-    const int pid = p.chunk_param[chunk];
-    if (pid < 0) continue;
-    const float lr = base_lr * p.lr_mult[pid];
-    const float wd = p.wd * p.wd_mult[pid];
-    const long long i = chunk * CHUNK + threadIdx.x * 4;
+  // Two chunks per iteration with every peer load issued before the first use: NVLink reads have ~2 us
+  // latency, so bandwidth comes from bytes in flight (2 x world x 16 B per thread).
+  constexpr int U = 2;
+  for (long long c0 = static_cast<long long>(blockIdx.x) * U; c0 < p.nchunks;
+       c0 += static_cast<long long>(gridDim.x) * U) {
+    float4 g[U];
+    int pid[U];
+    long long idx[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long c = c0 + k;
+      pid[k] = c < p.nchunks ? p.chunk_param[p.first_chunk + c] : -1;
+      idx[k] = (p.first_chunk + c) * CHUNK + threadIdx.x * 4;
+      g[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     // 2. reduce the peers' gradients (128-bit loads; remote ranks go over NVLink)
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int r = 0; r < MAX_WORLD; ++r) {
       if (r < p.world) {
-        const float4 t = *reinterpret_cast<const float4*>(p.grad[r] + i);
-        g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+        float4 t[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k)
+          t[k] = pid[k] >= 0 ? *reinterpret_cast<const float4*>(p.grad[r] + idx[k]) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < U; ++k) { g[k].x += t[k].x; g[k].y += t[k].y; g[k].z += t[k].z; g[k].w += t[k].w; }
       }
     }
-    g.x *= p.grad_scale; g.y *= p.grad_scale; g.z *= p.grad_scale; g.w *= p.grad_scale;
-    // 3. server update on the local master copy
-    float4 wv = *reinterpret_cast<const float4*>(p.w + i);
-    float4 hv = make_float4(0.f, 0.f, 0.f, 0.f), uv = hv;
-    if (need_h) hv = *reinterpret_cast<const float4*>(p.h + i);
-    if (need_u) uv = *reinterpret_cast<const float4*>(p.u + i);
-    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.x, g.x, hv.x, uv.x);
-    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.y, g.y, hv.y, uv.y);
-    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.z, g.z, hv.z, uv.z);
-    upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.w, g.w, hv.w, uv.w);
-    *reinterpret_cast<float4*>(p.w + i) = wv;
-    if (need_h) *reinterpret_cast<float4*>(p.h + i) = hv;
-    if (need_u) *reinterpret_cast<float4*>(p.u + i) = uv;
-    // 4. broadcast the fresh bf16 weights into every rank's mirror
-    const __nv_bfloat162 a = __floats2bfloat162_rn(wv.x, wv.y), b = __floats2bfloat162_rn(wv.z, wv.w);
-    uint2 o;
-    o.x = *reinterpret_cast<const uint32_t*>(&a);
-    o.y = *reinterpret_cast<const uint32_t*>(&b);
 #pragma unroll
-    for (int r = 0; r < MAX_WORLD; ++r)
-      if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+    for (int k = 0; k < U; ++k) {
+      if (pid[k] < 0) continue;
+      const long long i = idx[k];
+      const float lr = base_lr * p.lr_mult[pid[k]];
+      const float wd = p.wd * p.wd_mult[pid[k]];
+      float4 gv = g[k];
+      gv.x *= p.grad_scale; gv.y *= p.grad_scale; gv.z *= p.grad_scale; gv.w *= p.grad_scale;
+      // 3. server update on the local master copy
+      float4 wv = *reinterpret_cast<const float4*>(p.w + i);
+      float4 hv = make_float4(0.f, 0.f, 0.f, 0.f), uv = hv;
+      if (need_h) hv = *reinterpret_cast<const float4*>(p.h + i);
+      if (need_u) uv = *reinterpret_cast<const float4*>(p.u + i);
+      upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.x, gv.x, hv.x, uv.x);
+      upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.y, gv.y, hv.y, uv.y);
+      upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.z, gv.z, hv.z, uv.z);
+      upd(p.kind, lr, wd, p.momentum, p.delta, p.rho, wv.w, gv.w, hv.w, uv.w);
+      *reinterpret_cast<float4*>(p.w + i) = wv;
+      if (need_h) *reinterpret_cast<float4*>(p.h + i) = hv;
+      if (need_u) *reinterpret_cast<float4*>(p.u + i) = uv;
+      // 4. broadcast the fresh bf16 weights into every rank's mirror
+      const __nv_bfloat162 a = __floats2bfloat162_rn(wv.x, wv.y), b = __floats2bfloat162_rn(wv.z, wv.w);
+      uint2 o;
+      o.x = *reinterpret_cast<const uint32_t*>(&a);
+      o.y = *reinterpret_cast<const uint32_t*>(&b);
+#pragma unroll
+      for (int r = 0; r < MAX_WORLD; ++r)
+        if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+    }
   }
   // 5. publish: last CTA to arrive bumps the version flag on every rank
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
-    const unsigned int done = atomicAdd(p.counter, 1u) + 1u;
+    const unsigned long long done = atomicAdd(p.scratch, 1ull) + 1ull;
     if (done == gridDim.x) {
-      *p.counter = 0u;   // scratch must read zero at the next launch
+      p.scratch[0] = 0ull;   // arrival counter must read zero at the next launch
+      p.scratch[1] = target; // every CTA has read the old sequence number by now (all have arrived)
       __threadfence_system();
       for (int r = 0; r < p.world; ++r)
         if (p.version[r] != nullptr) st_release_sys(p.version[r], target);
@@ -162,9 +188,14 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
   }
 }
 
-__global__ void ps_flag_set_kernel(unsigned long long* flag, const long long* step_dev, long long value_add) {
+__global__ void ps_flag_set_kernel(unsigned long long* flag, const long long* step_dev, long long value_add,
+                                   int bump, unsigned long long* local_seq) {
+  if (local_seq != nullptr) *local_seq += 1ull;   // consumer-side wait sequence of the same layer (see gemm wait)
   __threadfence_system();
-  st_release_sys(flag, static_cast<unsigned long long>((step_dev ? *step_dev : 0) + value_add));
+  // bump: flag += 1 (single writer: the owning GPU's stream-ordered launches), else explicit value
+  const unsigned long long v = bump ? (*flag + 1ull)
+                                    : static_cast<unsigned long long>((step_dev ? *step_dev : 0) + value_add);
+  st_release_sys(flag, v);
 }
 
 struct WaitParams {
@@ -172,10 +203,12 @@ struct WaitParams {
   int n;
   const long long* step_dev;
   long long value_add;
+  const unsigned long long* seq;   // self-counting: wait for flags >= *seq (sg_ps_flag_bump advances it)
 };
 __global__ void ps_flag_wait_kernel(const WaitParams p) {
-  const unsigned long long target =
-      static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  const unsigned long long target = p.seq
+      ? *p.seq
+      : static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
   if (threadIdx.x < p.n) wait_flag_ge(p.flags[threadIdx.x], target);
 }
 
@@ -188,7 +221,7 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   SG_REQUIRE(a != nullptr, "sg_ps_push_update: null args");
   if (a->nchunks <= 0) return 0;
   SG_REQUIRE(a->world >= 1 && a->world <= MAX_WORLD, "sg_ps_push_update: world %d out of range [1,%d]", a->world, MAX_WORLD);
-  SG_REQUIRE(a->counter != nullptr, "sg_ps_push_update: needs a zeroed arrival counter (scratch)");
+  SG_REQUIRE(a->scratch != nullptr, "sg_ps_push_update: needs 16 bytes of zero-initialised scratch");
   SG_REQUIRE(a->up.kind >= SG_UPD_SGD && a->up.kind <= SG_UPD_ADADELTA, "sg_ps_push_update: unknown updater");
   const bool need_h = a->up.kind != SG_UPD_SGD || a->up.momentum > 0.f;
   SG_REQUIRE(!need_h || a->h != nullptr, "sg_ps_push_update: updater needs a history buffer");
@@ -208,8 +241,8 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   p.kind = a->up.kind; p.lr = a->up.lr; p.momentum = a->up.momentum; p.wd = a->up.weight_decay;
   p.delta = a->up.delta; p.rho = a->up.rho; p.grad_scale = a->up.grad_scale; p.lr_dev = a->up.lr_dev;
   p.step_dev = a->step_dev; p.value_add = a->value_add;
-  p.counter = a->counter;
-  long long grid = a->nchunks;
+  p.scratch = a->scratch; p.self_count = a->self_count;
+  long long grid = (a->nchunks + 1) / 2;
   const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward
   if (grid > cap) grid = cap;
   ps_push_update_kernel<<<static_cast<unsigned>(grid), 256, 0, s>>>(p);
@@ -217,20 +250,26 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   return 0;
 }
 
+extern "C" int sg_ps_flag_bump(unsigned long long* flag, unsigned long long* local_seq, void* stream) {
+  ps_flag_set_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flag, nullptr, 0, 1, local_seq);
+  SG_CHECK_LAUNCH("ps_flag_bump");
+  return 0;
+}
+
 extern "C" int sg_ps_flag_set(unsigned long long* flag, const long long* step_dev, long long value_add,
                               void* stream) {
-  ps_flag_set_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flag, step_dev, value_add);
+  ps_flag_set_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flag, step_dev, value_add, 0, nullptr);
   SG_CHECK_LAUNCH("ps_flag_set");
   return 0;
 }
 
 extern "C" int sg_ps_flag_wait(const unsigned long long* const* flags, int n, const long long* step_dev,
-                               long long value_add, void* stream) {
+                               long long value_add, const unsigned long long* seq, void* stream) {
   SG_REQUIRE(n >= 0 && n <= SG_PS_MAX_WAIT, "sg_ps_flag_wait: at most %d flags per call", SG_PS_MAX_WAIT);
   if (n == 0) return 0;
   WaitParams p;
   for (int i = 0; i < SG_PS_MAX_WAIT; ++i) p.flags[i] = i < n ? flags[i] : nullptr;
-  p.n = n; p.step_dev = step_dev; p.value_add = value_add;
+  p.n = n; p.step_dev = step_dev; p.value_add = value_add; p.seq = seq;
   ps_flag_wait_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p);
   SG_CHECK_LAUNCH("ps_flag_wait");
   return 0;

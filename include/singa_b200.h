@@ -49,6 +49,12 @@ typedef struct SgGemmEpilogue {
   int accumulate;        /* d32 += result instead of = */
   int perm_c;            /* >0: column j=(kk_idx*perm_c + c) is stored at column c*perm_kk + kk_idx (conv wgrad -> {F, C*k*k}) */
   int perm_kk;
+  /* Parameter pull fused into the GEMM (src/utils/param_manager.cc:204-234 WaitUpdate): before the first
+   * operand load the TMA producer acquire-spins until every wait_flags[i] >= *wait_seq — the version counters
+   * the parameter-server push kernel bumps after broadcasting fresh weights into this GPU's bf16 mirror. */
+  const unsigned long long* wait_flags[8];
+  int nwait;
+  const unsigned long long* wait_seq;
 } SgGemmEpilogue;
 
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
@@ -167,15 +173,22 @@ typedef struct SgPsPush {
   const int* chunk_param; const float* lr_mult; const float* wd_mult;
   long long first_chunk, nchunks;                   /* chunk range updated by this launch (owned by this rank) */
   SgUpdater up;
-  const long long* step_dev; long long value_add;
-  unsigned int* counter;                            /* scratch: 4 bytes of device memory, zero between launches */
+  const long long* step_dev; long long value_add;   /* explicit flag value (used when self_count == 0) */
+  unsigned long long* scratch;                      /* 16 bytes of device memory, zero-initialised once:
+                                                       [0] CTA arrival counter, [1] launch sequence number */
+  int self_count;                                   /* 1: flag value = scratch[1] + 1 (n-th launch waits for ready >= n,
+                                                       publishes version = n); independent of any step scalar */
   int max_ctas;                                     /* CTA budget (0 = 64) so backward keeps the SMs */
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
 /* release-store / acquire-wait on 64-bit flags in (peer) device memory */
 int sg_ps_flag_set(unsigned long long* flag, const long long* step_dev, long long value_add, void* stream);
+/* flag += 1 (single writer); local_seq (optional, local memory) += 1 as well — the per-layer sequence number
+ * that sg_gemm_bf16's fused weight wait reads (SgGemmEpilogue.wait_seq). */
+int sg_ps_flag_bump(unsigned long long* flag, unsigned long long* local_seq, void* stream);
+/* seq != NULL: wait for flags >= *seq (the sequence number sg_ps_flag_bump advances), else for the explicit value */
 int sg_ps_flag_wait(const unsigned long long* const* flags, int n, const long long* step_dev,
-                    long long value_add, void* stream);
+                    long long value_add, const unsigned long long* seq, void* stream);
 /* CUDA-IPC arenas: these (and only these) entry points allocate / free device memory. */
 int sg_ipc_alloc(long long bytes, void** out);
 int sg_ipc_free(void* p);

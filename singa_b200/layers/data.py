@@ -11,6 +11,8 @@ compute of batch i.
 """
 from __future__ import annotations
 
+import zlib
+
 import os
 import threading
 from typing import List, Optional
@@ -143,7 +145,7 @@ class DataLayer(Layer):
         self.batchsize = int(dp.batchsize)
         assert self.batchsize > 0, f"data layer {self.name}: batchsize must be set"
         self.random_skip = int(dp.random_skip)
-        self.source = make_source(dp, self.type_id, seed=hash(self.name) & 0xFFFF)
+        self.source = make_source(dp, self.type_id, seed=zlib.crc32(self.name.encode()) & 0xFFFF)
         self.sample_shape = list(self.source.sample_shape)
         d = int(np.prod(self.sample_shape))
         pin = torch.cuda.is_available()

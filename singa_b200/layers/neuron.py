@@ -15,6 +15,8 @@ Fusions decided by ``NeuralNet.fuse_activations`` (natural fusion boundaries of 
 """
 from __future__ import annotations
 
+import zlib
+
 from typing import List, Optional
 
 import torch
@@ -84,6 +86,8 @@ class NeuronLayer(Layer):
 class InnerProductLayer(NeuronLayer):
     """data = src . W + b with W {vdim, hdim}  (src/worker/layer.cc:162-213)."""
     type_id = "kInnerProduct"
+    supports_fused_pull = True     # the forward GEMM can acquire the parameter server's version flags itself
+    pull_wait = None
 
     def connection_type(self, k):
         return S.kOneToAll
@@ -176,7 +180,8 @@ class InnerProductLayer(NeuronLayer):
             out32 = self.data if self.data.dtype == torch.float32 else None
             out16 = self.data if self.data.dtype == torch.bfloat16 else None
             K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, out32=out32,
-                   out16=out16, bias=self.bias.data if self.bias_term else None, act=self.fused_act)
+                   out16=out16, bias=self.bias.data if self.bias_term else None, act=self.fused_act,
+                   wait=self.pull_wait if training else None)
             self._x_saved = x
         else:
             y = R.ip_fwd(x, self.weight.data, self.bias.data if self.bias_term else None)
@@ -489,7 +494,7 @@ class DropoutLayer(NeuronLayer):
         assert len(self.srclayers) == 1
         self.pkeep = 1.0 - self.proto.dropout_param.dropout_ratio
         self._alloc(self.srclayers[0].shape(self))
-        self.seed_base = (hash(self.name) & 0xFFFFFF) << 20
+        self.seed_base = (zlib.crc32(self.name.encode()) & 0xFFFFFF) << 20
         self.step_seed = 0
         self._training = False
 

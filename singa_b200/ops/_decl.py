@@ -34,7 +34,8 @@ SIGNATURES = {
     "sg_randomsync": [vp, vp, vp, i64, f32, u64, vp, vp, vp],
     "sg_ps_push_update": [vp, vp],
     "sg_ps_flag_set": [vp, vp, i64, vp],
-    "sg_ps_flag_wait": [vp, i32, vp, i64, vp],
+    "sg_ps_flag_wait": [vp, i32, vp, i64, vp, vp],
+    "sg_ps_flag_bump": [vp, vp, vp],
     "sg_ipc_alloc": [i64, vp],
     "sg_ipc_free": [vp],
     "sg_ipc_get_handle": [vp, vp],

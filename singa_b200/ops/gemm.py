@@ -59,7 +59,8 @@ def gemm_ref(a, b, a_mn=False, b_mn=False, bias=None, act=ACT_NONE, grad_act=ACT
 def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False, b_mn=False,
          out32: torch.Tensor | None = None, out16: torch.Tensor | None = None,
          bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
-         aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None):
+         aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None,
+         wait: tuple | None = None):
     """Launch the sm_100a kernel.  ``a``/``b`` are 2-D bf16 CUDA tensors whose last dim is contiguous
     (row stride = leading dimension, multiple of 8).  Outputs are written in place."""
     lib = native.require()
@@ -83,6 +84,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
     ep.accumulate = 1 if accumulate else 0
     if perm is not None:
         ep.perm_c, ep.perm_kk = perm
+    if wait is not None:   # (list of flag addresses, address of the sequence number): fused parameter pull
+        flags, seq = wait
+        for i, f in enumerate(flags):
+            ep.wait_flags[i] = f
+        ep.nwait, ep.wait_seq = len(flags), seq
     rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
                           b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
     native.check(rc, "sg_gemm_bf16")

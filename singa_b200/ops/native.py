@@ -28,6 +28,7 @@ class GemmEpilogue(ctypes.Structure):
         ("aux", ctypes.c_void_p), ("ldaux", ctypes.c_longlong), ("aux_bf16", ctypes.c_int),
         ("accumulate", ctypes.c_int),
         ("perm_c", ctypes.c_int), ("perm_kk", ctypes.c_int),
+        ("wait_flags", ctypes.c_void_p * 8), ("nwait", ctypes.c_int), ("wait_seq", ctypes.c_void_p),
     ]
 
 

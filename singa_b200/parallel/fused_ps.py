@@ -44,7 +44,8 @@ class PsPush(ctypes.Structure):
         ("first_chunk", ctypes.c_longlong), ("nchunks", ctypes.c_longlong),
         ("up", CUpdater),
         ("step_dev", ctypes.c_void_p), ("value_add", ctypes.c_longlong),
-        ("counter", ctypes.c_void_p),
+        ("scratch", ctypes.c_void_p),
+        ("self_count", ctypes.c_int),
         ("max_ctas", ctypes.c_int),
     ]
 
@@ -75,45 +76,59 @@ class FusedExchange:
         self.lidx = {l.name: i for i, l in enumerate(self.layers)}
         self.shards = shard_bounds(self.arena.nchunks, self.world)
         self.comm = torch.cuda.Stream()
-        self.counters = torch.zeros(max(len(self.layers), 1), dtype=torch.int32, device=ctx().device)
-        self.step_dev = step_state()["step"]
-        self.lr_dev = step_state()["lr"]
-        # per layer: the chunk range owned by this rank, and the owners whose shards intersect the layer
+        import os
+        self.max_ctas = int(os.environ.get("SINGA_B200_PUSH_CTAS", "96"))
+        # per layer: push scratch (arrival counter + sequence number) and the consumer's wait sequence number;
+        # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
+        self.scratch = torch.zeros(max(len(self.layers), 1), 2, dtype=torch.int64, device=ctx().device)
+        self.wait_seq = torch.zeros(max(len(self.layers), 1), dtype=torch.int64, device=ctx().device)
+        # Ownership is striped PER LAYER: layer L's chunk range is cut into `world` contiguous pieces and rank r
+        # serves piece r, so every layer's push is spread over all GPUs (the last layers of backward would
+        # otherwise all land on the rank owning the head of the arena).
         self.mine: Dict[str, Tuple[int, int]] = {}
         self.owners: Dict[str, List[int]] = {}
         for l in self.layers:
             lo, n = pm.layer_ranges[l.name]
-            hi = lo + n
-            s0, s1 = self.shards[self.rank]
-            a, b = max(lo, s0), min(hi, s1)
-            self.mine[l.name] = (a, max(0, b - a))
-            self.owners[l.name] = [r for r, (x, y) in enumerate(self.shards) if max(lo, x) < min(hi, y)]
+            pieces = [(lo + a, b - a) for a, b in shard_bounds(n, self.world)]
+            self.mine[l.name] = pieces[self.rank]
+            self.owners[l.name] = [r for r, (_, cnt) in enumerate(pieces) if cnt > 0]
         self._wait_arrays = {}
         for l in self.layers:
             i = self.lidx[l.name]
             arr = (ctypes.c_void_p * MAX_WAIT)()
             owners = self.owners[l.name]
             assert len(owners) <= MAX_WAIT
+            addrs = []
             for k, o in enumerate(owners):
                 arr[k] = heap.ptr("version", self.rank, (i * self.world + o) * 8)
+                addrs.append(arr[k])
             self._wait_arrays[l.name] = (arr, len(owners))
+            # parameter pull fused into the consumer GEMM: layers that support it get the flag addresses and
+            # the sequence number and acquire them inside their forward GEMM's TMA producer warp
+            if getattr(l, "supports_fused_pull", False) and len(addrs) <= 8:
+                l.pull_wait = (addrs, self.wait_seq[i:i + 1].data_ptr())
         self.launches = 0
         if self.world > 1:
             dist.barrier()
 
     # -- worker side ---------------------------------------------------------------------------------
-    def update_layer(self, layer, step: int) -> None:
+    def update_layer(self, layer, step: int, side_stream=None) -> None:
         i = self.lidx[layer.name]
         main = torch.cuda.current_stream()
-        native.check(self.lib.sg_ps_flag_set(ctypes.c_void_p(self.heap.ptr("ready", self.rank, i * 8)),
-                                             ctypes.c_void_p(self.step_dev.data_ptr()), 1, main.cuda_stream),
-                     "sg_ps_flag_set")
+        # everything below runs on the comm stream, which waits for BOTH gradients of the layer (data
+        # gradient on the compute stream, parameter gradient on its side stream): the compute stream goes
+        # straight on to the layer below
+        self.comm.wait_stream(main)
+        if side_stream is not None:
+            self.comm.wait_stream(side_stream)
+        native.check(self.lib.sg_ps_flag_bump(ctypes.c_void_p(self.heap.ptr("ready", self.rank, i * 8)),
+                                              ctypes.c_void_p(self.wait_seq[i:i + 1].data_ptr()),
+                                              self.comm.cuda_stream), "sg_ps_flag_bump")
         native.count_launch()
         first, n = self.mine[layer.name]
         if n <= 0:
             return
-        # -- server side: my shard of this layer, on the comm stream
-        self.comm.wait_stream(main)
+        # -- server side: my piece of this layer
         a = PsPush()
         a.world = self.world
         for r in range(self.world):
@@ -128,10 +143,11 @@ class FusedExchange:
         a.chunk_param, a.lr_mult, a.wd_mult = ar.chunk_param.data_ptr(), ar.lr_mult.data_ptr(), ar.wd_mult.data_ptr()
         a.first_chunk, a.nchunks = first, n
         a.up = CUpdater(_KIND_ID[u.kind], getattr(self.pm, "lr", 0.0), u.momentum, u.weight_decay, u.delta,
-                        u.rho, 1.0 / self.world, self.lr_dev.data_ptr())
-        a.step_dev, a.value_add = self.step_dev.data_ptr(), 1
-        a.counter = self.counters[i:i + 1].data_ptr()
-        a.max_ctas = 0
+                        u.rho, 1.0 / self.world, None)   # LR by value: this runs on the comm stream
+        a.step_dev, a.value_add = None, 0
+        a.scratch = self.scratch[i].data_ptr()
+        a.self_count = 1
+        a.max_ctas = self.max_ctas
         native.check(self.lib.sg_ps_push_update(ctypes.byref(a), self.comm.cuda_stream), "sg_ps_push_update")
         native.count_launch()
         self.launches += 1
@@ -140,12 +156,16 @@ class FusedExchange:
                 raise NotImplementedError("fused push/pull with repacked (convolution) weights: use push_pull=nccl")
 
     def wait_layer(self, layer, step: int) -> None:
-        if layer.name not in self._wait_arrays:
-            return
+        if layer.name not in self._wait_arrays or getattr(layer, "pull_wait", None) is not None:
+            return   # no parameters, or the wait happens inside the layer's forward GEMM
         arr, n = self._wait_arrays[layer.name]
-        native.check(self.lib.sg_ps_flag_wait(arr, n, ctypes.c_void_p(self.step_dev.data_ptr()), 0,
+        i = self.lidx[layer.name]
+        native.check(self.lib.sg_ps_flag_wait(arr, n, None, 0, ctypes.c_void_p(self.wait_seq[i:i + 1].data_ptr()),
                                               torch.cuda.current_stream().cuda_stream), "sg_ps_flag_wait")
         native.count_launch()
+
+    def end_step(self, step: int) -> None:
+        torch.cuda.current_stream().wait_stream(self.comm)
 
     # -- reference API no-ops in synchronous mode -----------------------------------------------------------
     def put_all(self):

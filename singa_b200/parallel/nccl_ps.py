@@ -23,7 +23,7 @@ class NcclExchange:
         self.hi = self.lo + self.per * 1024
         self.last_layer = pm._first_param_layer   # its gradient is the last one produced by backward
 
-    def update_layer(self, layer, step: int) -> None:
+    def update_layer(self, layer, step: int, side_stream=None) -> None:
         if layer is not self.last_layer:
             return
         ar = self.arena

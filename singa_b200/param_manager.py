@@ -124,10 +124,12 @@ class ParamManager:
         if self.use_device_lr:
             set_step_state(step, self.lr)
 
-    def update_param(self, layer, step: int) -> None:
-        """Called right after ``layer``'s backward."""
+    def update_param(self, layer, step: int, side_stream=None) -> None:
+        """Called right after ``layer``'s backward.  ``side_stream`` (optional) is the stream the layer's
+        parameter gradient was issued on; an exchange that pushes per layer waits on it (and on the compute
+        stream) itself, so the compute stream is never blocked by the push."""
         if self.backend is not None and self.backend.handles_update:
-            self.backend.update_layer(layer, step)
+            self.backend.update_layer(layer, step, side_stream)
             return
         # local update: one fused launch over the whole arena once the last gradient (the first layer in
         # forward order) is ready
@@ -154,6 +156,12 @@ class ParamManager:
                     p.pack16()
         else:
             self.updater.update_arena(step, self.arena, first_chunk, nchunks, grad_scale)
+
+    def end_step(self, step: int) -> None:
+        """End of backward: join the exchange's side streams into the compute stream (required for CUDA-graph
+        capture; free in synchronous mode because the next forward needs the last push anyway)."""
+        if self.backend is not None and hasattr(self.backend, "end_step"):
+            self.backend.end_step(step)
 
     def wait_update(self, layer, step: int) -> None:
         """Called right before ``layer``'s forward: block until its parameters are fresh enough."""

@@ -82,7 +82,7 @@ class Executor:
         self._copy_stream = torch.cuda.Stream() if ctx().device.type == "cuda" else None
         env = os.environ.get("SINGA_B200_CUDA_GRAPH")
         if use_graph is None:
-            use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local",)
+            use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local", "fused", "nccl")
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
@@ -191,7 +191,7 @@ class Executor:
         reduction) is independent of its data gradient, so it is issued on a side stream and the data
         gradient — the critical path to the layers below — continues on the main stream; the parameter
         update joins the side streams.  Small GEMMs that cannot fill 148 SMs alone then overlap."""
-        split = self._side_streams is not None and self.pm.backend_name == "local"
+        split = self._side_streams is not None and self.pm.backend_name in ("local", "fused", "nccl")
         main = torch.cuda.current_stream() if split else None
         k = 0
         for layer in reversed(net.layers):
@@ -210,12 +210,14 @@ class Executor:
                 if layer is self.pm._first_param_layer:
                     for s_ in self._side_streams:
                         main.wait_stream(s_)
+                self.pm.update_param(layer, step, side)
             else:
                 layer.compute_gradient()
-            if has_params:
-                self.pm.update_param(layer, step)
+                if has_params:
+                    self.pm.update_param(layer, step)
             if layer.is_bridgedstlayer:
                 self.bridge.send_grad(layer)
+        self.pm.end_step(step)
 
     # -- one training step --------------------------------------------------------------------------------
     def train_one_batch(self, step: int) -> None:

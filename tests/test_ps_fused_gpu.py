@@ -22,7 +22,7 @@ def test_push_update_emulated(world, kind, kid):
     n = nchunks * 1024
     grads = [torch.randn(n, device=dev) for _ in range(world)]
     mirrors = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(world)]
-    ready = torch.full((world,), 5, dtype=torch.int64, device=dev)
+    ready = torch.full((world,), 2, dtype=torch.int64, device=dev)
     version = torch.zeros(world, dtype=torch.int64, device=dev)
     w = torch.randn(n, device=dev)
     h = torch.rand(n, device=dev)
@@ -30,8 +30,7 @@ def test_push_update_emulated(world, kind, kid):
     chunk_param[20:] = 1
     lr_mult = torch.tensor([1.0, 0.5], device=dev)
     wd_mult = torch.tensor([1.0, 1.0], device=dev)
-    counter = torch.zeros(1, dtype=torch.int32, device=dev)
-    step_dev = torch.tensor([4], dtype=torch.int64, device=dev)
+    scratch = torch.zeros(2, dtype=torch.int64, device=dev)
     wr, hr = w.clone(), h.clone()
     first, cnt = 8, 25       # only a sub-range is owned by "this server"
     a = PsPush()
@@ -45,10 +44,11 @@ def test_push_update_emulated(world, kind, kid):
     a.chunk_param, a.lr_mult, a.wd_mult = chunk_param.data_ptr(), lr_mult.data_ptr(), wd_mult.data_ptr()
     a.first_chunk, a.nchunks = first, cnt
     a.up = CUpdater(kid, 0.01, 0.9, 0.001, 1e-7, 0.9, 1.0 / world, None)
-    a.step_dev, a.value_add = step_dev.data_ptr(), 1
-    a.counter = counter.data_ptr()
+    a.step_dev, a.value_add = None, 0
+    a.scratch = scratch.data_ptr()
+    a.self_count = 1
     a.max_ctas = 7
-    for _ in range(2):   # two launches: the arrival counter must be back to zero after the first
+    for launch in range(2):   # two launches: the arrival counter must be back to zero after the first
         native.check(lib.sg_ps_push_update(ctypes.byref(a), torch.cuda.current_stream().cuda_stream))
         torch.cuda.synchronize()
         g = sum(grads) / world
@@ -63,8 +63,8 @@ def test_push_update_emulated(world, kind, kid):
         for m in mirrors:
             assert torch.equal(m[lo:hi], w[lo:hi].to(torch.bfloat16))
             assert float(m[:lo].abs().sum()) == 0 and float(m[hi:].abs().sum()) == 0
-        assert int(counter.item()) == 0
-        assert version.tolist() == [5] * world
+        assert scratch.tolist() == [0, launch + 1]
+        assert version.tolist() == [launch + 1] * world
 
 
 def test_flag_set_wait():
@@ -78,6 +78,26 @@ def test_flag_set_wait():
     arr = (ctypes.c_void_p * 32)()
     for i in range(3):
         arr[i] = flags[i:i + 1].data_ptr()
-    native.check(lib.sg_ps_flag_wait(arr, 3, ctypes.c_void_p(step.data_ptr()), 1, s))   # already satisfied
+    native.check(lib.sg_ps_flag_wait(arr, 3, ctypes.c_void_p(step.data_ptr()), 1, None, s))   # already satisfied
+    seq = torch.tensor([10], dtype=torch.int64, device="cuda")
+    native.check(lib.sg_ps_flag_wait(arr, 3, None, 0, ctypes.c_void_p(seq.data_ptr()), s))   # self-counting
+    for i in range(3):
+        native.check(lib.sg_ps_flag_bump(ctypes.c_void_p(flags[i:i + 1].data_ptr()),
+                                         ctypes.c_void_p(seq.data_ptr()) if i == 0 else None, s))
+    native.check(lib.sg_ps_flag_wait(arr, 3, None, 0, ctypes.c_void_p(seq.data_ptr()), s))
     torch.cuda.synchronize()
-    assert flags.tolist() == [10, 10, 10]
+    assert flags.tolist() == [11, 11, 11] and int(seq.item()) == 11
+
+
+def test_gemm_fused_wait_passes_when_version_reached():
+    from singa_b200.ops import gemm as G
+    dev = "cuda"
+    a = torch.randn(256, 128, device=dev).to(torch.bfloat16)
+    b = torch.randn(128, 256, device=dev).to(torch.bfloat16)
+    out = torch.empty(256, 256, device=dev)
+    flags = torch.tensor([3, 4], dtype=torch.int64, device=dev)
+    seq = torch.tensor([3], dtype=torch.int64, device=dev)
+    G.gemm(a, b, 256, 256, 128, b_mn=True, out32=out,
+           wait=([flags[0:1].data_ptr(), flags[1:2].data_ptr()], seq.data_ptr()))
+    torch.cuda.synchronize()
+    torch.testing.assert_close(out, a.float() @ b.float(), rtol=2e-3, atol=2e-2)
