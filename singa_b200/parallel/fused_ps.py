@@ -77,7 +77,7 @@ class FusedExchange:
         self.shards = shard_bounds(self.arena.nchunks, self.world)
         self.comm = torch.cuda.Stream()
         import os
-        self.max_ctas = int(os.environ.get("SINGA_B200_PUSH_CTAS", "96"))
+        self.max_ctas = int(os.environ.get("SINGA_B200_PUSH_CTAS", "296"))
         # per layer: push scratch (arrival counter + sequence number) and the consumer's wait sequence number;
         # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
         self.scratch = torch.zeros(max(len(self.layers), 1), 2, dtype=torch.int64, device=ctx().device)
