@@ -21,6 +21,8 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "../include/singa_b200.h"
 #include "common.h"
 
@@ -301,4 +303,76 @@ extern "C" int sg_ipc_open_handle(const void* handle64, void** out) {
 extern "C" int sg_ipc_close_handle(void* p) {
   if (p == nullptr) return 0;
   return check_cuda(cudaIpcCloseMemHandle(p), "cudaIpcCloseMemHandle");
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of the push.
+//
+// Who needs it: code that drives this library from a place where it may not create device memory — a host
+// application whose memory manager owns every byte of HBM and hands out nothing at run time, a plug-in invoked
+// from a callback in which cudaMalloc (which synchronises the device and takes driver-wide locks) is forbidden,
+// or a latency-critical loop that must never block on the allocator.  Such a caller can pass its inputs and
+// outputs but has nowhere to get the push kernel's scratch words from, so this entry point keeps them in the
+// library image: a file-scope device array, one 256-byte line per slot, SG_PS_NOALLOC_SLOTS slots (16 KB that
+// every GPU which loads the library holds until the process exits).
+//
+// Rules that follow from sharing one built-in array:
+//  * In host code the array's name is only a stand-in; the device address is obtained once per device with
+//    cudaGetSymbolAddress while that device is current.  The FIRST call on a device performs this set-up, so
+//    make that first call before starting any stream capture on that device.
+//  * The scratch keeps whatever the previous call left; the words that must start at zero are cleared on the
+//    caller's stream before each launch.
+//  * All calls with the same slot share the same words: two launches that can overlap on the GPU (different
+//    streams, or the same slot used for two layers in flight) race.  Use one slot per concurrently pushed layer.
+//  * Only the explicit flag-value mode is available (self_count must be 0): the self-counted sequence number
+//    would be part of the cleared scratch.
+// Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ------------------------------------------------------------------------------------------------
+namespace sg {
+constexpr int NOALLOC_WORDS_PER_SLOT = 32;   // 256 bytes
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[SG_PS_NOALLOC_SLOTS * NOALLOC_WORDS_PER_SLOT];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static unsigned long long* g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of the built-in scratch on the CURRENT device (looked up once per device).
+static int noalloc_scratch_base(unsigned long long** out) {
+  int dev = -1;
+  if (check_cuda(cudaGetDevice(&dev), "sg_ps_push_update_noalloc: cudaGetDevice")) return 1;
+  SG_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "sg_ps_push_update_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    if (check_cuda(cudaGetSymbolAddress(&p, g_noalloc_scratch), "sg_ps_push_update_noalloc: cudaGetSymbolAddress"))
+      return 1;
+    SG_REQUIRE(p != nullptr, "sg_ps_push_update_noalloc: built-in scratch has no device address");
+    g_noalloc_dev_ptr[dev] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return 0;
+}
+}  // namespace sg
+
+extern "C" int sg_ps_push_update_noalloc(const SgPsPush* a, int slot, void* stream) {
+  SG_REQUIRE(a != nullptr, "sg_ps_push_update_noalloc: null args");
+  SG_REQUIRE(slot >= 0 && slot < SG_PS_NOALLOC_SLOTS,
+             "sg_ps_push_update_noalloc: slot %d is outside the built-in scratch (%d slots of 256 bytes); "
+             "use sg_ps_push_update with caller-provided scratch for more layers in flight",
+             slot, SG_PS_NOALLOC_SLOTS);
+  SG_REQUIRE(a->self_count == 0,
+             "sg_ps_push_update_noalloc: self-counted flag values are not available (the scratch is cleared per call); "
+             "pass the flag value through step_dev / value_add");
+  if (a->nchunks <= 0) return 0;
+  unsigned long long* base = nullptr;
+  if (int rc = noalloc_scratch_base(&base)) return rc;
+  unsigned long long* mine = base + static_cast<long long>(slot) * NOALLOC_WORDS_PER_SLOT;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  // arrival counter (and the unused sequence word) must read zero when the kernel starts
+  if (check_cuda(cudaMemsetAsync(mine, 0, 2 * sizeof(unsigned long long), s), "sg_ps_push_update_noalloc: clear scratch"))
+    return 1;
+  SgPsPush b = *a;
+  b.scratch = mine;
+  b.self_count = 0;
+  return sg_ps_push_update(&b, stream);
 }

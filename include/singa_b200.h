@@ -181,6 +181,17 @@ typedef struct SgPsPush {
   int max_ctas;                                     /* CTA budget (0 = 64) so backward keeps the SMs */
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
+/* Allocation-free variant of sg_ps_push_update — no counterpart in the reference (its parameter server keeps
+ * all state in host objects).  For callers that cannot create device memory (a host application whose memory
+ * manager owns all of HBM, a callback where cudaMalloc is forbidden, a loop that must never block on the
+ * allocator): the kernel's scratch words live in a device array built into the library, SG_PS_NOALLOC_SLOTS
+ * slots of 256 bytes (16 KB per GPU for the life of the process).  `slot` selects the words; slots beyond the
+ * maximum are rejected.  args->scratch is ignored; args->self_count must be 0 (explicit flag value).  The
+ * first call on a device looks up the array's device address — make it before any stream capture.  The
+ * scratch is cleared on `stream` before each launch; launches that share a slot and may overlap on the GPU
+ * race.  Calls no cudaMalloc/cudaFree or other allocating routine. */
+#define SG_PS_NOALLOC_SLOTS 64
+int sg_ps_push_update_noalloc(const SgPsPush* args, int slot, void* stream);
 /* release-store / acquire-wait on 64-bit flags in (peer) device memory */
 int sg_ps_flag_set(unsigned long long* flag, const long long* step_dev, long long value_add, void* stream);
 /* flag += 1 (single writer); local_seq (optional, local memory) += 1 as well — the per-layer sequence number

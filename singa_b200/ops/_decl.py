@@ -33,6 +33,7 @@ SIGNATURES = {
     "sg_easgd_sync": [vp, vp, i64, f32, vp, vp],
     "sg_randomsync": [vp, vp, vp, i64, f32, u64, vp, vp, vp],
     "sg_ps_push_update": [vp, vp],
+    "sg_ps_push_update_noalloc": [vp, i32, vp],
     "sg_ps_flag_set": [vp, vp, i64, vp],
     "sg_ps_flag_wait": [vp, i32, vp, i64, vp, vp],
     "sg_ps_flag_bump": [vp, vp, vp],
