@@ -207,6 +207,23 @@ int sg_ipc_get_handle(void* p, void* handle64);
 int sg_ipc_open_handle(const void* handle64, void** out);
 int sg_ipc_close_handle(void* p);
 
+/* ------------------------------------------------------------------------------------------------
+ * Shard record file (host code; include/utils/shard.h:33-142, src/utils/shard.cc:24-206):
+ * <folder>/shard.dat = [u64 keylen][key][u64 vallen][val]...; mode 'r' read, 'c' create, 'a' append (recovers
+ * from a torn tail, ignores duplicate keys).  sg_shard_read_image_batch decodes singa.Record image records
+ * straight into batch buffers (ShardDataLayer, src/worker/layer.cc:646-661).
+ * ---------------------------------------------------------------------------------------------- */
+void* sg_shard_open(const char* folder, char mode, long long capacity);
+void sg_shard_close(void* shard);
+int sg_shard_insert(void* shard, const void* key, long long klen, const void* val, long long vlen);
+int sg_shard_flush(void* shard);
+int sg_shard_next(void* shard);
+const void* sg_shard_key(void* shard, long long* len);
+const void* sg_shard_val(void* shard, long long* len);
+void sg_shard_seek_to_first(void* shard);
+long long sg_shard_count(void* shard);
+int sg_shard_read_image_batch(void* shard, void* pixels_u8, int* labels, int batch, long long dim);
+
 #ifdef __cplusplus
 }
 #endif
