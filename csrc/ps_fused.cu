@@ -45,7 +45,22 @@ struct PushParams {
   unsigned long long* scratch;                       // [0] CTA arrival counter (zero between launches)
                                                      // [1] launch sequence number (self-counting flag value)
   int self_count;
+  const float* grad_mc;                              // NVLS: multicast address of the gradient arenas (or null)
+  __nv_bfloat16* w16_mc;                             // NVLS: multicast address of the bf16 mirrors (or null)
 };
+
+// NVLS (NVLink SHARP) accessors: one instruction reduces / broadcasts across every GPU bound to the multicast
+// object, inside the NVSwitch — the reduce-scatter costs each GPU 1/world of the bytes the peer-load version pulls.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};"
+               ::"l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)) : "memory");
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
   unsigned long long v;
@@ -133,7 +148,13 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
       idx[k] = (p.first_chunk + c) * CHUNK + threadIdx.x * 4;
       g[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    // 2. reduce the peers' gradients (128-bit loads; remote ranks go over NVLink)
+    // 2. reduce the peers' gradients: in the switch (NVLS) when a multicast mapping exists, else with
+    //    128-bit peer loads (remote ranks go over NVLink)
+    if (p.grad_mc != nullptr) {
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (pid[k] >= 0) g[k] = multimem_ld_reduce_add(p.grad_mc + idx[k]);
+    } else
 #pragma unroll
     for (int r = 0; r < MAX_WORLD; ++r) {
       if (r < p.world) {
@@ -170,9 +191,13 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
       uint2 o;
       o.x = *reinterpret_cast<const uint32_t*>(&a);
       o.y = *reinterpret_cast<const uint32_t*>(&b);
+      if (p.w16_mc != nullptr) {
+        multimem_st_b64(p.w16_mc + i, o);
+      } else {
 #pragma unroll
-      for (int r = 0; r < MAX_WORLD; ++r)
-        if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+        for (int r = 0; r < MAX_WORLD; ++r)
+          if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+      }
     }
   }
   // 5. publish: last CTA to arrive bumps the version flag on every rank
@@ -244,6 +269,7 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   p.delta = a->up.delta; p.rho = a->up.rho; p.grad_scale = a->up.grad_scale; p.lr_dev = a->up.lr_dev;
   p.step_dev = a->step_dev; p.value_add = a->value_add;
   p.scratch = a->scratch; p.self_count = a->self_count;
+  p.grad_mc = a->grad_mc; p.w16_mc = reinterpret_cast<__nv_bfloat16*>(a->w16_mc);
   long long grid = (a->nchunks + 1) / 2;
   const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward
   if (grid > cap) grid = cap;

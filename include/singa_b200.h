@@ -179,6 +179,10 @@ typedef struct SgPsPush {
   int self_count;                                   /* 1: flag value = scratch[1] + 1 (n-th launch waits for ready >= n,
                                                        publishes version = n); independent of any step scalar */
   int max_ctas;                                     /* CTA budget (0 = 64) so backward keeps the SMs */
+  const float* grad_mc;                             /* optional NVLS multicast address of all ranks' gradient arenas:
+                                                       the reduction then happens inside the NVSwitch (multimem.ld_reduce) */
+  void* w16_mc;                                     /* optional NVLS multicast address of all ranks' bf16 mirrors:
+                                                       one multimem.st broadcasts the fresh weights */
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
 /* Allocation-free variant of sg_ps_push_update — no counterpart in the reference (its parameter server keeps

@@ -47,6 +47,8 @@ class PsPush(ctypes.Structure):
         ("scratch", ctypes.c_void_p),
         ("self_count", ctypes.c_int),
         ("max_ctas", ctypes.c_int),
+        ("grad_mc", ctypes.c_void_p),
+        ("w16_mc", ctypes.c_void_p),
     ]
 
 
@@ -78,6 +80,9 @@ class FusedExchange:
         self.comm = torch.cuda.Stream()
         import os
         self.max_ctas = int(os.environ.get("SINGA_B200_PUSH_CTAS", "296"))
+        # NVLS: in-switch reduction / broadcast when the heap has a multicast mapping (torch symmetric memory)
+        self.use_nvls = bool(getattr(heap, "mc_ptr", None)) and heap.mc_ptr("grad") != 0 and \
+            os.environ.get("SINGA_B200_NVLS", "1") != "0"
         # per layer: push scratch (arrival counter + sequence number) and the consumer's wait sequence number;
         # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
         self.scratch = torch.zeros(max(len(self.layers), 1), 2, dtype=torch.int64, device=ctx().device)
@@ -148,6 +153,9 @@ class FusedExchange:
         a.scratch = self.scratch[i].data_ptr()
         a.self_count = 1
         a.max_ctas = self.max_ctas
+        if self.use_nvls:
+            a.grad_mc = self.heap.mc_ptr("grad")
+            a.w16_mc = self.heap.mc_ptr("data16")
         native.check(self.lib.sg_ps_push_update(ctypes.byref(a), self.comm.cuda_stream), "sg_ps_push_update")
         native.count_launch()
         self.launches += 1

@@ -22,13 +22,15 @@ class NcclExchange:
         self.lo = self.rank * self.per * 1024
         self.hi = self.lo + self.per * 1024
         self.last_layer = pm._first_param_layer   # its gradient is the last one produced by backward
+        self.gshard = torch.empty(self.per * 1024, dtype=torch.float32, device=self.arena.grad.device)
 
     def update_layer(self, layer, step: int, side_stream=None) -> None:
         if layer is not self.last_layer:
             return
         ar = self.arena
         if self.world > 1:
-            dist.reduce_scatter_tensor(ar.grad[self.lo:self.hi], ar.grad, op=dist.ReduceOp.AVG)
+            dist.reduce_scatter_tensor(self.gshard, ar.grad, op=dist.ReduceOp.AVG)
+            ar.grad[self.lo:self.hi].copy_(self.gshard)
         self.pm._update_range(self.rank * self.per, self.per, step)
         if self.world > 1:
             if ar.data16 is not None:

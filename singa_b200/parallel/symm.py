@@ -98,3 +98,66 @@ class SymmetricHeap:
 
     def close(self) -> None:
         self.buf.close()
+
+
+class TorchSymmetricHeap:
+    """Same interface as :class:`SymmetricHeap`, backed by ``torch.distributed._symmetric_memory`` — the
+    allocation / handle exchange plumbing of PyTorch — which additionally binds the buffer to an NVLS multicast
+    object when the fabric supports it.  ``mc_ptr(name)`` is the multicast address of a region (0 when
+    unavailable); kernels use it with ``multimem.ld_reduce`` / ``multimem.st``."""
+
+    def __init__(self, regions, rank: int, world: int, device):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.offsets = {}
+        off = 0
+        for name, nbytes in regions:
+            self.offsets[name] = (off, nbytes)
+            off += (nbytes + 255) // 256 * 256
+        self.rank, self.world, self.device = rank, world, device
+        self.t = symm_mem.empty(max(off, 256), dtype=torch.uint8, device=device)
+        self.t.zero_()
+        self.hdl = symm_mem.rendezvous(self.t, dist.group.WORLD)
+        self.peer_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        mc = 0
+        try:
+            if self.hdl.has_multicast_support(device.type if hasattr(device, "type") else "cuda", device.index or 0) \
+                    if callable(getattr(self.hdl, "has_multicast_support", None)) else True:
+                mc = int(self.hdl.multicast_ptr)
+        except Exception:  # noqa: BLE001
+            try:
+                mc = int(self.hdl.multicast_ptr)
+            except Exception:  # noqa: BLE001
+                mc = 0
+        self.multicast_base = mc
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def tensor(self, name: str, dtype: torch.dtype, rank: Optional[int] = None) -> torch.Tensor:
+        off, nbytes = self.offsets[name]
+        r = self.rank if rank is None else rank
+        if r == self.rank:
+            return self.t[off:off + nbytes].view(dtype)
+        return wrap_pointer(self.peer_ptrs[r] + off, nbytes, dtype, self.device, keepalive=self)
+
+    def ptr(self, name: str, rank: int, byte_offset: int = 0) -> int:
+        return self.peer_ptrs[rank] + self.offsets[name][0] + byte_offset
+
+    def mc_ptr(self, name: str) -> int:
+        return self.multicast_base + self.offsets[name][0] if self.multicast_base else 0
+
+    def close(self) -> None:
+        self.hdl = None
+        self.t = None
+
+
+def make_heap(regions, rank: int, world: int, device):
+    """Prefer torch symmetric memory (NVLS multicast) for multi-rank jobs; CUDA-IPC heap otherwise."""
+    import os
+    kind = os.environ.get("SINGA_B200_HEAP", "symm" if world > 1 else "ipc")
+    if kind == "symm" and world > 1:
+        try:
+            return TorchSymmetricHeap(regions, rank, world, device)
+        except Exception as e:  # noqa: BLE001
+            import logging
+            logging.getLogger("singa").error("torch symmetric memory unavailable (%s); using the CUDA-IPC heap", e)
+    return SymmetricHeap(regions, rank, world, device)

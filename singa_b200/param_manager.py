@@ -55,11 +55,11 @@ class ParamManager:
         if backend == "fused":
             # gradient arena, bf16 mirror and flags live in ONE peer-mapped allocation per rank
             from .parallel.fused_ps import symmetric_regions
-            from .parallel.symm import SymmetricHeap
+            from .parallel.symm import make_heap
             probe = ParamArena.layout_total(owners, pad_chunks_to=world)
             nlayers = sum(1 for l in net.layers if l.get_params())
-            heap = SymmetricHeap(symmetric_regions(probe, nlayers, world), dist.get_rank() if world > 1 else 0,
-                                 world, ctx().device)
+            heap = make_heap(symmetric_regions(probe, nlayers, world), dist.get_rank() if world > 1 else 0,
+                             world, ctx().device)
 
             def allocator(name, n, dt, heap=heap):
                 if name in ("grad", "data16"):

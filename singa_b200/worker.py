@@ -258,9 +258,16 @@ class Executor:
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         n0 = native.launch_count
-        with torch.cuda.graph(g):
-            self.forward(self.train_net, step, True, skip_inputs=True)
-            self.backward(self.train_net, step)
+        try:
+            with torch.cuda.graph(g):
+                self.forward(self.train_net, step, True, skip_inputs=True)
+                self.backward(self.train_net, step)
+        except Exception as e:  # noqa: BLE001 - e.g. a library op that cannot be captured: run eagerly instead
+            log.error("CUDA-graph capture failed (%s); continuing without graphs", str(e).splitlines()[0])
+            torch.cuda.synchronize()
+            self.use_graph = False
+            native.launch_count = n0
+            return
         self.graph_kernel_count = native.launch_count - n0
         native.launch_count = n0          # capture records launches, it does not execute them
         self._graph = g
