@@ -233,9 +233,9 @@ struct WaitParams {
   const unsigned long long* seq;   // self-counting: wait for flags >= *seq (sg_ps_flag_bump advances it)
 };
 __global__ void ps_flag_wait_kernel(const WaitParams p) {
-  const unsigned long long target = p.seq
-      ? *p.seq
-      : static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  long long explicit_target = (p.step_dev ? *p.step_dev : 0) + p.value_add;
+  if (explicit_target < 0) explicit_target = 0;   // e.g. "step - staleness" during the first steps
+  const unsigned long long target = p.seq ? *p.seq : static_cast<unsigned long long>(explicit_target);
   if (threadIdx.x < p.n) wait_flag_ge(p.flags[threadIdx.x], target);
 }
 

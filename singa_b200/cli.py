@@ -72,9 +72,11 @@ def main(argv=None) -> int:
         torch.cuda.set_device(torch.device(dev))
     device.set_context(dev, args.backend or None)
     push_pull = args.push_pull or (pcluster.push_pull if cluster.nservers > 0 else "")
-    if cluster.nservers > 0 and not dev.startswith("cuda") and push_pull in ("fused", "nccl", ""):
+    if cluster.nservers > 0 and dev.startswith("cuda") and not cluster.synchronous and push_pull in ("", "fused"):
+        push_pull = "async" if not args.push_pull else push_pull    # asynchronous groups are the reference's default mode
+    if cluster.nservers > 0 and not dev.startswith("cuda") and push_pull in ("fused", "nccl", "async", ""):
         push_pull = "zmq"
-    if push_pull in ("fused", "nccl") and cluster.nworkers > 1:
+    if push_pull in ("fused", "nccl", "async") and cluster.nworkers > 1:
         import torch.distributed as dist
         if not dist.is_initialized():
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

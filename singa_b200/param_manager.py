@@ -11,6 +11,8 @@ Exchange backends:
                  ``sync_frequency`` steps; CPU plumbing config and cross-host control.
   * ``nccl``   — synchronous data parallel with NCCL reduce-scatter -> shard update -> all-gather
                  (the library baseline).
+  * ``async``  — asynchronous worker groups with bounded staleness: local updates + EASGD / RandomSync kernels
+                 on peer-mapped server shards, device-side progress counters (parallel/async_ps.py).
   * ``fused``  — the B200 product path: reduce-scatter + updater + broadcast in ONE kernel over NVSwitch peer
                  memory with device-side version counters (singa_b200/parallel/fused_ps.py).
 """
@@ -65,9 +67,15 @@ class ParamManager:
                 if name in ("grad", "data16"):
                     return heap.tensor(name, dt)
                 return None
+        if backend == "async":
+            from .parallel.async_ps import async_regions
+            from .parallel.symm import make_heap
+            probe = ParamArena.layout_total(owners, pad_chunks_to=world)
+            heap = make_heap(async_regions(probe, world), dist.get_rank() if world > 1 else 0, world, ctx().device)
         self.arena = ParamArena(owners, with_update=self.updater.needs_update,
                                 with_snapshot=(self.param_type == "RandomSync" and nservers > 0),
-                                allocator=allocator, pad_chunks_to=world if backend in ("fused", "nccl") else 1)
+                                allocator=allocator,
+                                pad_chunks_to=world if backend in ("fused", "nccl", "async") else 1)
         self.paramid2version: Dict[int, int] = {p.id: 0 for p in net.params}
         self.layer_ranges = {}
         for layer in net.layers:
@@ -87,6 +95,9 @@ class ParamManager:
         elif backend == "fused":
             from .parallel.fused_ps import FusedExchange
             self.backend = FusedExchange(self, heap)
+        elif backend == "async":
+            from .parallel.async_ps import AsyncExchange
+            self.backend = AsyncExchange(self, heap)
         elif backend != "local":
             raise ValueError(f"unknown exchange backend {backend!r}")
         self.use_device_lr = ctx().is_native
@@ -95,7 +106,11 @@ class ParamManager:
     def init_params(self) -> None:
         for p in self.arena.params:
             p.init(self.seed)
+        if self.arena.snapshot is not None:
+            self.arena.snapshot.copy_(self.arena.data)
         self.arena.sync_mirror()
+        if self.backend is not None and hasattr(self.backend, "seed_center"):
+            self.backend.seed_center()
 
     def sync_config(self, compute_time: float) -> None:
         """RandomSync sizing: ratio = bandwidth * nservers / (modelMB * nworkers / compute_time), <= 1
@@ -123,6 +138,8 @@ class ParamManager:
         self.lr = self.updater.learning_rate(step)
         if self.use_device_lr:
             set_step_state(step, self.lr)
+        if self.backend is not None and hasattr(self.backend, "begin_step"):
+            self.backend.begin_step(step)
 
     def update_param(self, layer, step: int, side_stream=None) -> None:
         """Called right after ``layer``'s backward.  ``side_stream`` (optional) is the stream the layer's

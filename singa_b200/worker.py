@@ -83,6 +83,8 @@ class Executor:
         env = os.environ.get("SINGA_B200_CUDA_GRAPH")
         if use_graph is None:
             use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local", "fused", "nccl")
+        if pm.backend_name in ("async", "zmq"):
+            use_graph = False        # sync steps differ from plain steps: run eagerly
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3

@@ -1,0 +1,96 @@
+"""Multi-GPU check of asynchronous worker groups with bounded staleness (run under torch.distributed.run).
+
+Every rank trains with local updates + EASGD (or RandomSync) against the peer-memory server shards; rank 1 is
+artificially slowed down (fault injection: extra host sleep per step).  Checks: (1) the fast group never runs more
+than `staleness` steps ahead of the slow one (sampled through the device progress counters), (2) the loss falls,
+(3) the groups' weights stay close to the center (elastic force works).
+"""
+import os
+import sys
+import time
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from singa_b200 import device
+    from singa_b200.cluster import Cluster
+    from singa_b200.models import configs
+    from singa_b200.proto import schema as S
+    from singa_b200.worker import Worker
+    device.set_context(f"cuda:{local}", "native")
+    ok = True
+    for param_type in ("Elastic", "RandomSync"):
+        model = configs.mnist_mlp(batch=128, hidden=(256, 128))
+        model.display_frequency = 0
+        model.prefetch = False
+        u = model.updater
+        u.base_learning_rate, u.sync_frequency, u.warmup_steps, u.moving_rate = 0.05, 2, 2, 0.5
+        u.param_type = param_type
+        cp = S.ClusterProto()
+        cp.nworkers = cp.nservers = world
+        cp.workspace = "/tmp/singa_b200_async"
+        cp.staleness = 3
+        Cluster.reset()
+        cluster = Cluster.get(cp, "", rank)
+        w = Worker(cluster, backend="async")
+        w.build(model)
+        w.pm.sample_ratio = 0.5
+        ex, be = w.executor, w.pm.backend
+        steps, worst_lead = 60, 0
+        first = last = None
+        for step in range(steps):
+            ex.ticks += 1
+            ex.train_one_batch(step)
+            if rank == 1:
+                time.sleep(0.003)                       # the slow group
+            if step % 5 == 4:
+                prog = be.progress()
+                worst_lead = max(worst_lead, max(prog) - min(prog))
+            if step == 9 or step == steps - 1:
+                torch.cuda.synchronize()
+                m = w.train_net.losslayers[0].metric
+                val = float(m[0]) / (10 if step == 9 else steps - 10)
+                m.zero_()
+                if step == 9:
+                    first = val
+                else:
+                    last = val
+        torch.cuda.synchronize()
+        dist.barrier()
+        lo, hi = be.shards[rank]
+        dev_from_center = 0.0
+        for o, (a, b) in enumerate(be.shards):
+            if b > a:
+                c = be.center_peer[o][a:b]
+                dev_from_center = max(dev_from_center,
+                                      float((w.pm.arena.data[a:b] - c).norm() / (c.norm() + 1e-12)))
+        t = torch.tensor([worst_lead, dev_from_center, first, last], device="cuda", dtype=torch.float64)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        if rank == 0:
+            lead = max(float(x[0]) for x in allt)
+            devc = max(float(x[1]) for x in allt)
+            f0, l0 = float(allt[0][2]), float(allt[0][3])
+            good = lead <= cp.staleness + 1 and l0 < f0 and devc < 0.5 and be.nsync > 0
+            ok = ok and good
+            print(f"{'PASS' if good else 'FAIL'} async {param_type}: world={world} staleness={cp.staleness} "
+                  f"max observed lead={lead:.0f} steps, loss {f0:.4f} -> {l0:.4f}, "
+                  f"max relative distance to the center {devc:.3f}, syncs={be.nsync}")
+        w.pm.finish()
+        dist.barrier()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    sys.stdout.flush()
+    os._exit(0 if int(flag.item()) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
