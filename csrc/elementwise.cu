@@ -125,7 +125,8 @@ __global__ void colsum_kernel(const T* __restrict__ x, long long ld, int rows, i
 // dst[r][c] (bf16, row stride ldd, padding columns zeroed) = src[r][pc] (fp32, row stride lds) where
 // pc = c for a plain cast, or for conv weights (perm_c = C, perm_kk = k*k): destination column
 // j = kk_idx*C + c reads source column c*kk + kk_idx.
-__global__ void cast_pack_kernel(const float* __restrict__ src, long long lds,
+template <typename S>
+__global__ void cast_pack_kernel(const S* __restrict__ src, long long lds,
                                  __nv_bfloat16* __restrict__ dst, long long ldd, int rows, int cols,
                                  int perm_c, int perm_kk) {
   const long long total = static_cast<long long>(rows) * ldd;
@@ -136,7 +137,7 @@ __global__ void cast_pack_kernel(const float* __restrict__ src, long long lds,
     float v = 0.f;
     if (c < cols) {
       const int sc = perm_c > 0 ? (c % perm_c) * perm_kk + (c / perm_c) : c;
-      v = src[static_cast<long long>(r) * lds + sc];
+      v = to_float(src[static_cast<long long>(r) * lds + sc]);
     }
     dst[i] = __float2bfloat16_rn(v);
   }
@@ -343,9 +344,24 @@ extern "C" int sg_cast_pack(const float* src, long long lds, void* dst, long lon
   SG_REQUIRE(ldd >= cols && lds >= cols, "sg_cast_pack: leading dimensions too small");
   SG_REQUIRE(perm_c == 0 || perm_c * perm_kk == cols, "sg_cast_pack: perm_c*perm_kk must equal cols");
   const long long total = static_cast<long long>(rows) * ldd;
-  cast_pack_kernel<<<ew_grid(total, 256), 256, 0, s>>>(src, lds, (__nv_bfloat16*)dst, ldd, rows, cols,
-                                                       perm_c, perm_kk);
+  cast_pack_kernel<float><<<ew_grid(total, 256), 256, 0, s>>>(src, lds, (__nv_bfloat16*)dst, ldd, rows, cols,
+                                                              perm_c, perm_kk);
   SG_CHECK_LAUNCH("cast_pack");
+  return 0;
+}
+
+// Same re-layout from a bf16 source (the parameter server's weight mirror) — used by ranks that do not hold the
+// fp32 master copy of a convolution weight.
+extern "C" int sg_repack_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
+                              int perm_c, int perm_kk, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || cols <= 0) return 0;
+  SG_REQUIRE(ldd >= cols && lds >= cols, "sg_repack_bf16: leading dimensions too small");
+  SG_REQUIRE(perm_c == 0 || perm_c * perm_kk == cols, "sg_repack_bf16: perm_c*perm_kk must equal cols");
+  const long long total = static_cast<long long>(rows) * ldd;
+  cast_pack_kernel<__nv_bfloat16><<<ew_grid(total, 256), 256, 0, s>>>((const __nv_bfloat16*)src, lds, (__nv_bfloat16*)dst,
+                                                                      ldd, rows, cols, perm_c, perm_kk);
+  SG_CHECK_LAUNCH("repack_bf16");
   return 0;
 }
 

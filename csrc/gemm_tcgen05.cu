@@ -47,7 +47,7 @@ struct GemmParams {
   int M, N, K;
   float* d32; long long ldd32;
   __nv_bfloat16* d16; long long ldd16;
-  const float* bias;
+  const void* bias; int bias_bf16;
   int act, grad_act;
   const void* aux; long long ldaux; int aux_bf16;
   int accumulate;
@@ -251,7 +251,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         if (p.bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (j < nvalid) v[j] += __ldg(p.bias + nb + j);
+            if (j < nvalid)
+              v[j] += p.bias_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[nb + j])
+                                  : __ldg(reinterpret_cast<const float*>(p.bias) + nb + j);
         }
         if (p.act != SG_ACT_NONE) {
 #pragma unroll
@@ -486,7 +488,7 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   p.M = M; p.N = N; p.K = K;
   p.d32 = ep->d32; p.ldd32 = ep->ldd32;
   p.d16 = reinterpret_cast<__nv_bfloat16*>(ep->d16); p.ldd16 = ep->ldd16;
-  p.bias = ep->bias; p.act = ep->act; p.grad_act = ep->grad_act;
+  p.bias = ep->bias; p.bias_bf16 = ep->bias_bf16; p.act = ep->act; p.grad_act = ep->grad_act;
   p.aux = ep->aux; p.ldaux = ep->ldaux; p.aux_bf16 = ep->aux_bf16;
   p.accumulate = ep->accumulate; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
   SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 8, "sg_gemm_bf16: at most 8 wait flags");

@@ -40,7 +40,7 @@ typedef struct SgGemmEpilogue {
   long long ldd32;
   void* d16;             /* optional bf16 output [M][ldd16] */
   long long ldd16;
-  const float* bias;     /* optional [N] */
+  const void* bias;      /* optional [N], fp32 (or bf16 when bias_bf16) */
   int act;               /* SG_ACT_* applied to acc+bias */
   int grad_act;          /* SG_ACT_*: multiply by the activation derivative evaluated from aux (= activation OUTPUT) */
   const void* aux;       /* [M][ldaux], bf16 if aux_bf16 else fp32 */
@@ -55,6 +55,7 @@ typedef struct SgGemmEpilogue {
   const unsigned long long* wait_flags[8];
   int nwait;
   const unsigned long long* wait_seq;
+  int bias_bf16;         /* bias points at bf16 values (the parameter server's weight mirror) instead of fp32 */
 } SgGemmEpilogue;
 
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
@@ -82,6 +83,9 @@ int sg_colsum(const void* x, long long ld, int rows, int cols, float* out, int a
  * (c,ky,kx) -> (ky,kx,c) given perm_c = C, perm_kk = k*k. */
 int sg_cast_pack(const float* src, long long lds, void* dst, long long ldd, int rows, int cols,
                  int perm_c, int perm_kk, void* stream);
+/* the same re-layout from a bf16 source (a rank that only holds the parameter server's bf16 weight mirror) */
+int sg_repack_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, int perm_c,
+                   int perm_kk, void* stream);
 int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
 /* bf16 [rows][lds] -> bf16 [rows][ldd], padding columns zeroed (re-striding to a TMA-legal leading dimension). */
 int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, void* stream);

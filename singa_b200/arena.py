@@ -113,8 +113,10 @@ class ParamArena:
                 p.update = view(self.update, p.update)
             if self.snapshot is not None:
                 p.snapshot = view(self.snapshot, p.snapshot)
-            if self.data16 is not None and p.pack16 is None:
-                p.data16 = shaped(self.data16)   # GEMM operand = the arena's bf16 mirror
+            if self.data16 is not None:
+                p.mirror16 = shaped(self.data16)     # always: the parameter server broadcasts into the mirror
+                if p.pack16 is None:
+                    p.data16 = p.mirror16            # GEMM operand = the arena's bf16 mirror
         self.sync_mirror()
 
     def view16(self, p: Param) -> torch.Tensor:

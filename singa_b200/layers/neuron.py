@@ -60,6 +60,14 @@ workspace = _Workspace()
 class NeuronLayer(Layer):
     """Shared fusion plumbing."""
 
+    def _bias_operand(self):
+        """Bias for the GEMM epilogue: the fp32 master value, or — when a sharded parameter server keeps the
+        master copy elsewhere — this rank's bf16 mirror, which is what the servers broadcast into."""
+        b = self.bias if self.bias.is_owner else self.bias.owner
+        if getattr(b, "use_mirror", False):
+            return b.mirror16
+        return b.data
+
     def __init__(self):
         super().__init__()
         self.fused_act = ACT_NONE          # activation applied in this layer's forward epilogue
@@ -180,7 +188,7 @@ class InnerProductLayer(NeuronLayer):
             out32 = self.data if self.data.dtype == torch.float32 else None
             out16 = self.data if self.data.dtype == torch.bfloat16 else None
             K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, out32=out32,
-                   out16=out16, bias=self.bias.data if self.bias_term else None, act=self.fused_act,
+                   out16=out16, bias=self._bias_operand() if self.bias_term else None, act=self.fused_act,
                    wait=self.pull_wait if training else None)
             self._x_saved = x
         else:
@@ -309,14 +317,20 @@ class ConvolutionLayer(NeuronLayer):
         kk = self.kernel * self.kernel
 
         def pack(w=self.weight, dst=self.w16_packed):
-            _K().cast_pack(w.data, K_, dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
+            # from the fp32 master copy, or — on a rank that is not this parameter's server — from the bf16
+            # mirror the parameter server broadcasts into
+            if getattr(w, "pack_from_mirror", False):
+                m = w.mirror16
+                _K().repack_bf16(m, m.stride(0), dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
+            else:
+                _K().cast_pack(w.data, K_, dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
         self.weight.pack16 = pack
         # scratch: dcol [P][Kpad] in the workspace shared by all conv layers (used and consumed within one
         # data-gradient step); a padded copy of dy [P][Fpad] per layer when F % 8 != 0 (read by both gradient GEMMs)
         self.ws_bytes = self.P * self.Kpad * 2
         workspace.reserve(self.ws_bytes)
-        self.dy_pad = torch.zeros(self.P, self.Fpad, dtype=torch.bfloat16, device=dev) if F_ % 8 else None
-        self._dy_op = None
+        self.dy_pad = [torch.zeros(self.P, self.Fpad, dtype=torch.bfloat16, device=dev) for _ in range(2)] \
+            if F_ % 8 else None
 
     def get_params(self):
         return [self.weight, self.bias] if self.bias_term else [self.weight]
@@ -345,7 +359,7 @@ class ConvolutionLayer(NeuronLayer):
             y2d = self.data.permute(0, 2, 3, 1).reshape(self.P, self.num_filters)   # view of NHWC storage
             assert y2d.data_ptr() == self.data.data_ptr()
             K.gemm(col, self._w16(), self.P, self.num_filters, self.col_height,
-                   out16=y2d, bias=self.bias.data if self.bias_term else None, act=self.fused_act)
+                   out16=y2d, bias=self._bias_operand() if self.bias_term else None, act=self.fused_act)
             self._col_saved = col
         else:
             x = src.float()
@@ -366,13 +380,14 @@ class ConvolutionLayer(NeuronLayer):
         self.compute_param_gradient()
         self.compute_data_gradient()
 
-    def _dy_operand(self):
-        """dY as a [P][F] bf16 matrix with a TMA-legal row stride (padded copy in the workspace if F % 8)."""
+    def _dy_operand(self, which: int = 0):
+        """dY as a [P][F] bf16 matrix with a TMA-legal row stride (a padded copy when F % 8).  The parameter
+        and the data gradient run on different streams, so each has its own padded buffer (``which``)."""
         K = _K()
         F_, P = self.num_filters, self.P
         dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
         if F_ % 8:
-            dyp = self.dy_pad
+            dyp = self.dy_pad[which]
             K.copy2d_bf16(dy2d, F_, dyp, self.Fpad, P, F_)
             return dy2d, dyp[:, :F_]
         return dy2d, dy2d
@@ -382,8 +397,7 @@ class ConvolutionLayer(NeuronLayer):
             K = _K()
             F_, K_, P = self.num_filters, self.col_height, self.P
             accumulate = getattr(self, "_accumulate_wgrad", False)
-            dy2d, dy_op = self._dy_operand()
-            self._dy_op = dy_op
+            dy2d, dy_op = self._dy_operand(0)
             if self.bias_term:
                 K.colsum(dy2d, P, F_, F_, self.bias.grad, accumulate=accumulate)
             kk = self.kernel * self.kernel
@@ -406,7 +420,7 @@ class ConvolutionLayer(NeuronLayer):
             K = _K()
             F_, K_, P = self.num_filters, self.col_height, self.P
             N, H, W, C = self.batchsize, self.height, self.width, self.channels
-            dy_op = self._dy_operand()[1] if not hasattr(self, "_dy_op") or self._dy_op is None else self._dy_op
+            dy_op = self._dy_operand(1)[1]
             if self.pointwise:
                 d2 = dst.permute(0, 2, 3, 1).reshape(P, C)
                 a2 = aux.permute(0, 2, 3, 1).reshape(P, C) if aux is not None else None

@@ -15,6 +15,7 @@ SIGNATURES = {
     "sg_dropout": [vp, vp, i64, f32, u64, vp, i32, vp],
     "sg_colsum": [vp, i64, i32, i32, vp, i32, i32, vp],
     "sg_cast_pack": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
+    "sg_repack_bf16": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
     "sg_convert": [vp, i32, vp, i32, i64, vp],
     "sg_copy2d_bf16": [vp, i64, vp, i64, i32, i32, vp],
     "sg_transpose_planes": [vp, i32, vp, i32, i32, i32, i32, vp],

@@ -74,8 +74,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
         assert out16.dtype == torch.bfloat16 and out16.stride(-1) == 1
         ep.d16, ep.ldd16 = out16.data_ptr(), out16.stride(0)
     if bias is not None:
-        assert bias.dtype == torch.float32 and bias.is_contiguous()
+        assert bias.dtype in (torch.float32, torch.bfloat16) and bias.is_contiguous()
         ep.bias = bias.data_ptr()
+        ep.bias_bf16 = 1 if bias.dtype == torch.bfloat16 else 0
     ep.act, ep.grad_act = act, grad_act
     if grad_act != ACT_NONE:
         assert aux is not None and aux.stride(-1) == 1

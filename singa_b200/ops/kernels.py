@@ -50,6 +50,10 @@ def cast_pack(src, lds, dst, ldd, rows, cols, perm=(0, 0)):
     _call("sg_cast_pack", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols, perm[0], perm[1])
 
 
+def repack_bf16(src, lds, dst, ldd, rows, cols, perm=(0, 0)):
+    _call("sg_repack_bf16", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols, perm[0], perm[1])
+
+
 def convert(src, dst):
     _call("sg_convert", src.data_ptr(), _bf(src), dst.data_ptr(), _bf(dst), src.numel())
 

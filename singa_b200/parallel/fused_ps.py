@@ -89,6 +89,7 @@ class FusedExchange:
         # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
         self.scratch = torch.zeros(max(len(self.layers), 1), 2, dtype=torch.int64, device=ctx().device)
         self.wait_seq = torch.zeros(max(len(self.layers), 1), dtype=torch.int64, device=ctx().device)
+        self.lr_dev = step_state()["lr"]
         # Ownership is striped PER LAYER: layer L's chunk range is cut into `world` contiguous pieces and rank r
         # serves piece r, so every layer's push is spread over all GPUs (the last layers of backward would
         # otherwise all land on the rank owning the head of the arena).
@@ -115,7 +116,13 @@ class FusedExchange:
             if getattr(l, "supports_fused_pull", False) and len(addrs) <= 8:
                 l.pull_wait = (addrs, self.wait_seq[i:i + 1].data_ptr())
         self.launches = 0
+        # the fp32 master copy of a parameter is current only on its server; every other consumer (bias in the GEMM
+        # epilogue, repacked conv weights) must read this rank's bf16 mirror
         if self.world > 1:
+            for p in self.arena.params:
+                p.use_mirror = True
+                if p.pack16 is not None:
+                    p.pack_from_mirror = True
             dist.barrier()
 
     # -- worker side ---------------------------------------------------------------------------------
@@ -150,7 +157,9 @@ class FusedExchange:
         a.chunk_param, a.lr_mult, a.wd_mult = ar.chunk_param.data_ptr(), ar.lr_mult.data_ptr(), ar.wd_mult.data_ptr()
         a.first_chunk, a.nchunks = first, n
         a.up = CUpdater(_KIND_ID[u.kind], getattr(self.pm, "lr", 0.0), u.momentum, u.weight_decay, u.delta,
-                        u.rho, 1.0 / self.world, None)   # LR by value: this runs on the comm stream
+                        u.rho, 1.0 / self.world, self.lr_dev.data_ptr())
+        # LR is read from device memory so a captured graph follows the schedule; safe on the comm stream because
+        # end_step joins it into the compute stream before the next step's LR copy is enqueued
         a.step_dev, a.value_add = None, 0
         a.scratch = self.scratch[i].data_ptr()
         a.self_count = 1
@@ -161,9 +170,6 @@ class FusedExchange:
         native.check(self.lib.sg_ps_push_update(ctypes.byref(a), self.comm.cuda_stream), "sg_ps_push_update")
         native.count_launch()
         self.launches += 1
-        for p in layer.get_params():
-            if p.pack16 is not None:   # repacked operands (conv weights) follow the mirror on every rank
-                raise NotImplementedError("fused push/pull with repacked (convolution) weights: use push_pull=nccl")
 
     def wait_layer(self, layer, step: int) -> None:
         if layer.name not in self._wait_arrays or getattr(layer, "pull_wait", None) is not None:
@@ -173,6 +179,10 @@ class FusedExchange:
         native.check(self.lib.sg_ps_flag_wait(arr, n, None, 0, ctypes.c_void_p(self.wait_seq[i:i + 1].data_ptr()),
                                               torch.cuda.current_stream().cuda_stream), "sg_ps_flag_wait")
         native.count_launch()
+        for p in layer.get_params():
+            if p.pack16 is not None:     # repacked operands (convolution weights) are re-derived from the mirror
+                p.pack_from_mirror = True
+                p.pack16()
 
     def end_step(self, step: int) -> None:
         torch.cuda.current_stream().wait_stream(self.comm)

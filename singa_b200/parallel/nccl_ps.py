@@ -22,6 +22,11 @@ class NcclExchange:
         self.lo = self.rank * self.per * 1024
         self.hi = self.lo + self.per * 1024
         self.last_layer = pm._first_param_layer   # its gradient is the last one produced by backward
+        if self.world > 1 and self.arena.data16 is not None:
+            for p in self.arena.params:
+                p.use_mirror = True
+                if p.pack16 is not None:
+                    p.pack_from_mirror = True
         self.gshard = torch.empty(self.per * 1024, dtype=torch.float32, device=self.arena.grad.device)
 
     def update_layer(self, layer, step: int, side_stream=None) -> None:
@@ -35,10 +40,6 @@ class NcclExchange:
         if self.world > 1:
             if ar.data16 is not None:
                 dist.all_gather_into_tensor(ar.data16, ar.data16[self.lo:self.hi])
-                for p in ar.params:
-                    if p.pack16 is not None:
-                        dist.all_gather_into_tensor(ar.data, ar.data[self.lo:self.hi])
-                        break
                 for p in ar.params:
                     if p.pack16 is not None:
                         p.pack16()

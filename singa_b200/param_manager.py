@@ -101,6 +101,11 @@ class ParamManager:
         elif backend != "local":
             raise ValueError(f"unknown exchange backend {backend!r}")
         self.use_device_lr = ctx().is_native
+        import os
+        if os.environ.get("SINGA_B200_BIAS_MIRROR") == "1" and self.arena.data16 is not None:
+            # numerics knob for equivalence tests: read biases from the bf16 mirror like the sharded exchanges do
+            for p in self.arena.params:
+                p.use_mirror = True
 
     # -- reference API -----------------------------------------------------------------------------
     def init_params(self) -> None:
