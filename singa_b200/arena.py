@@ -87,8 +87,9 @@ class ParamArena:
             off += _round_up(n, CHUNK)
         return _round_up(max(off, CHUNK), CHUNK * max(1, pad_chunks_to))
 
-    def adopt(self) -> None:
-        """Re-point every owner parameter's blobs into the arena (existing values are preserved)."""
+    def adopt(self, all_params: Sequence[Param] = ()) -> None:
+        """Re-point every owner parameter's blobs into the arena (existing values are preserved); parameters that
+        share an owner (test nets, replicas of a data-partitioned layer) are re-aliased afterwards."""
         for p in self.params:
             o, n = self.offsets[id(p)], self.slot[id(p)]
             p.arena_offset = o
@@ -117,6 +118,12 @@ class ParamArena:
                 p.mirror16 = shaped(self.data16)     # always: the parameter server broadcasts into the mirror
                 if p.pack16 is None:
                     p.data16 = p.mirror16            # GEMM operand = the arena's bf16 mirror
+        for q in all_params:
+            if not q.is_owner:
+                shared_grad = q.grad is not None and q.owner.grad is not None and getattr(q, "_shares_grad", False)
+                q.data, q.data16 = q.owner.data, q.owner.data16
+                if shared_grad:
+                    q.grad = q.owner.grad
         self.sync_mirror()
 
     def view16(self, p: Param) -> torch.Tensor:

@@ -128,11 +128,22 @@ class Graph:
         return node
 
     def insert_bridge_node(self, srcnode: Node, dstnode: Node) -> Tuple[Node, Node]:
+        """Replace the edge srcnode -> dstnode by srcnode -> s-.. -> d-.. -> dstnode IN PLACE (the position of the
+        edge in dstnode's source list is kept: Concate / Slice consumers depend on the order of their sources).
+        Works whether or not the direct edge still exists."""
         src = self.add_node(f"s-{srcnode.name}-{dstnode.name}", srcnode.val.copy(origin="kBridgeSrc"))
         dst = self.add_node(f"d-{srcnode.name}-{dstnode.name}", dstnode.val.copy(origin="kBridgeDst"))
-        self.add_edge(srcnode, src)
+        if dstnode in srcnode.dstnodes:
+            i = srcnode.dstnodes.index(dstnode)
+            j = dstnode.srcnodes.index(srcnode)
+            srcnode.dstnodes[i] = src
+            src.srcnodes.append(srcnode)
+            dstnode.srcnodes[j] = dst
+            dst.dstnodes.append(dstnode)
+        else:
+            self.add_edge(srcnode, src)
+            self.add_edge(dst, dstnode)
         self.add_edge(src, dst)
-        self.add_edge(dst, dstnode)
         return src, dst
 
     # -- dump ----------------------------------------------------------------------------------

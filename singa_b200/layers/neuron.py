@@ -219,9 +219,14 @@ class InnerProductLayer(NeuronLayer):
                    out32=self.weight.grad, accumulate=accumulate)
         else:
             _, dw, db = R.ip_bwd(x, self.weight.data, dy.float(), False)
-            self.weight.grad.copy_(dw)
-            if self.bias_term:
-                self.bias.grad.copy_(db)
+            if getattr(self, "_accumulate_wgrad", False):
+                self.weight.grad.add_(dw)
+                if self.bias_term:
+                    self.bias.grad.add_(db)
+            else:
+                self.weight.grad.copy_(dw)
+                if self.bias_term:
+                    self.bias.grad.copy_(db)
 
     def compute_data_gradient(self):
         """dX = dY W^T (times act'(x) when the source activation's backward is fused here)."""
@@ -408,9 +413,14 @@ class ConvolutionLayer(NeuronLayer):
         else:
             self._dx_ref, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
                                               self.stride, self.pad, self._need_src_grad())
-            self.weight.grad.copy_(dw)
-            if self.bias_term:
-                self.bias.grad.copy_(db)
+            if getattr(self, "_accumulate_wgrad", False):
+                self.weight.grad.add_(dw)
+                if self.bias_term:
+                    self.bias.grad.add_(db)
+            else:
+                self.weight.grad.copy_(dw)
+                if self.bias_term:
+                    self.bias.grad.copy_(db)
 
     def compute_data_gradient(self):
         if not self._need_src_grad():

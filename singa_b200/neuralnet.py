@@ -40,6 +40,7 @@ class NeuralNet:
                 lp.partition_type = proto.partition_type
         self.group_size = group_size
         self.graph = Graph()
+        self.param_shares: Dict[int, int] = {}
         self.layers: List[Layer] = []
         self.name2layer_: Dict[str, Layer] = {}
         self.params: List[Param] = []
@@ -142,6 +143,27 @@ class NeuralNet:
                 got = layer.shape(None)
                 assert list(expect) == list(got), \
                     f"{layer.name}: shape after partition {got} != expected {expect}"
+        # replicas of a DATA-partitioned layer are the same layer on different slices of the batch: they share
+        # one set of parameters and accumulate into one gradient (the reference aggregates the gradients of the
+        # threads sharing a Param and applies ONE update with grad_scale = 1/shares,
+        # src/utils/param_manager.cc:169-190)
+        first: Dict[str, Layer] = {}
+        for node in self.graph.nodes:
+            layer = self.name2layer_[node.name]
+            origin = node.val.origin
+            old = old_name2layer.get(origin)
+            if old is None or old.partition_type != S.kDataPartition or not layer.get_params():
+                continue
+            layer._accumulate_wgrad = True        # every replica adds into the shared (zeroed) gradient
+            if origin not in first:
+                first[origin] = layer
+                continue
+            lead = first[origin]
+            for p, q in zip(layer.get_params(), lead.get_params()):
+                p.share_data(q)
+                p.grad = q.grad
+                self.param_shares[id(q)] = self.param_shares.get(id(q), 1) + 1
+            layer._accumulate_wgrad = True
 
     def _create_partitioned_graph(self, layers, name2layer) -> Graph:
         graph = Graph()
@@ -217,10 +239,18 @@ class NeuralNet:
         for node in list(graph.nodes):
             for dst in list(node.dstnodes):
                 if node.val.locationid != dst.val.locationid:
-                    graph.remove_edge(node, dst)
-                    graph.insert_bridge_node(node, dst)
+                    graph.insert_bridge_node(node, dst)      # replaces the edge in place (source order kept)
         graph.sort()
         return graph
+
+    def zero_shared_grads(self) -> None:
+        """Gradients shared by the replicas of a data-partitioned layer are accumulated: clear them before a
+        backward pass."""
+        for layer in self.layers:
+            if getattr(layer, "_accumulate_wgrad", False):
+                for p in layer.get_params():
+                    if p.is_owner:
+                        p.grad.zero_()
 
     # ------------------------------------------------------------------------------------------
     def fuse_activations(self) -> None:

@@ -76,6 +76,9 @@ class ParamManager:
                                 with_snapshot=(self.param_type == "RandomSync" and nservers > 0),
                                 allocator=allocator,
                                 pad_chunks_to=world if backend in ("fused", "nccl", "async") else 1)
+        for p in net.params:      # replicas of data-partitioned layers: re-alias value AND gradient to the owner
+            if not p.is_owner:
+                p.data, p.data16, p.grad = p.owner.data, p.owner.data16, p.owner.grad
         self.paramid2version: Dict[int, int] = {p.id: 0 for p in net.params}
         self.layer_ranges = {}
         for layer in net.layers:
@@ -156,7 +159,8 @@ class ParamManager:
         # local update: one fused launch over the whole arena once the last gradient (the first layer in
         # forward order) is ready
         if layer is self._first_param_layer:
-            self._update_range(0, self.arena.nchunks, step)
+            shares = max(self.net.param_shares.values()) if getattr(self.net, "param_shares", None) else 1
+            self._update_range(0, self.arena.nchunks, step, grad_scale=1.0 / shares)
             for p in self.net.params:
                 self.paramid2version[p.id] = step + 1
             if self.backend is not None and self.sync_now(step):

@@ -193,6 +193,8 @@ class Executor:
         reduction) is independent of its data gradient, so it is issued on a side stream and the data
         gradient — the critical path to the layers below — continues on the main stream; the parameter
         update joins the side streams.  Small GEMMs that cannot fill 148 SMs alone then overlap."""
+        if net.param_shares:
+            net.zero_shared_grads()
         split = self._side_streams is not None and self.pm.backend_name in ("local", "fused", "nccl")
         main = torch.cuda.current_stream() if split else None
         k = 0
@@ -339,6 +341,70 @@ class Executor:
         return step
 
 
+class HogwildGroup:
+    """Several executor threads inside one process training ONE shared set of parameters (CPU path).
+
+    Reference: ``Worker::Start`` spawns ``nthreads_per_procs - 1`` extra ``Executor`` threads
+    (src/worker/worker.cc:33-39) and ``ParamManager::UpdateParam`` either lets every thread update the shared
+    Param without locks (hogwild, src/utils/param_manager.cc:165-167) or aggregates the threads' gradients under
+    a mutex and applies one update with ``grad_scale = 1/shares`` (:169-190).  Each thread owns a replica of the
+    net (its own activations, gradients and data stream) whose parameters alias the master net's values.
+    """
+
+    def __init__(self, worker: "Worker", nthreads: int, hogwild: bool):
+        self.worker, self.nthreads, self.hogwild = worker, nthreads, hogwild
+        self.replicas: List[NeuralNet] = [worker.train_net]
+        for t in range(1, nthreads):
+            net = worker.setup_neuralnet(worker.model, S.kTrain)
+            net.share_weights(worker.train_net)
+            for d in net.datalayers:                      # every thread reads its own part of the stream
+                d.source.skip(t * d.batchsize)
+            self.replicas.append(net)
+        self._lock = threading.Lock()
+        self._agg = {}
+        self._arrived = {}
+        self.updates = 0
+
+    def _thread(self, tid: int, steps: int, start: int) -> None:
+        net = self.replicas[tid]
+        upd = self.worker.pm.updater
+        owners = [p if p.is_owner else p.owner for p in net.params]
+        for step in range(start, start + steps):
+            for d in net.datalayers:
+                d.compute_feature(True)
+                if self.nthreads > 1:
+                    d.source.skip((self.nthreads - 1) * d.batchsize)
+            for l in net.layers:
+                if not l.is_datalayer:
+                    l.compute_feature(True)
+            for l in reversed(net.layers):
+                if l.is_datalayer or l.is_parserlayer:
+                    continue
+                l.compute_gradient()
+                for p, o in zip(l.get_params(), [q if q.is_owner else q.owner for q in l.get_params()]):
+                    if self.hogwild:
+                        o.grad = p.grad                   # lock-free: this thread's gradient, shared value
+                        upd.update(step, o)
+                        self.updates += 1
+                    else:
+                        with self._lock:
+                            acc = self._agg.get(id(o))
+                            self._agg[id(o)] = p.grad.clone() if acc is None else acc.add_(p.grad)
+                            self._arrived[id(o)] = self._arrived.get(id(o), 0) + 1
+                            if self._arrived[id(o)] == self.nthreads:
+                                o.grad = self._agg.pop(id(o))
+                                self._arrived[id(o)] = 0
+                                upd.update(step, o, grad_scale=1.0 / self.nthreads)
+                                self.updates += 1
+
+    def run(self, steps: int, start: int = 0) -> None:
+        ths = [threading.Thread(target=self._thread, args=(t, steps, start)) for t in range(self.nthreads)]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+
+
 class Worker:
     """``Worker(cluster).start(model)`` — build the phase nets, parameters and executors, warm up, exchange
     the initial parameters with the servers and train (src/worker/worker.cc:14-106)."""
@@ -432,6 +498,14 @@ class Worker:
             else:
                 pm.get_params_from_servers()
         start = max(self.start_step, warm)
+        nthreads = self.cluster.nthreads_per_procs if self.cluster is not None else 1
+        if nthreads > 1 and ctx().device.type == "cpu" and not self.train_net.param_shares \
+                and pm.backend_name == "local":
+            group = HogwildGroup(self, nthreads, pm.hogwild and model.updater.hogwild)
+            group.run(max(0, model.train_steps - start), start)
+            log.error("\t%s", Performance(self.train_net).to_string())
+            pm.finish()
+            return model.train_steps
         step = ex.run(self.perf, start, on_step=self._maybe_checkpoint)
         _sync()
         pm.finish()
