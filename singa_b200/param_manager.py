@@ -105,6 +105,7 @@ class ParamManager:
             raise ValueError(f"unknown exchange backend {backend!r}")
         self.use_device_lr = ctx().is_native
         import os
+        self.per_layer_update = os.environ.get("SINGA_B200_PER_LAYER_UPDATE") == "1"
         if os.environ.get("SINGA_B200_BIAS_MIRROR") == "1" and self.arena.data16 is not None:
             # numerics knob for equivalence tests: read biases from the bf16 mirror like the sharded exchanges do
             for p in self.arena.params:
@@ -156,8 +157,25 @@ class ParamManager:
         if self.backend is not None and self.backend.handles_update:
             self.backend.update_layer(layer, step, side_stream)
             return
-        # local update: one fused launch over the whole arena once the last gradient (the first layer in
-        # forward order) is ready
+        # local update, per layer on the layer's side stream: the update of layer L then overlaps the backward of
+        # the layers below it.  The side stream first waits for the compute stream, because L's data gradient
+        # (already enqueued there) still reads the bf16 weights this update overwrites.
+        # (Measured on the MNIST MLP: 0.375 ms/step with per-layer updates vs 0.307 ms with one update at the end — the
+        # extra stream dependencies cost more than the overlap gains — so this is opt-in.)
+        if self.per_layer_update and side_stream is not None and self.arena.use16 \
+                and not getattr(self.net, "param_shares", None) and self.backend is None:
+            main = torch.cuda.current_stream()
+            side_stream.wait_stream(main)
+            first, n = self.layer_ranges[layer.name]
+            with torch.cuda.stream(side_stream):
+                self._update_range(first, n, step)
+            if layer is self._first_param_layer:
+                main.wait_stream(side_stream)
+            for p in layer.get_params():
+                self.paramid2version[p.id] = step + 1
+            return
+        # otherwise one fused launch over the whole arena once the last gradient (the first layer in forward
+        # order) is ready
         if layer is self._first_param_layer:
             shares = max(self.net.param_shares.values()) if getattr(self.net, "param_shares", None) else 1
             self._update_range(0, self.arena.nchunks, step, grad_scale=1.0 / shares)

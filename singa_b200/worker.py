@@ -211,10 +211,14 @@ class Executor:
                 with torch.cuda.stream(side):
                     layer.compute_param_gradient()
                 layer.compute_data_gradient()
-                if layer is self.pm._first_param_layer:
-                    for s_ in self._side_streams:
+                last = layer is self.pm._first_param_layer
+                if last and self.pm.backend_name == "nccl":
+                    for s_ in self._side_streams:      # the collective on the compute stream needs every gradient
                         main.wait_stream(s_)
                 self.pm.update_param(layer, step, side)
+                if last:
+                    for s_ in self._side_streams:
+                        main.wait_stream(s_)
             else:
                 layer.compute_gradient()
                 if has_params:
