@@ -25,57 +25,9 @@
 #include "../include/singa_b200.h"
 #include "common.h"
 #include "ptx.cuh"
+#include "gemm_common.cuh"
 
 namespace sg {
-
-constexpr int BM = 128;
-constexpr int BK = 64;                       // 64 bf16 = one 128-byte swizzle row
-constexpr int UMMA_K = 16;
-constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
-constexpr int GEMM_THREADS = 192;
-constexpr int SMEM_BUDGET = 200 * 1024;
-
-template <int BN> struct GemmCfg {
-  static constexpr int B_STAGE_BYTES = BN * BK * 2;
-  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
-  static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // power of two for BN in {64,128,256}
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-};
-
-struct GemmParams {
-  int M, N, K;
-  float* d32; long long ldd32;
-  __nv_bfloat16* d16; long long ldd16;
-  const void* bias; int bias_bf16;
-  int act, grad_act;
-  const void* aux; long long ldaux; int aux_bf16;
-  int accumulate;
-  int perm_c, perm_kk;
-  const unsigned long long* wait_flags[8];
-  int nwait;
-  const unsigned long long* wait_seq;
-};
-
-__device__ __forceinline__ float tanh_fast(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-// Scaled tanh of the reference (include/mshadow/cxxnet_op.h:77-87): y = 1.7159047 tanh(0.66666667 x).
-constexpr float kStanhA = 1.7159047f;
-constexpr float kStanhB = 0.66666667f;
-
-__device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == SG_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == SG_ACT_STANH) return kStanhA * tanh_fast(kStanhB * v);
-  return v;
-}
-__device__ __forceinline__ float act_grad_from_output(float y, int act) {
-  if (act == SG_ACT_RELU) return y > 0.f ? 1.f : 0.f;
-  if (act == SG_ACT_STANH) return kStanhA * kStanhB - (kStanhB / kStanhA) * y * y;
-  return 1.f;
-}
 
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -212,14 +164,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     // ------------------------------------------------------------------ epilogue (warps 2..5)
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may read
     const int row_in_tile = quad * 32 + lane;
-    const bool vec32_ok = p.d32 == nullptr ||
-        ((p.ldd32 & 3) == 0 && (reinterpret_cast<uintptr_t>(p.d32) & 15) == 0);
-    const bool vec16_ok = p.d16 == nullptr ||
-        ((p.ldd16 & 7) == 0 && (reinterpret_cast<uintptr_t>(p.d16) & 15) == 0);
-    const bool vecaux_ok = p.grad_act == SG_ACT_NONE ||
-        (p.aux_bf16 ? ((p.ldaux & 7) == 0 && (reinterpret_cast<uintptr_t>(p.aux) & 15) == 0)
-                    : ((p.ldaux & 3) == 0 && (reinterpret_cast<uintptr_t>(p.aux) & 15) == 0));
-    const bool fast_ok = vec32_ok && vec16_ok && vecaux_ok && p.perm_c == 0;
+    const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int m0 = (tile % m_tiles) * BM;
@@ -242,102 +187,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
-        const int nb = n0 + c;
-        if (!row_ok || nb >= p.N) continue;
-        const int nvalid = min(32, p.N - nb);
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < nvalid)
-              v[j] += p.bias_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[nb + j])
-                                  : __ldg(reinterpret_cast<const float*>(p.bias) + nb + j);
-        }
-        if (p.act != SG_ACT_NONE) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
-        }
-        if (fast_ok && nvalid == 32) {
-          if (p.grad_act != SG_ACT_NONE) {
-            if (p.aux_bf16) {
-              const uint4* ap = reinterpret_cast<const uint4*>(
-                  reinterpret_cast<const __nv_bfloat16*>(p.aux) + row * p.ldaux + nb);
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const uint4 u = __ldg(ap + q);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                  const float y0 = __uint_as_float(w[t] << 16);
-                  const float y1 = __uint_as_float(w[t] & 0xFFFF0000u);
-                  v[q * 8 + t * 2] *= act_grad_from_output(y0, p.grad_act);
-                  v[q * 8 + t * 2 + 1] *= act_grad_from_output(y1, p.grad_act);
-                }
-              }
-            } else {
-              const float4* ap = reinterpret_cast<const float4*>(
-                  reinterpret_cast<const float*>(p.aux) + row * p.ldaux + nb);
-#pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const float4 y = __ldg(ap + q);
-                v[q * 4 + 0] *= act_grad_from_output(y.x, p.grad_act);
-                v[q * 4 + 1] *= act_grad_from_output(y.y, p.grad_act);
-                v[q * 4 + 2] *= act_grad_from_output(y.z, p.grad_act);
-                v[q * 4 + 3] *= act_grad_from_output(y.w, p.grad_act);
-              }
-            }
-          }
-          if (p.d32 != nullptr) {
-            float4* dp = reinterpret_cast<float4*>(p.d32 + row * p.ldd32 + nb);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              float4 o = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
-              if (p.accumulate) {
-                const float4 old = dp[q];
-                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-                v[q * 4] = o.x; v[q * 4 + 1] = o.y; v[q * 4 + 2] = o.z; v[q * 4 + 3] = o.w;
-              }
-              dp[q] = o;
-            }
-          }
-          if (p.d16 != nullptr) {
-            uint4* dp = reinterpret_cast<uint4*>(p.d16 + row * p.ldd16 + nb);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              uint32_t w[4];
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                const __nv_bfloat162 h = __floats2bfloat162_rn(v[q * 8 + t * 2], v[q * 8 + t * 2 + 1]);
-                w[t] = *reinterpret_cast<const uint32_t*>(&h);
-              }
-              dp[q] = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-          }
-        } else {
-          // generic path: ragged N, unaligned leading dimensions, or permuted columns
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (j < nvalid) {
-              const int n = nb + j;
-              float x = v[j];
-              if (p.grad_act != SG_ACT_NONE) {
-                const float y = p.aux_bf16
-                    ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.aux)[row * p.ldaux + n])
-                    : reinterpret_cast<const float*>(p.aux)[row * p.ldaux + n];
-                x *= act_grad_from_output(y, p.grad_act);
-              }
-              const int nout = p.perm_c > 0 ? (n % p.perm_c) * p.perm_kk + (n / p.perm_c) : n;
-              if (p.d32 != nullptr) {
-                float* dp = p.d32 + row * p.ldd32 + nout;
-                if (p.accumulate) x += *dp;
-                *dp = x;
-              }
-              if (p.d16 != nullptr) p.d16[row * p.ldd16 + nout] = __float2bfloat16_rn(x);
-            }
-          }
-        }
+        epilogue_chunk(p, r, row, row_ok, n0 + c, fast_ok);
       }
     }
   }
@@ -347,6 +197,200 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// CTA-pair variant: a cluster of two CTAs (two SMs of one TPC) computes one 256 x BN tile with
+// tcgen05.mma.cta_group::2.  Each CTA stages its own 128 rows of A and only HALF of the B tile; the tensor core
+// reads the other half from the peer's shared memory, so both the L2->smem traffic and the smem read bandwidth
+// per flop drop (per CTA and k-block: 16 KB + BN*64 B instead of 16 KB + BN*128 B).
+//   leader (cluster rank 0): warp 1 issues every MMA for the pair; commits are multicast to both CTAs' barriers
+//   both CTAs: warp 0 = TMA producer (transaction bytes are counted on the LEADER's full barrier),
+//              warps 2..5 = epilogue of the CTA's own 128 accumulator rows (its own TMEM), arriving on the
+//              leader's tmem-empty barrier
+// ------------------------------------------------------------------------------------------------
+template <int BN> struct PairCfg {
+  static constexpr int B_HALF_BYTES = (BN / 2) * BK * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_HALF_BYTES;       // per CTA
+  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
+                              const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+  using Cfg = PairCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int B_HALF_BYTES = Cfg::B_HALF_BYTES;
+  constexpr int BNH = BN / 2;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA0 = smem_base;
+  const uint32_t sB0 = smem_base + STAGES * A_STAGE_BYTES;
+  const uint32_t bar0 = smem_base + STAGES * Cfg::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar0 + 8u * (2 * STAGES + 4);
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair_id = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const int m_tiles = (p.M + 2 * BM - 1) / (2 * BM);
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 2);     // leader's own arrive.expect_tx + the peer's remote arrive
+      mbar_init(empty_bar(s), 1);    // multicast commit from the leader's MMA warp
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);    // multicast commit
+      mbar_init(tempty_bar(a), 8);   // 4 epilogue warps x 2 CTAs (only the leader's copy is waited on)
+    }
+    fence_mbar_init();
+  }
+  cluster_sync_all();                // barrier inits of both CTAs visible before anyone signals / allocates
+  if (warp == 1) {
+    tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (both CTAs)
+    if (lane == 0) {
+      if (p.nwait > 0) {
+        const unsigned long long target = *p.wait_seq;
+        for (int i = 0; i < p.nwait; ++i) {
+          const unsigned long long* f = p.wait_flags[i];
+          unsigned long long v;
+          const long long t0 = clock64();
+          do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+            if (v < target && clock64() - t0 > 60000000000LL) __trap();
+          } while (v < target);
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");
+      }
+      uint32_t stage = 0, phase = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+        const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 rows
+        const int n0 = (tile / m_tiles) * BN + static_cast<int>(rank) * BNH;        // this CTA's half of B
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t fb = full_bar(stage);
+          if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
+          else mbar_arrive_remote(fb, 0);
+          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+          const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          const int k0 = kb * BK;
+          if (!A_MN) {
+            tma_load_2d_pair(sa, &tma_a, fb, k0, m0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b) tma_load_2d_pair(sa + b * 8192, &tma_a, fb, m0 + b * 64, k0);
+          }
+          if (!B_MN) {
+            tma_load_2d_pair(sb, &tma_b, fb, k0, n0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BNH / 64; ++b) tma_load_2d_pair(sb + b * 8192, &tma_b, fb, n0 + b * 64, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (leader) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      constexpr uint32_t A_LBO = A_MN ? 8192 : 16;
+      constexpr uint32_t B_LBO = B_MN ? 8192 : 16;
+      uint32_t stage = 0, phase = 0;
+      int it = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+            const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
+              const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+              umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit_pair(empty_bar(stage), 3);                       // frees the slot in BOTH CTAs
+            if (kb == num_kb - 1) umma_commit_pair(tfull_bar(acc), 3);   // accumulator ready in BOTH CTAs
+          }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+    const int quad = warp & 3;
+    const int row_in_tile = quad * 32 + lane;
+    const bool fast_ok = epilogue_fast_ok(p);
+    int it = 0;
+    for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+      const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;
+      const int n0 = (tile / m_tiles) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const long long row = m0 + row_in_tile;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c, r);
+        tmem_ld_wait();
+        if (c + 32 >= BN) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(tempty_bar(acc), 0);   // the leader's MMA warp waits on ITS barrier
+        }
+        epilogue_chunk(p, r, row, row_ok, n0 + c, fast_ok);
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();      // both CTAs done with both TMEMs and with each other's barriers
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -415,6 +459,39 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
+                            cudaStream_t stream) {
+  using Cfg = PairCfg<BN>;
+  auto kern = gemm_bf16_tcgen05_pair_kernel<BN, A_MN, B_MN>;
+  static thread_local int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    if (check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES),
+                   "cudaFuncSetAttribute(gemm pair smem)"))
+      return 1;
+    attr_dev = dev;
+  }
+  const int m_tiles = (p.M + 2 * BM - 1) / (2 * BM);
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int tiles = m_tiles * n_tiles;
+  const int max_pairs = num_sms() / 2;
+  const int pairs = tiles < max_pairs ? tiles : max_pairs;
+  kern<<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  SG_CHECK_LAUNCH("gemm_bf16_tcgen05_pair");
+  return 0;
+}
+
+template <int BN>
+static int dispatch_major_pair(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                               const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm_pair<BN, false, false>(ta, tb, p, s);
+  if (!a_mn && b_mn) return launch_gemm_pair<BN, false, true>(ta, tb, p, s);
+  if (a_mn && !b_mn) return launch_gemm_pair<BN, true, false>(ta, tb, p, s);
+  return launch_gemm_pair<BN, true, true>(ta, tb, p, s);
+}
+
 template <int BN>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
                           const GemmParams& p, cudaStream_t s) {
@@ -455,6 +532,7 @@ static int pick_bn(int M, int N, int K) {
 }
 
 int g_force_bn = 0;  // test hook (sg_gemm_set_tile)
+int g_pair_mode = 0; // 0 = single-CTA tiles, 1 = CTA-pair (cta_group::2) tiles, 2 = choose per problem
 
 }  // namespace sg
 
@@ -467,6 +545,15 @@ extern "C" int sg_gemm_set_tile(int bn) {
   return 0;
 }
 
+extern "C" int sg_gemm_set_pair(int mode) {
+  if (mode < 0 || mode > 2) {
+    sg::set_error("sg_gemm_set_pair: mode must be 0 (off), 1 (on) or 2 (auto)");
+    return 2;
+  }
+  sg::g_pair_mode = mode;
+  return 0;
+}
+
 extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B,
                             int b_mn_major, long long ldb, int M, int N, int K,
                             const SgGemmEpilogue* ep, void* stream) {
@@ -475,13 +562,16 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   SG_REQUIRE(ep != nullptr && (ep->d32 != nullptr || ep->d16 != nullptr),
              "sg_gemm_bf16: epilogue needs an output");
   SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm_bf16: grad_act needs aux");
-  const int bn = g_force_bn ? g_force_bn : pick_bn(M, N, K);
+  int bn = g_force_bn ? g_force_bn : pick_bn(M, N, K);
+  // CTA pairs need BN in {128, 256} (each CTA stages BN/2 columns of B in 64-column boxes)
+  bool pair = g_pair_mode == 1 || (g_pair_mode == 2 && static_cast<long long>(M) * N >= 4096LL * 4096LL);
+  if (pair && bn < 128) bn = 128;
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn_major) rc = make_tmap_bf16(&ta, A, K, M, lda, BK, BM);
   else rc = make_tmap_bf16(&ta, A, M, K, lda, 64, BK);
   if (rc) return rc;
-  if (!b_mn_major) rc = make_tmap_bf16(&tb, B, K, N, ldb, BK, bn);
+  if (!b_mn_major) rc = make_tmap_bf16(&tb, B, K, N, ldb, BK, pair ? bn / 2 : bn);
   else rc = make_tmap_bf16(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
   GemmParams p;
@@ -496,6 +586,10 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   for (int i = 0; i < 8; ++i) p.wait_flags[i] = i < ep->nwait ? ep->wait_flags[i] : nullptr;
   p.nwait = ep->nwait; p.wait_seq = ep->wait_seq;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (pair) {
+    if (bn == 256) return dispatch_major_pair<256>(a_mn_major, b_mn_major, ta, tb, p, s);
+    return dispatch_major_pair<128>(a_mn_major, b_mn_major, ta, tb, p, s);
+  }
   switch (bn) {
     case 256: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, p, s);
     case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, p, s);

@@ -63,6 +63,9 @@ int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, in
 
 /* Test hook: force the N-tile width (64/128/256) of sg_gemm_bf16; 0 restores the heuristic. */
 int sg_gemm_set_tile(int bn);
+/* Tile shape policy: 0 = one CTA per 128 x BN tile, 1 = CTA pairs (cta_group::2) on 256 x BN tiles,
+ * 2 = pairs for large problems only. */
+int sg_gemm_set_pair(int mode);
 
 /* ------------------------------------------------------------------------------------------------
  * Element-wise family (reference: every mshadow expression lowers to MapPlanKernel,

@@ -44,6 +44,7 @@ def _declare(lib):
         ctypes.POINTER(GemmEpilogue), ctypes.c_void_p,
     ]
     lib.sg_gemm_set_tile.argtypes = [ctypes.c_int]
+    lib.sg_gemm_set_pair.argtypes = [ctypes.c_int]
 
 
 def load():

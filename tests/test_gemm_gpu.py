@@ -111,3 +111,56 @@ def test_gemm_large_timing():
     print(f"\n[gemm 8192^3 bf16] {ms:.3f} ms  {2 * M * N * K / ms / 1e9:.1f} TFLOP/s")
     ref = (a[:256].float() @ b[:512].float().t())
     torch.testing.assert_close(out16[:256, :512].float(), ref, rtol=2e-2, atol=5e-2)
+
+
+# ---------------------------------------------------------------------------------------------- CTA pairs
+def _run_pair(M, N, K, a_mn, b_mn, bn, **kw):
+    lib = native.require()
+    lib.sg_gemm_set_pair(1)
+    try:
+        return _run(M, N, K, a_mn, b_mn, bn, **kw)
+    finally:
+        lib.sg_gemm_set_pair(0)
+
+
+@pytest.mark.parametrize("bn", [128, 256])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_pair_majors_tiles(a_mn, b_mn, bn):
+    out, ref = _run_pair(512, 512, 384, a_mn, b_mn, bn)
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 2500, 784), (1000, 10, 500), (130, 70, 72), (777, 1500, 2000),
+                                   (4096, 1024, 520)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (False, False), (True, True)])
+def test_gemm_pair_ragged(M, N, K, a_mn, b_mn):
+    out, ref = _run_pair(M, N, K, a_mn, b_mn, 0)
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=3e-2)
+
+
+def test_gemm_pair_epilogue_and_timing():
+    bias = torch.randn(300, device="cuda")
+    out, ref = _run_pair(700, 300, 264, False, True, 0, bias=bias, act=G.ACT_STANH)
+    torch.testing.assert_close(out, ref, rtol=5e-3, atol=3e-2)
+    M = N = K = 8192
+    a = (torch.randn(M, K, device="cuda") * 0.05).to(torch.bfloat16)
+    b = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+    o = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    lib = native.require()
+    res = {}
+    for mode in (0, 1):
+        lib.sg_gemm_set_pair(mode)
+        for _ in range(3):
+            G.gemm(a, b, M, N, K, out16=o)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            G.gemm(a, b, M, N, K, out16=o)
+        e1.record()
+        torch.cuda.synchronize()
+        res[mode] = e0.elapsed_time(e1) / 10
+        torch.testing.assert_close(o[:256, :512].float(), a[:256].float() @ b[:512].float().t(), rtol=2e-2, atol=5e-2)
+    lib.sg_gemm_set_pair(0)
+    print(f"\n[gemm 8192^3] single-CTA tiles {res[0]:.3f} ms ({2*M*N*K/res[0]/1e9:.0f} TFLOP/s), "
+          f"CTA pairs {res[1]:.3f} ms ({2*M*N*K/res[1]/1e9:.0f} TFLOP/s)")

@@ -130,4 +130,7 @@ def membound_cases():
 
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "gemm"
+    if len(sys.argv) > 2:      # second argument: tile policy (0 single CTA, 1 CTA pairs, 2 auto)
+        native.require().sg_gemm_set_pair(int(sys.argv[2]))
+        print(f"# sg_gemm_set_pair({sys.argv[2]})")
     {"gemm": gemm_cases, "push": push_case, "membound": membound_cases}[what]()
