@@ -532,7 +532,7 @@ static int pick_bn(int M, int N, int K) {
 }
 
 int g_force_bn = 0;  // test hook (sg_gemm_set_tile)
-int g_pair_mode = 0; // 0 = single-CTA tiles, 1 = CTA-pair (cta_group::2) tiles, 2 = choose per problem
+int g_pair_mode = 2; // 0 = single-CTA tiles, 1 = CTA-pair (cta_group::2) tiles, 2 = choose per problem
 
 }  // namespace sg
 
@@ -562,9 +562,12 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   SG_REQUIRE(ep != nullptr && (ep->d32 != nullptr || ep->d16 != nullptr),
              "sg_gemm_bf16: epilogue needs an output");
   SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm_bf16: grad_act needs aux");
-  int bn = g_force_bn ? g_force_bn : pick_bn(M, N, K);
+  // per-call tile choice (autotuner) > process-wide test hooks > built-in model
+  int bn = ep->tile_bn ? ep->tile_bn : (g_force_bn ? g_force_bn : pick_bn(M, N, K));
+  SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_gemm_bf16: tile_bn must be 0, 64, 128 or 256");
   // CTA pairs need BN in {128, 256} (each CTA stages BN/2 columns of B in 64-column boxes)
-  bool pair = g_pair_mode == 1 || (g_pair_mode == 2 && static_cast<long long>(M) * N >= 4096LL * 4096LL);
+  bool pair = ep->tile_pair == 2 || (ep->tile_pair == 0 &&
+      (g_pair_mode == 1 || (g_pair_mode == 2 && static_cast<long long>(M) * N >= 4096LL * 4096LL)));
   if (pair && bn < 128) bn = 128;
   CUtensorMap ta, tb;
   int rc;

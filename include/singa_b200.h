@@ -56,6 +56,8 @@ typedef struct SgGemmEpilogue {
   int nwait;
   const unsigned long long* wait_seq;
   int bias_bf16;         /* bias points at bf16 values (the parameter server's weight mirror) instead of fp32 */
+  int tile_bn;           /* 0 = library's choice, else 64 / 128 / 256 (set by the shape autotuner) */
+  int tile_pair;         /* 0 = library's choice, 1 = single-CTA tiles, 2 = CTA pairs */
 } SgGemmEpilogue;
 
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,

@@ -56,6 +56,49 @@ def gemm_ref(a, b, a_mn=False, b_mn=False, bias=None, act=ACT_NONE, grad_act=ACT
     return v
 
 
+# ---------------------------------------------------------------------------------------------------------
+# Shape autotuner ("measure, don't guess"): the first time a (M, N, K, majors) problem is seen outside of graph
+# capture, every tile configuration is timed with CUDA events on the caller's own operands and the fastest is
+# remembered for the rest of the process.  The layer shapes of a net are static, so this costs a few
+# milliseconds during the eager warm-up steps and nothing afterwards.
+# ---------------------------------------------------------------------------------------------------------
+import os as _os
+
+# Opt-in: tuned in isolation the small MNIST-MLP GEMMs pick narrow tiles that fill every SM, which then starve the
+# weight-gradient GEMMs running concurrently on the side streams (measured 0.366 ms/step tuned vs 0.307 ms with the
+# built-in wide-tile model), so the model is the default.
+_TUNE = _os.environ.get("SINGA_B200_GEMM_AUTOTUNE", "0") == "1"
+_tuned: dict = {}
+_CANDIDATES = [(64, 1), (128, 1), (256, 1), (128, 2), (256, 2)]
+
+
+def tuned_configs() -> dict:
+    return dict(_tuned)
+
+
+def _autotune(key, launch) -> tuple:
+    best, best_t = (0, 0), float("inf")
+    for bn, pair in _CANDIDATES:
+        if bn > 64 and key[1] <= bn // 2:
+            continue
+        try:
+            launch(bn, pair)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(4):
+                launch(bn, pair)
+            e1.record()
+            torch.cuda.synchronize()
+            t = e0.elapsed_time(e1)
+        except RuntimeError:
+            continue
+        if t < best_t:
+            best, best_t = (bn, pair), t
+    _tuned[key] = best
+    return best
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False, b_mn=False,
          out32: torch.Tensor | None = None, out16: torch.Tensor | None = None,
          bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
@@ -90,7 +133,21 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
         for i, f in enumerate(flags):
             ep.wait_flags[i] = f
         ep.nwait, ep.wait_seq = len(flags), seq
-    rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
-                          b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
-    native.check(rc, "sg_gemm_bf16")
+    def launch(bn=0, pair=0):
+        ep.tile_bn, ep.tile_pair = bn, pair
+        rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
+                              b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
+        native.check(rc, "sg_gemm_bf16")
+
+    cfg = (0, 0)
+    if _TUNE:
+        key = (M, N, K, bool(a_mn), bool(b_mn))
+        cfg = _tuned.get(key)
+        if cfg is None:
+            # tuning re-runs the kernel: only when that is harmless (no accumulation, no flag wait, not capturing)
+            if accumulate or wait is not None or torch.cuda.is_current_stream_capturing():
+                cfg = (0, 0)
+            else:
+                cfg = _autotune(key, launch)
+    launch(*cfg)
     native.count_launch()

@@ -62,9 +62,10 @@ def gemm_cases():
         b = (torch.randn(Kd if b_mn else N, pad(N if b_mn else Kd), device=DEV) * 0.05).to(torch.bfloat16)[:, :(N if b_mn else Kd)]
         out = torch.empty(M, pad(N), device=DEV, dtype=torch.bfloat16)[:, :N]
         ms = timed(lambda: G.gemm(a, b, M, N, Kd, a_mn=a_mn, b_mn=b_mn, out16=out))
+        cfg = G.tuned_configs().get((M, N, Kd, a_mn, b_mn))
         tf = 2.0 * M * N * Kd / ms / 1e9
         rows.append((name, M, N, Kd, ms * 1e3, tf, tf / peak))
-        print(f"{name:28s} M={M:5d} N={N:5d} K={Kd:5d}  {ms*1e3:8.1f} us  {tf:7.1f} TFLOP/s  {tf/peak*100:5.1f}% of {which} cuBLAS bf16 peak")
+        print(f"{name:28s} M={M:5d} N={N:5d} K={Kd:5d}  {ms*1e3:8.1f} us  {tf:7.1f} TFLOP/s  {tf/peak*100:5.1f}% of {which} cuBLAS bf16 peak  tile={cfg}")
     return rows
 
 
