@@ -37,6 +37,7 @@ struct GemmParams {
   const unsigned long long* wait_flags[8];
   int nwait;
   const unsigned long long* wait_seq;
+  int split_k, kb_per_split;
 };
 
 __device__ __forceinline__ float tanh_fast(float x) {
@@ -81,7 +82,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
         }
-        if (fast_ok && nvalid == 32) {
+        if (fast_ok && nvalid == 32 && p.accumulate != 2) {
           if (p.grad_act != SG_ACT_NONE) {
             if (p.aux_bf16) {
               const uint4* ap = reinterpret_cast<const uint4*>(
@@ -153,6 +154,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
               const int nout = p.perm_c > 0 ? (n % p.perm_c) * p.perm_kk + (n / p.perm_c) : n;
               if (p.d32 != nullptr) {
                 float* dp = p.d32 + row * p.ldd32 + nout;
+                if (p.accumulate == 2) {
+                  atomicAdd(dp, x);          // split-K partial (result unused: compiles to RED.ADD)
+                  continue;
+                }
                 if (p.accumulate) x += *dp;
                 *dp = x;
               }

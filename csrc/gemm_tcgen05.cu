@@ -57,6 +57,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   const int n_tiles = (p.N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int num_kb = (p.K + BK - 1) / BK;
+  // split-K: work item w = (tile, k-slice); each item reduces its own range of k-blocks and the epilogue adds the
+  // partial tile into the zeroed fp32 output with red.global.add (weight gradients of convolutions have a huge
+  // K = batch x pixels and only a handful of output tiles)
+  const int num_items = num_tiles * p.split_k;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -100,10 +104,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         asm volatile("fence.proxy.async;" ::: "memory");
       }
       uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int tile = item % num_tiles;
+        const int kb_lo = (item / num_tiles) * p.kb_per_split;
+        const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
         const int m0 = (tile % m_tiles) * BM;
         const int n0 = (tile / m_tiles) * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t fb = full_bar(stage);
           mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
@@ -135,13 +142,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     constexpr uint32_t B_LBO = B_MN ? 8192 : 16;
     uint32_t stage = 0, phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+      const int kb_lo = (item / num_tiles) * p.kb_per_split;
+      const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tempty_bar(acc), acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
         if (lane == 0) {
@@ -151,10 +160,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
             const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
-            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
-          if (kb == num_kb - 1) umma_commit(tfull_bar(acc));
+          if (kb == kb_hi - 1) umma_commit(tfull_bar(acc));
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -166,7 +175,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int row_in_tile = quad * 32 + lane;
     const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+      const int tile = item % num_tiles;
       const int m0 = (tile % m_tiles) * BM;
       const int n0 = (tile / m_tiles) * BN;
       const int acc = it & 1;
@@ -452,7 +462,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   }
   const int m_tiles = (p.M + BM - 1) / BM;
   const int n_tiles = (p.N + BN - 1) / BN;
-  const int tiles = m_tiles * n_tiles;
+  const int tiles = m_tiles * n_tiles * p.split_k;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
   SG_CHECK_LAUNCH("gemm_bf16_tcgen05");
@@ -588,7 +598,38 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   SG_REQUIRE(ep->nwait == 0 || ep->wait_seq != nullptr, "sg_gemm_bf16: wait flags need wait_seq");
   for (int i = 0; i < 8; ++i) p.wait_flags[i] = i < ep->nwait ? ep->wait_flags[i] : nullptr;
   p.nwait = ep->nwait; p.wait_seq = ep->wait_seq;
+  p.split_k = 1; p.kb_per_split = (K + BK - 1) / BK;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  // split-K for plain fp32-output GEMMs (weight gradients) whose tiles cannot fill the machine: take the widest
+  // tile (best bytes/flop) and cut the K loop into as many slices as there are idle SMs
+  if (!pair && ep->d16 == nullptr && ep->bias == nullptr && ep->act == SG_ACT_NONE &&
+      ep->grad_act == SG_ACT_NONE && ep->nwait == 0 && ep->split_k != 1) {
+    const int num_kb = (K + BK - 1) / BK;
+    int split = ep->split_k > 1 ? ep->split_k : 1;
+    if (ep->split_k == 0 && num_kb >= 64 && !ep->tile_bn && !g_force_bn) {
+      const int wide = N > 128 ? 256 : (N > 64 ? 128 : 64);
+      const long long tiles_w = static_cast<long long>((M + BM - 1) / BM) * ((N + wide - 1) / wide);
+      if (tiles_w * 2 <= num_sms()) {
+        split = static_cast<int>(num_sms() / tiles_w);
+        if (split > num_kb / 8) split = num_kb / 8;
+        if (split > 64) split = 64;
+        if (split > 1 && wide != bn) {
+          bn = wide;   // the B tensor map depends on the tile width: rebuild it
+          if (!b_mn_major) { rc = make_tmap_bf16(&tb, B, K, N, ldb, BK, bn); if (rc) return rc; }
+        }
+      }
+    }
+    if (split > 1) {
+      p.kb_per_split = (num_kb + split - 1) / split;
+      p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
+      if (!ep->accumulate) {
+        if (check_cuda(cudaMemset2DAsync(ep->d32, ep->ldd32 * sizeof(float), 0, N * sizeof(float), M, s),
+                       "sg_gemm_bf16: zero the split-K output"))
+          return 1;
+      }
+      p.accumulate = 2;   // epilogue: atomic add of the partial tile
+    }
+  }
   if (pair) {
     if (bn == 256) return dispatch_major_pair<256>(a_mn_major, b_mn_major, ta, tb, p, s);
     return dispatch_major_pair<128>(a_mn_major, b_mn_major, ta, tb, p, s);

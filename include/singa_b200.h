@@ -58,6 +58,9 @@ typedef struct SgGemmEpilogue {
   int bias_bf16;         /* bias points at bf16 values (the parameter server's weight mirror) instead of fp32 */
   int tile_bn;           /* 0 = library's choice, else 64 / 128 / 256 (set by the shape autotuner) */
   int tile_pair;         /* 0 = library's choice, 1 = single-CTA tiles, 2 = CTA pairs */
+  int split_k;           /* fp32-output GEMMs without bias/activation only: 0 = library's choice (splits the K loop
+                            across CTAs when the output has too few tiles, partial tiles are added atomically into the
+                            zeroed output), 1 = never, n > 1 = n slices */
 } SgGemmEpilogue;
 
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,

@@ -103,7 +103,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
          out32: torch.Tensor | None = None, out16: torch.Tensor | None = None,
          bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
          aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None,
-         wait: tuple | None = None):
+         wait: tuple | None = None, split_k: int = 0):
     """Launch the sm_100a kernel.  ``a``/``b`` are 2-D bf16 CUDA tensors whose last dim is contiguous
     (row stride = leading dimension, multiple of 8).  Outputs are written in place."""
     lib = native.require()
@@ -128,6 +128,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
     ep.accumulate = 1 if accumulate else 0
     if perm is not None:
         ep.perm_c, ep.perm_kk = perm
+    ep.split_k = split_k
     if wait is not None:   # (list of flag addresses, address of the sequence number): fused parameter pull
         flags, seq = wait
         for i, f in enumerate(flags):

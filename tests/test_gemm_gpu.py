@@ -164,3 +164,39 @@ def test_gemm_pair_epilogue_and_timing():
     lib.sg_gemm_set_pair(0)
     print(f"\n[gemm 8192^3] single-CTA tiles {res[0]:.3f} ms ({2*M*N*K/res[0]/1e9:.0f} TFLOP/s), "
           f"CTA pairs {res[1]:.3f} ms ({2*M*N*K/res[1]/1e9:.0f} TFLOP/s)")
+
+
+# ---------------------------------------------------------------------------------------------- split-K
+@pytest.mark.parametrize("split", [0, 1, 7])
+@pytest.mark.parametrize("accumulate", [False, True])
+def test_gemm_split_k_wgrad_shapes(split, accumulate):
+    # conv-wgrad-like: tiny output, huge K (= batch x pixels), both operands MN-major, permuted columns
+    F, C, kk, P = 96, 3, 121, 20000
+    dev = "cuda"
+    a, b = _mk(P, F, dev, 0.1), _mk(P, C * kk, dev, 0.1)
+    out = torch.full((F, C * kk), 0.5, device=dev)
+    G.gemm(a, b, F, C * kk, P, a_mn=True, b_mn=True, out32=out, perm=(C, kk), split_k=split, accumulate=accumulate)
+    torch.cuda.synchronize()
+    ref = G.gemm_ref(a, b, True, True, perm=(C, kk)) + (0.5 if accumulate else 0.0)
+    torch.testing.assert_close(out, ref, rtol=3e-3, atol=5e-2)
+
+
+def test_gemm_split_k_plain_and_timing():
+    M, N, K = 256, 2400, 46656            # AlexNet conv2 weight gradient at batch 64
+    dev = "cuda"
+    a, b = _mk(K, M, dev, 0.05), _mk(K, N, dev, 0.05)
+    outs, times = {}, {}
+    for split in (1, 0):
+        out = torch.empty(M, N, device=dev)
+        for _ in range(2):
+            G.gemm(a, b, M, N, K, a_mn=True, b_mn=True, out32=out, split_k=split)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            G.gemm(a, b, M, N, K, a_mn=True, b_mn=True, out32=out, split_k=split)
+        e1.record()
+        torch.cuda.synchronize()
+        outs[split], times[split] = out, e0.elapsed_time(e1) / 5
+    torch.testing.assert_close(outs[0], outs[1], rtol=2e-3, atol=5e-2)
+    print(f"\n[wgrad 256x2400x46656] no split {times[1]*1e3:.0f} us, split-K {times[0]*1e3:.0f} us")
