@@ -13,31 +13,43 @@
 namespace sg {
 
 // col[p][(ky*k + kx)*C + c] = x[n][oy*s - pad + ky][ox*s - pad + kx][c]   (zero outside the image)
-// VEC = channels moved per thread (8 -> one 128-bit access; needs C % 8 == 0 and ld % 8 == 0).
+//
+// With channels-last input, one (pixel, ky) "row" of the column matrix — k*C elements — is a CONTIGUOUS run of the
+// input (the k horizontally adjacent pixels with all their channels).  A warp-row (32 lanes, blockDim.y rows per
+// block) copies one such run; the pixel decomposition and the border clipping are computed once per run, not per
+// element.  VEC = elements per lane access (8 -> 128-bit; needs C % 8 == 0 and ld % 8 == 0).
 template <int VEC>
-__global__ void im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col,
-                                   long long ld, int N, int H, int W, int C, int OH, int OW, int k,
-                                   int s, int pad) {
-  const int cv = C / VEC;
-  const long long total = static_cast<long long>(N) * OH * OW * k * k * cv;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
-    const int c = static_cast<int>(i % cv) * VEC;
-    long long t = i / cv;
-    const int kx = static_cast<int>(t % k); t /= k;
-    const int ky = static_cast<int>(t % k); t /= k;
-    const long long p = t;
+__global__ void __launch_bounds__(256)
+im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, long long ld, int N,
+                   int H, int W, int C, int OH, int OW, int k, int s, int pad) {
+  const long long rows = static_cast<long long>(N) * OH * OW * k;
+  const int row_len = k * C;
+  const long long row_stride = static_cast<long long>(gridDim.x) * blockDim.y;
+  for (long long row = static_cast<long long>(blockIdx.x) * blockDim.y + threadIdx.y; row < rows; row += row_stride) {
+    const int ky = static_cast<int>(row % k);
+    const long long p = row / k;
+    long long t = p;
     const int ox = static_cast<int>(t % OW); t /= OW;
     const int oy = static_cast<int>(t % OH);
     const int n = static_cast<int>(t / OH);
-    const int yy = oy * s - pad + ky, xx = ox * s - pad + kx;
-    const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
-    __nv_bfloat16* dst = col + p * ld + static_cast<long long>(ky * k + kx) * C + c;
-    const __nv_bfloat16* src = x + ((static_cast<long long>(n) * H + yy) * W + xx) * C + c;
+    const int yy = oy * s - pad + ky;
+    const int x0 = ox * s - pad;
+    // elements [e_lo, e_hi) of the run fall inside the image
+    int e_lo = 0, e_hi = 0;
+    if (yy >= 0 && yy < H) {
+      e_lo = max(0, -x0) * C;
+      e_hi = min(k, W - x0) * C;
+    }
+    __nv_bfloat16* dst = col + p * ld + static_cast<long long>(ky) * row_len;
+    const __nv_bfloat16* src = x + ((static_cast<long long>(n) * H + yy) * W + x0) * C;
     if (VEC == 8) {
-      *reinterpret_cast<uint4*>(dst) = in ? __ldg(reinterpret_cast<const uint4*>(src)) : make_uint4(0, 0, 0, 0);
+      for (int e = threadIdx.x * 8; e < row_len; e += 32 * 8) {
+        const bool in = e >= e_lo && e < e_hi;   // C % 8 == 0: a vector never straddles the border
+        *reinterpret_cast<uint4*>(dst + e) = in ? __ldg(reinterpret_cast<const uint4*>(src + e)) : make_uint4(0, 0, 0, 0);
+      }
     } else {
-      *dst = in ? *src : __float2bfloat16_rn(0.f);
+      for (int e = threadIdx.x; e < row_len; e += 32)
+        dst[e] = (e >= e_lo && e < e_hi) ? src[e] : __float2bfloat16_rn(0.f);
     }
   }
 }
@@ -83,6 +95,50 @@ __global__ void col2im_nhwc_kernel(const __nv_bfloat16* __restrict__ dcol, long 
   }
 }
 
+// 8 channels per thread (128-bit loads of dcol, fp32 accumulation): needs C % 8 == 0 and ld % 8 == 0.
+__global__ void __launch_bounds__(256)
+col2im_nhwc_vec8_kernel(const __nv_bfloat16* __restrict__ dcol, long long ld, __nv_bfloat16* __restrict__ dx,
+                        int N, int H, int W, int C, int OH, int OW, int k, int s, int pad, int grad_act,
+                        const __nv_bfloat16* __restrict__ aux) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % cv) * 8;
+    long long t = i / cv;
+    const int xx = static_cast<int>(t % W); t /= W;
+    const int yy = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // taps (ky,kx) with (yy + pad - ky) = oy*s and (xx + pad - kx) = ox*s, oy/ox in range
+    for (int ky = (yy + pad) % s; ky < k; ky += s) {
+      const int ty = yy + pad - ky;
+      if (ty < 0) break;
+      const int oy = ty / s;
+      if (oy >= OH) continue;
+      for (int kx = (xx + pad) % s; kx < k; kx += s) {
+        const int tx = xx + pad - kx;
+        if (tx < 0) break;
+        const int ox = tx / s;
+        if (ox >= OW) continue;
+        const long long p = (static_cast<long long>(n) * OH + oy) * OW + ox;
+        float v[8];
+        Vec<__nv_bfloat16>::load(dcol + p * ld + static_cast<long long>(ky * k + kx) * C + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] += v[j];
+      }
+    }
+    const long long o = ((static_cast<long long>(n) * H + yy) * W + xx) * C + c;
+    if (grad_act != SG_ACT_NONE) {
+      float a[8];
+      Vec<__nv_bfloat16>::load(aux + o, a);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] *= actgrad(a[j], grad_act);
+    }
+    Vec<__nv_bfloat16>::store(dx + o, g);
+  }
+}
+
 static inline int grid_for(long long n, int threads) {
   long long b = (n + threads - 1) / threads;
   const long long cap = static_cast<long long>(num_sms()) * 16;
@@ -100,12 +156,16 @@ extern "C" int sg_im2col_nhwc(const void* x, void* col, long long ld, int N, int
   SG_REQUIRE(k > 0 && stride > 0 && pad >= 0, "sg_im2col_nhwc: bad geometry");
   SG_REQUIRE(ld >= static_cast<long long>(k) * k * C, "sg_im2col_nhwc: ld smaller than k*k*C");
   const bool vec = (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)x & 15) == 0) && (((uintptr_t)col & 15) == 0);
-  const long long total = static_cast<long long>(N) * OH * OW * k * k * (vec ? C / 8 : C);
-  if (total <= 0) return 0;
+  const long long rows = static_cast<long long>(N) * OH * OW * k;
+  if (rows <= 0) return 0;
+  const dim3 block(32, 8);
+  long long blocks = (rows + 7) / 8;
+  const long long cap = static_cast<long long>(num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
   if (vec)
-    im2col_nhwc_kernel<8><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
+    im2col_nhwc_kernel<8><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
   else
-    im2col_nhwc_kernel<1><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
+    im2col_nhwc_kernel<1><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
   SG_CHECK_LAUNCH("im2col_nhwc");
   return 0;
 }
@@ -118,8 +178,14 @@ extern "C" int sg_col2im_nhwc(const void* dcol, long long ld, void* dx, int N, i
   SG_REQUIRE(grad_act == SG_ACT_NONE || aux != nullptr, "sg_col2im_nhwc: grad_act needs aux");
   const long long total = static_cast<long long>(N) * H * W * C;
   if (total <= 0) return 0;
-  col2im_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k,
-                                                         stride, pad, grad_act, (const __nv_bfloat16*)aux);
+  const bool vec = (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)dcol & 15) == 0) && (((uintptr_t)dx & 15) == 0) &&
+                   (aux == nullptr || ((uintptr_t)aux & 15) == 0);
+  if (vec)
+    col2im_nhwc_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C,
+                                                                     OH, OW, k, stride, pad, grad_act, (const __nv_bfloat16*)aux);
+  else
+    col2im_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k,
+                                                           stride, pad, grad_act, (const __nv_bfloat16*)aux);
   SG_CHECK_LAUNCH("col2im_nhwc");
   return 0;
 }

@@ -127,6 +127,82 @@ __global__ void pool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y
   }
 }
 
+// 8 channels per thread (bf16, 128-bit accesses): C % 8 == 0.
+__global__ void __launch_bounds__(256)
+pool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H, int W, int C,
+                     int OH, int OW, int k, int s, int pad, int is_max) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * OH * OW * cv;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % cv) * 8;
+    long long t = i / cv;
+    const int ox = static_cast<int>(t % OW); t /= OW;
+    const int oy = static_cast<int>(t % OH);
+    const int n = static_cast<int>(t / OH);
+    const int y0 = oy * s - pad, x0 = ox * s - pad;
+    const int y1 = min(y0 + k, H), x1 = min(x0 + k, W);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = is_max ? -FLT_MAX : 0.f;
+    for (int yy = max(y0, 0); yy < y1; ++yy)
+      for (int xx = max(x0, 0); xx < x1; ++xx) {
+        float v[8];
+        Vec<__nv_bfloat16>::load(x + ((static_cast<long long>(n) * H + yy) * W + xx) * C + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = is_max ? fmaxf(acc[j], v[j]) : acc[j] + v[j];
+      }
+    if (!is_max) {
+      const float inv = 1.f / (k * k);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    }
+    Vec<__nv_bfloat16>::store(y + ((static_cast<long long>(n) * OH + oy) * OW + ox) * C + c, acc);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+pool_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                     const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H, int W,
+                     int C, int OH, int OW, int k, int s, int pad, int is_max) {
+  const int cv = C / 8;
+  const long long total = static_cast<long long>(N) * H * W * cv;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int c = static_cast<int>(i % cv) * 8;
+    long long t = i / cv;
+    const int xx = static_cast<int>(t % W); t /= W;
+    const int yy = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    const long long xi = ((static_cast<long long>(n) * H + yy) * W + xx) * C + c;
+    float xv[8], g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    Vec<__nv_bfloat16>::load(x + xi, xv);
+    const int oy_lo = max(0, (yy + pad - k + s) / s), oy_hi = min(OH - 1, (yy + pad) / s);
+    const int ox_lo = max(0, (xx + pad - k + s) / s), ox_hi = min(OW - 1, (xx + pad) / s);
+    for (int oy = oy_lo; oy <= oy_hi; ++oy)
+      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
+        const long long o = ((static_cast<long long>(n) * OH + oy) * OW + ox) * C + c;
+        float gv[8];
+        Vec<__nv_bfloat16>::load(dy + o, gv);
+        if (is_max) {
+          float yv[8];
+          Vec<__nv_bfloat16>::load(y + o, yv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += (yv[j] == xv[j]) ? gv[j] : 0.f;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += gv[j];
+        }
+      }
+    if (!is_max) {
+      const float inv = 1.f / (k * k);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] *= inv;
+    }
+    Vec<__nv_bfloat16>::store(dx + xi, g);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // LRN across channels, NHWC.  norm = knorm + (alpha/n) * sum_{c' in [c-n/2, c+n/2]} x^2; y = x * norm^-beta.
 // Backward: dx = dy*norm^-beta - (2*beta*alpha/n) * x * sum_{c'} dy*x*norm^(-beta-1)... evaluated at c'.
@@ -210,7 +286,9 @@ extern "C" int sg_pool_fwd(const void* x, void* y, int N, int H, int W, int C, i
   const long long total = static_cast<long long>(N) * OH * OW * C;
   if (total <= 0) return 0;
   SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_fwd: bad window");
-  if (is_bf16)
+  if (is_bf16 && C % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0)
+    pool_fwd_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  else if (is_bf16)
     pool_fwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
   else
     pool_fwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (float*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
@@ -225,7 +303,10 @@ extern "C" int sg_pool_bwd(const void* x, const void* y, const void* dy, void* d
   const long long total = static_cast<long long>(N) * H * W * C;
   if (total <= 0) return 0;
   SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_bwd: bad window");
-  if (is_bf16)
+  if (is_bf16 && C % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0 && ((uintptr_t)dy & 15) == 0 &&
+      ((uintptr_t)dx & 15) == 0)
+    pool_bwd_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
+  else if (is_bf16)
     pool_bwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
   else
     pool_bwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (const float*)y, (const float*)dy, (float*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
