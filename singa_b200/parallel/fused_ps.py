@@ -63,6 +63,22 @@ def symmetric_regions(total_elems: int, nlayers: int, world: int):
             ("ready", max(nlayers, 1) * 8), ("version", max(nlayers, 1) * world * 8)]
 
 
+def gather_owned(arena, ranges, world: int) -> None:
+    """Every rank contributes the ranges it owns (zeros elsewhere); a sum all-reduce rebuilds the full buffers."""
+    torch.cuda.synchronize()
+    if world <= 1:
+        return
+    for buf in (arena.data, arena.history, arena.update):
+        if buf is None:
+            continue
+        tmp = torch.zeros_like(buf)
+        for lo, hi in ranges:
+            tmp[lo:hi].copy_(buf[lo:hi])
+        dist.all_reduce(tmp)
+        buf.copy_(tmp)
+    torch.cuda.synchronize()
+
+
 class FusedExchange:
     handles_update = True
 
@@ -186,6 +202,14 @@ class FusedExchange:
 
     def end_step(self, step: int) -> None:
         torch.cuda.current_stream().wait_stream(self.comm)
+
+    def owned_ranges(self) -> List[Tuple[int, int]]:
+        """Element ranges of the arena whose fp32 master copy (and optimizer state) lives on this rank."""
+        return [(a * 1024, (a + n) * 1024) for a, n in self.mine.values() if n > 0]
+
+    def gather_master(self) -> None:
+        """Collective: assemble the full fp32 master weights / history on every rank (checkpointing)."""
+        gather_owned(self.arena, self.owned_ranges(), self.world)
 
     # -- reference API no-ops in synchronous mode -----------------------------------------------------------
     def put_all(self):

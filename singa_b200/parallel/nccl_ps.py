@@ -49,6 +49,10 @@ class NcclExchange:
     def wait_layer(self, layer, step: int) -> None:
         pass
 
+    def gather_master(self) -> None:
+        from .fused_ps import gather_owned
+        gather_owned(self.arena, [(self.lo, self.hi)], self.world)
+
     def put_all(self):
         pass
 
