@@ -25,20 +25,43 @@ template <int BN> struct GemmCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+// Kept at 96 bytes: with the two 128-byte tensor maps the kernel's parameter block stays under 368 bytes.  Growing it
+// to ~410 bytes cost ~1.3 us on EVERY launch (measured: +0.026 ms on the 18-GEMM MNIST step), so flags are bytes
+// and leading dimensions are 32-bit.
 struct GemmParams {
   int M, N, K;
-  float* d32; long long ldd32;
-  __nv_bfloat16* d16; long long ldd16;
-  const void* bias; int bias_bf16;
-  int act, grad_act;
-  const void* aux; long long ldaux; int aux_bf16;
-  int accumulate;
-  int perm_c, perm_kk;
-  const unsigned long long* wait_flags[8];
-  int nwait;
+  int kb_per_split;
+  float* d32;
+  __nv_bfloat16* d16;
+  const void* bias;
+  const void* aux;
+  const unsigned long long* const* wait_flags;   // device array of nwait flag addresses
   const unsigned long long* wait_seq;
-  int split_k, kb_per_split;
+  int ldd32, ldd16, ldaux;
+  int perm_c, perm_kk;
+  short nwait, split_k;
+  unsigned char act, grad_act, aux_bf16, accumulate, bias_bf16;
 };
+static_assert(sizeof(GemmParams) <= 96, "GemmParams grew: see the launch-latency note above");
+
+// Fused parameter pull (src/utils/param_manager.cc:204-234 WaitUpdate): the weights a forward GEMM reads are written
+// into this GPU's bf16 mirror by the server shards' push kernels (peer stores over NVLink).  The TMA producer thread
+// acquires their version counters here, then orders the generic-proxy acquire before the async-proxy (TMA) reads.
+// Kept out of line so the common (no wait) path carries no extra code or registers.
+__device__ __noinline__ void wait_param_versions(const unsigned long long* const* flags, int nwait,
+                                                 const unsigned long long* seq) {
+  const unsigned long long target = *seq;
+  for (int i = 0; i < nwait; ++i) {
+    const unsigned long long* f = flags[i];
+    unsigned long long v;
+    const long long t0 = clock64();
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (v < target && clock64() - t0 > 60000000000LL) __trap();
+    } while (v < target);
+  }
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
 
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
@@ -72,11 +95,40 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
         if (p.bias != nullptr) {
+          // two separate, fully unrolled loops so the 32 loads of a chunk are independent and issued together
+          // (one loop with a per-element fp32/bf16 select serialised them: +5-10 us per forward GEMM)
+          if (p.bias_bf16) {
+            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+            if (nvalid == 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < nvalid)
-              v[j] += p.bias_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[nb + j])
-                                  : __ldg(reinterpret_cast<const float*>(p.bias) + nb + j);
+              for (int q = 0; q < 4; ++q) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(bp) + q);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                  v[q * 8 + t * 2] += __uint_as_float(w[t] << 16);
+                  v[q * 8 + t * 2 + 1] += __uint_as_float(w[t] & 0xFFFF0000u);
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nvalid) v[j] += __bfloat162float(bp[j]);
+            }
+          } else {
+            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+            if (nvalid == 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + q);
+                v[q * 4] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nvalid) v[j] += __ldg(bp + j);
+            }
+          }
         }
         if (p.act != SG_ACT_NONE) {
 #pragma unroll

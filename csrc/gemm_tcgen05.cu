@@ -87,26 +87,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      if (p.nwait > 0) {
-        // fused parameter pull: the weights this GEMM reads are written into this GPU's mirror by the
-        // server shards' push kernels (peer stores over NVLink); acquire their version counters here, then
-        // order the generic-proxy acquire before the async-proxy (TMA) reads
-        const unsigned long long target = *p.wait_seq;
-        for (int i = 0; i < p.nwait; ++i) {
-          const unsigned long long* f = p.wait_flags[i];
-          unsigned long long v;
-          const long long t0 = clock64();
-          do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
-            if (v < target && clock64() - t0 > 60000000000LL) __trap();
-          } while (v < target);
-        }
-        asm volatile("fence.proxy.async;" ::: "memory");
-      }
+      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
       uint32_t stage = 0, phase = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-        const int tile = item % num_tiles;
-        const int kb_lo = (item / num_tiles) * p.kb_per_split;
+        const int slice = p.split_k == 1 ? 0 : item / num_tiles;   // no division on the common path
+        const int tile = item - slice * num_tiles;
+        const int kb_lo = slice * p.kb_per_split;
         const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
         const int m0 = (tile % m_tiles) * BM;
         const int n0 = (tile / m_tiles) * BN;
@@ -143,7 +129,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     uint32_t stage = 0, phase = 0;
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
-      const int kb_lo = (item / num_tiles) * p.kb_per_split;
+      const int kb_lo = p.split_k == 1 ? 0 : (item / num_tiles) * p.kb_per_split;
       const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
@@ -176,7 +162,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
-      const int tile = item % num_tiles;
+      const int tile = p.split_k == 1 ? item : item % num_tiles;
       const int m0 = (tile % m_tiles) * BM;
       const int n0 = (tile / m_tiles) * BN;
       const int acc = it & 1;
@@ -288,19 +274,7 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
     if (lane == 0) {
-      if (p.nwait > 0) {
-        const unsigned long long target = *p.wait_seq;
-        for (int i = 0; i < p.nwait; ++i) {
-          const unsigned long long* f = p.wait_flags[i];
-          unsigned long long v;
-          const long long t0 = clock64();
-          do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
-            if (v < target && clock64() - t0 > 60000000000LL) __trap();
-          } while (v < target);
-        }
-        asm volatile("fence.proxy.async;" ::: "memory");
-      }
+      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
       uint32_t stage = 0, phase = 0;
       for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
         const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 rows
@@ -588,16 +562,19 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   else rc = make_tmap_bf16(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
   GemmParams p;
+  SG_REQUIRE(ep->ldd32 < (1LL << 31) && ep->ldd16 < (1LL << 31) && ep->ldaux < (1LL << 31),
+             "sg_gemm_bf16: leading dimensions must fit in 31 bits");
   p.M = M; p.N = N; p.K = K;
-  p.d32 = ep->d32; p.ldd32 = ep->ldd32;
-  p.d16 = reinterpret_cast<__nv_bfloat16*>(ep->d16); p.ldd16 = ep->ldd16;
-  p.bias = ep->bias; p.bias_bf16 = ep->bias_bf16; p.act = ep->act; p.grad_act = ep->grad_act;
-  p.aux = ep->aux; p.ldaux = ep->ldaux; p.aux_bf16 = ep->aux_bf16;
-  p.accumulate = ep->accumulate; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
-  SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 8, "sg_gemm_bf16: at most 8 wait flags");
-  SG_REQUIRE(ep->nwait == 0 || ep->wait_seq != nullptr, "sg_gemm_bf16: wait flags need wait_seq");
-  for (int i = 0; i < 8; ++i) p.wait_flags[i] = i < ep->nwait ? ep->wait_flags[i] : nullptr;
-  p.nwait = ep->nwait; p.wait_seq = ep->wait_seq;
+  p.d32 = ep->d32; p.ldd32 = static_cast<int>(ep->ldd32);
+  p.d16 = reinterpret_cast<__nv_bfloat16*>(ep->d16); p.ldd16 = static_cast<int>(ep->ldd16);
+  p.bias = ep->bias; p.bias_bf16 = ep->bias_bf16 != 0;
+  p.act = static_cast<unsigned char>(ep->act); p.grad_act = static_cast<unsigned char>(ep->grad_act);
+  p.aux = ep->aux; p.ldaux = static_cast<int>(ep->ldaux); p.aux_bf16 = ep->aux_bf16 != 0;
+  p.accumulate = ep->accumulate != 0; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
+  SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 64, "sg_gemm_bf16: at most 64 wait flags");
+  SG_REQUIRE(ep->nwait == 0 || (ep->wait_seq != nullptr && ep->wait_flags != nullptr),
+             "sg_gemm_bf16: wait flags need the flag list and wait_seq");
+  p.wait_flags = ep->wait_flags; p.nwait = static_cast<short>(ep->nwait); p.wait_seq = ep->wait_seq;
   p.split_k = 1; p.kb_per_split = (K + BK - 1) / BK;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   // split-K for plain fp32-output GEMMs (weight gradients) whose tiles cannot fill the machine: take the widest

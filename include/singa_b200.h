@@ -50,9 +50,10 @@ typedef struct SgGemmEpilogue {
   int perm_c;            /* >0: column j=(kk_idx*perm_c + c) is stored at column c*perm_kk + kk_idx (conv wgrad -> {F, C*k*k}) */
   int perm_kk;
   /* Parameter pull fused into the GEMM (src/utils/param_manager.cc:204-234 WaitUpdate): before the first
-   * operand load the TMA producer acquire-spins until every wait_flags[i] >= *wait_seq — the version counters
-   * the parameter-server push kernel bumps after broadcasting fresh weights into this GPU's bf16 mirror. */
-  const unsigned long long* wait_flags[8];
+   * operand load the TMA producer acquire-spins until every *wait_flags[i] >= *wait_seq — the version counters
+   * the parameter-server push kernel bumps after broadcasting fresh weights into this GPU's bf16 mirror.
+   * wait_flags is a DEVICE array of nwait flag addresses. */
+  const unsigned long long* const* wait_flags;
   int nwait;
   const unsigned long long* wait_seq;
   int bias_bf16;         /* bias points at bf16 values (the parameter server's weight mirror) instead of fp32 */

@@ -204,6 +204,7 @@ class ParserLayer(Layer):
         super().__init__()
         self.staging: List[Optional[torch.Tensor]] = [None, None]
         self.stage_events: List[Optional[torch.cuda.Event]] = [None, None]
+        self.parse_events: List[Optional[torch.cuda.Event]] = [None, None]
         self.stage_fill = 0          # staging slot the next prefetch writes
         self.stage_ready = -1        # slot holding a staged-but-unconsumed batch
         self._lock = threading.Lock()
@@ -228,6 +229,8 @@ class ParserLayer(Layer):
         if dev.type == "cuda":
             st = stream or torch.cuda.current_stream()
             with torch.cuda.stream(st):
+                if self.parse_events[slot] is not None:
+                    st.wait_event(self.parse_events[slot])   # the parse kernel that last read this slot is done
                 self.staging[slot].copy_(host, non_blocking=True)
                 ev = self.stage_events[slot] or torch.cuda.Event()
                 ev.record(st)
@@ -263,6 +266,10 @@ class ParserLayer(Layer):
         if ev is not None and ctx().device.type == "cuda":
             torch.cuda.current_stream().wait_event(ev)
         self.parse(self.staging[slot], training)
+        if ctx().device.type == "cuda":
+            pe = self.parse_events[slot] or torch.cuda.Event()
+            pe.record(torch.cuda.current_stream())
+            self.parse_events[slot] = pe
 
     def reparse(self, training: bool) -> None:
         """Parse the most recently consumed staged batch again (device-resident input, no host traffic)."""

@@ -129,11 +129,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
     if perm is not None:
         ep.perm_c, ep.perm_kk = perm
     ep.split_k = split_k
-    if wait is not None:   # (list of flag addresses, address of the sequence number): fused parameter pull
+    if wait is not None:   # (device int64 tensor of flag addresses, address of the sequence number)
         flags, seq = wait
-        for i, f in enumerate(flags):
-            ep.wait_flags[i] = f
-        ep.nwait, ep.wait_seq = len(flags), seq
+        assert flags.dtype == torch.int64 and flags.is_cuda
+        ep.wait_flags, ep.nwait, ep.wait_seq = flags.data_ptr(), flags.numel(), seq
     def launch(bn=0, pair=0):
         ep.tile_bn, ep.tile_pair = bn, pair
         rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,

@@ -28,7 +28,7 @@ class GemmEpilogue(ctypes.Structure):
         ("aux", ctypes.c_void_p), ("ldaux", ctypes.c_longlong), ("aux_bf16", ctypes.c_int),
         ("accumulate", ctypes.c_int),
         ("perm_c", ctypes.c_int), ("perm_kk", ctypes.c_int),
-        ("wait_flags", ctypes.c_void_p * 8), ("nwait", ctypes.c_int), ("wait_seq", ctypes.c_void_p),
+        ("wait_flags", ctypes.c_void_p), ("nwait", ctypes.c_int), ("wait_seq", ctypes.c_void_p),
         ("bias_bf16", ctypes.c_int),
         ("tile_bn", ctypes.c_int), ("tile_pair", ctypes.c_int), ("split_k", ctypes.c_int),
     ]

@@ -129,8 +129,9 @@ class FusedExchange:
             self._wait_arrays[l.name] = (arr, len(owners))
             # parameter pull fused into the consumer GEMM: layers that support it get the flag addresses and
             # the sequence number and acquire them inside their forward GEMM's TMA producer warp
-            if getattr(l, "supports_fused_pull", False) and len(addrs) <= 8:
-                l.pull_wait = (addrs, self.wait_seq[i:i + 1].data_ptr())
+            if getattr(l, "supports_fused_pull", False):
+                flag_list = torch.tensor([int(a) for a in addrs], dtype=torch.int64, device=ctx().device)
+                l.pull_wait = (flag_list, self.wait_seq[i:i + 1].data_ptr())
         self.launches = 0
         # the fp32 master copy of a parameter is current only on its server; every other consumer (bias in the GEMM
         # epilogue, repacked conv weights) must read this rank's bf16 mirror

@@ -88,6 +88,10 @@ class Executor:
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
+        self._prefed_step = -1
+        self._pipeline_feed = ctx().device.type == "cuda" and os.environ.get("SINGA_B200_PIPELINE_FEED", "1") != "0" \
+            and pm.backend_name in ("local", "fused", "nccl")
+        self._prefetch_q = None
         nside = int(os.environ.get("SINGA_B200_SIDE_STREAMS", "2"))
         self._side_streams = [torch.cuda.Stream() for _ in range(nside)] \
             if (ctx().is_native and nside > 0) else None
@@ -143,17 +147,34 @@ class Executor:
             if self._is_local(p):
                 p.prefetching(training, self._copy_stream)
 
+    def _prefetch_loop(self) -> None:
+        while True:
+            job = self._prefetch_q.get()
+            if job is None:
+                return
+            try:
+                self._prefetch(*job)
+            finally:
+                self._prefetch_done.set()
+
     def _start_prefetch(self, net, training) -> None:
+        """Hand the next batch to the (persistent) prefetch thread — the reference starts a new std::thread per
+        batch (src/worker/worker.cc:306-310); a queue avoids the per-step thread start."""
         if not self.model.prefetch:
             return
-        t = threading.Thread(target=self._prefetch, args=(net, training), daemon=True)
-        t.start()
-        self._prefetch_thread = t
+        if self._prefetch_q is None:
+            import queue
+            self._prefetch_q = queue.SimpleQueue()
+            self._prefetch_done = threading.Event()
+            self._prefetch_done.set()
+            self._prefetch_thread = threading.Thread(target=self._prefetch_loop, daemon=True)
+            self._prefetch_thread.start()
+        self._prefetch_done.clear()
+        self._prefetch_q.put((net, training))
 
     def _join_prefetch(self) -> None:
-        if self._prefetch_thread is not None:
-            self._prefetch_thread.join()
-            self._prefetch_thread = None
+        if self._prefetch_q is not None:
+            self._prefetch_done.wait()
 
     def _feed(self, net: NeuralNet, training: bool) -> None:
         """Make the staged batch current (parse kernels), then start staging the next one."""
@@ -212,9 +233,10 @@ class Executor:
                     layer.compute_param_gradient()
                 layer.compute_data_gradient()
                 last = layer is self.pm._first_param_layer
-                if last and self.pm.backend_name == "nccl":
-                    for s_ in self._side_streams:      # the collective on the compute stream needs every gradient
-                        main.wait_stream(s_)
+                if last and (self.pm.backend_name == "nccl" or
+                             (self.pm.backend_name == "local" and not self.pm.per_layer_update)):
+                    for s_ in self._side_streams:      # the update / collective on the compute stream needs
+                        main.wait_stream(s_)           # every weight gradient issued on the side streams
                 self.pm.update_param(layer, step, side)
                 if last:
                     for s_ in self._side_streams:
@@ -229,9 +251,19 @@ class Executor:
 
     # -- one training step --------------------------------------------------------------------------------
     def train_one_batch(self, step: int) -> None:
-        self.pm.begin_step(step)
-        self._feed(self.train_net, True)
+        """One training step.  On a GPU the host-side preparation of step+1 (LR/step scalars, parse kernels of the
+        already staged batch, start of the next staging copy) is ENQUEUED right after this step's compute has been
+        launched, so it overlaps the GPU work; stream order keeps it behind this step's kernels."""
+        if self._prefed_step != step:
+            self.pm.begin_step(step)
+            self._feed(self.train_net, True)
+        self._prefed_step = -1
         self._run_compute(step)
+        if self._pipeline_feed and not self.stop_now(step + 1) and not self.test_now(step + 1) \
+                and not self.validate_now(step + 1):
+            self.pm.begin_step(step + 1)
+            self._feed(self.train_net, True)
+            self._prefed_step = step + 1
 
     def _run_compute(self, step: int) -> None:
         """forward + backward (+ per-layer parameter update / push) of one step on the already-parsed batch;

@@ -98,6 +98,7 @@ def test_gemm_fused_wait_passes_when_version_reached():
     flags = torch.tensor([3, 4], dtype=torch.int64, device=dev)
     seq = torch.tensor([3], dtype=torch.int64, device=dev)
     G.gemm(a, b, 256, 256, 128, b_mn=True, out32=out,
-           wait=([flags[0:1].data_ptr(), flags[1:2].data_ptr()], seq.data_ptr()))
+           wait=(torch.tensor([flags[0:1].data_ptr(), flags[1:2].data_ptr()], dtype=torch.int64, device=dev),
+                 seq.data_ptr()))
     torch.cuda.synchronize()
     torch.testing.assert_close(out, a.float() @ b.float(), rtol=2e-3, atol=2e-2)
