@@ -6,7 +6,7 @@
 //   warp 0      TMA producer: cp.async.bulk.tensor tiles of A and B into a STAGES-deep smem ring
 //   warp 1      TMEM owner + MMA issuer: one lane issues tcgen05.mma (M=128, N=BN, K=16) x4 per stage,
 //               tcgen05.commit releases the smem slot and, after the last k-block, publishes the accumulator
-//   warps 2..5  epilogue: tcgen05.ld the 128 x BN fp32 accumulator (one TMEM lane = one output row per
+//   warps 2..9  epilogue: tcgen05.ld the 128 x BN fp32 accumulator (one TMEM lane = one output row per
 //               thread), fuse bias / activation / activation-gradient / accumulate, store fp32 and/or bf16
 // Two TMEM accumulator buffers let the MMA of tile i+1 overlap the epilogue of tile i.
 //
@@ -28,6 +28,7 @@
 #include "gemm_common.cuh"
 
 namespace sg {
+
 
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -52,6 +53,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) SG_TRACE(0);
 
   const int m_tiles = (p.M + BM - 1) / BM;
   const int n_tiles = (p.N + BN - 1) / BN;
@@ -71,7 +73,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);  // one arrive per epilogue warp
+      mbar_init(tempty_bar(a), EPI_WARPS);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -83,6 +85,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) SG_TRACE(1);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -115,9 +118,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 #pragma unroll
             for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * 8192, &tma_b, fb, n0 + b * 64, k0);
           }
+          if (kb == kb_lo) SG_TRACE(2);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
+      SG_TRACE(3);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -139,6 +144,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
+        if (lane == 0 && kb == kb_lo) SG_TRACE(4);
         if (lane == 0) {
           const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
           const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
@@ -149,16 +155,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
-          if (kb == kb_hi - 1) umma_commit(tfull_bar(acc));
+          if (kb == kb_hi - 1) { umma_commit(tfull_bar(acc)); SG_TRACE(5); }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    // ------------------------------------------------------------------ epilogue (warps 2..9)
     const int quad = warp & 3;                 // TMEM lane quadrant this warp may read
-    const int row_in_tile = quad * 32 + lane;
+    // this warp's staging tile sits behind the barrier block
+    float* stg = reinterpret_cast<float*>(smem_raw + (bar0 - smem_u32(smem_raw)) + 256) + (warp - 2) * EPI_WARP_FLOATS;
     const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -169,30 +176,35 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const long long row = m0 + row_in_tile;
-      const bool row_ok = row < p.M;
+      if (warp == 2 && lane == 0) SG_TRACE(6);
+      const long long row0 = m0 + quad * 32;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = ((warp - 2) >> 2) * 32; c < BN; c += 64) {
         uint32_t r[32];
         tmem_ld_32x32(taddr + c, r);
         tmem_ld_wait();
-        if (c + 32 >= BN) {
+        if (warp == 2 && lane == 0 && c <= 64) SG_TRACE(10 + 2 * (c >> 6));
+        if (c + 64 >= BN) {
           // accumulator fully in registers: hand the TMEM buffer back to the MMA warp early
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
-        epilogue_chunk(p, r, row, row_ok, n0 + c, fast_ok);
+        epilogue_chunk(p, r, row0, lane, n0 + c, fast_ok, stg);
+        if (warp == 2 && lane == 0 && c <= 64) SG_TRACE(11 + 2 * (c >> 6));
       }
+      if (warp == 2 && lane == 0) SG_TRACE(7);
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) SG_TRACE(8);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if (lane == 0) SG_TRACE(9);
   }
 }
 
@@ -204,7 +216,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 // per flop drop (per CTA and k-block: 16 KB + BN*64 B instead of 16 KB + BN*128 B).
 //   leader (cluster rank 0): warp 1 issues every MMA for the pair; commits are multicast to both CTAs' barriers
 //   both CTAs: warp 0 = TMA producer (transaction bytes are counted on the LEADER's full barrier),
-//              warps 2..5 = epilogue of the CTA's own 128 accumulator rows (its own TMEM), arriving on the
+//              warps 2..9 = epilogue of the CTA's own 128 accumulator rows (its own TMEM), arriving on the
 //              leader's tmem-empty barrier
 // ------------------------------------------------------------------------------------------------
 template <int BN> struct PairCfg {
@@ -212,7 +224,7 @@ template <int BN> struct PairCfg {
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_HALF_BYTES;       // per CTA
   static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + 16 * 1024 /*epilogue staging*/;
 };
 
 template <int BN, bool A_MN, bool B_MN>
@@ -257,7 +269,7 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);    // multicast commit
-      mbar_init(tempty_bar(a), 8);   // 4 epilogue warps x 2 CTAs (only the leader's copy is waited on)
+      mbar_init(tempty_bar(a), 2 * EPI_WARPS);   // epilogue warps x 2 CTAs (only the leader's copy is waited on)
     }
     fence_mbar_init();
   }
@@ -340,9 +352,10 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5, both CTAs)
+    // ------------------------------------------------------------------ epilogue (warps 2..9, both CTAs)
     const int quad = warp & 3;
-    const int row_in_tile = quad * 32 + lane;
+    // this warp's staging tile sits behind the barrier block
+    float* stg = reinterpret_cast<float*>(smem_raw + (bar0 - smem_u32(smem_raw)) + 256) + (warp - 2) * EPI_WARP_FLOATS;
     const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
     for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
@@ -352,20 +365,19 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const long long row = m0 + row_in_tile;
-      const bool row_ok = row < p.M;
+      const long long row0 = m0 + quad * 32;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = ((warp - 2) >> 2) * 32; c < BN; c += 64) {
         uint32_t r[32];
         tmem_ld_32x32(taddr + c, r);
         tmem_ld_wait();
-        if (c + 32 >= BN) {
+        if (c + 64 >= BN) {
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(tempty_bar(acc), 0);   // the leader's MMA warp waits on ITS barrier
         }
-        epilogue_chunk(p, r, row, row_ok, n0 + c, fast_ok);
+        epilogue_chunk(p, r, row0, lane, n0 + c, fast_ok, stg);
       }
     }
   }
@@ -617,3 +629,9 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
     default: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, p, s);
   }
 }
+
+#ifdef SG_GEMM_TRACE
+extern "C" int sg_gemm_trace_read(unsigned long long* out16) {
+  return cudaMemcpyFromSymbol(out16, sg::g_gemm_trace, sizeof(unsigned long long) * 32) == cudaSuccess ? 0 : 1;
+}
+#endif

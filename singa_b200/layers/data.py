@@ -44,27 +44,50 @@ class BatchSource:
 
 class SyntheticSource(BatchSource):
     """Deterministic pseudo-data of the configured shape (no network / datasets on the box).  A pool of
-    pre-generated records is cycled so the per-step host work is a memcpy, like reading a page-cached file."""
+    pre-generated records lives in pinned host memory and is cycled; a batch that does not wrap around the pool is
+    handed out as a VIEW (``next_view``) so the host->device copy reads the records in place, like DMA from a
+    page-cached file, instead of assembling them into a second pinned buffer first."""
 
     def __init__(self, shape, classes=10, pool=4096, seed=0):
         self.sample_shape = [int(s) for s in shape]
         d = int(np.prod(self.sample_shape))
         rng = np.random.default_rng(seed)
-        pool = max(pool, 1)
-        self.labels = rng.integers(0, classes, size=pool, dtype=np.int32)
+        pool = max(min(pool, (512 << 20) // max(d, 1)), 1)      # at most 512 MB of pinned records
+        labels = rng.integers(0, classes, size=pool, dtype=np.int32)
         # class-dependent mean so that the loss can actually go down on synthetic data
         base = rng.integers(0, 256, size=(classes, d), dtype=np.int32)
-        noise = rng.integers(-64, 64, size=(pool, d), dtype=np.int32)
-        self.pixels = np.clip(base[self.labels] + noise, 0, 255).astype(np.uint8)
+        pin = torch.cuda.is_available()
+        self.pixels_t = torch.empty(pool, d, dtype=torch.uint8, pin_memory=pin)
+        self.labels_t = torch.empty(pool, dtype=torch.int32, pin_memory=pin)
+        self.pixels = self.pixels_t.numpy()
+        self.labels = self.labels_t.numpy()
+        self.labels[:] = labels
+        for lo in range(0, pool, 256):                           # chunked: the int32 temporaries stay small
+            hi = min(pool, lo + 256)
+            noise = rng.integers(-64, 64, size=(hi - lo, d), dtype=np.int32)
+            np.clip(base[labels[lo:hi]] + noise, 0, 255, out=noise)
+            self.pixels[lo:hi] = noise
         self.pos = 0
+
+    def next_view(self, n):
+        """(pixels, labels) pinned tensor views of the next n records, or None when the batch wraps around."""
+        pool = self.pixels.shape[0]
+        if self.pos + n > pool:
+            return None
+        v = (self.pixels_t[self.pos:self.pos + n], self.labels_t[self.pos:self.pos + n])
+        self.pos = (self.pos + n) % pool
+        return v
 
     def next_batch(self, pixels, labels):
         n = pixels.shape[0]
         pool = self.pixels.shape[0]
-        idx = (self.pos + np.arange(n)) % pool
-        np.take(self.pixels, idx, axis=0, out=pixels)
-        np.take(self.labels, idx, out=labels)
-        self.pos = (self.pos + n) % pool
+        done = 0
+        while done < n:                                          # contiguous slices (np.take is ~4x slower)
+            m = min(n - done, pool - self.pos)
+            pixels[done:done + m] = self.pixels[self.pos:self.pos + m]
+            labels[done:done + m] = self.labels[self.pos:self.pos + m]
+            self.pos = (self.pos + m) % pool
+            done += m
 
     def skip(self, n):
         self.pos = (self.pos + n) % self.pixels.shape[0]
@@ -151,6 +174,7 @@ class DataLayer(Layer):
         pin = torch.cuda.is_available()
         self.pixels = torch.zeros(self.batchsize, d, dtype=torch.uint8, pin_memory=pin)
         self.labels = torch.zeros(self.batchsize, dtype=torch.int32, pin_memory=pin)
+        self._own_pixels, self._own_labels = self.pixels, self.labels
         self._np_pixels = self.pixels.numpy()
         self._np_labels = self.labels.numpy()
         self.shape_ = [self.batchsize] + self.sample_shape
@@ -172,8 +196,14 @@ class DataLayer(Layer):
             self.source.skip(self.group_id * self.batchsize)
 
     def compute_feature(self, training):
-        """Read the next batch of records into the pinned host buffers."""
-        self.source.next_batch(self._np_pixels, self._np_labels)
+        """Read the next batch of records into the pinned host buffers (or take a pinned view of them when the
+        source can hand the records out in place)."""
+        view = self.source.next_view(self.batchsize) if hasattr(self.source, "next_view") else None
+        if view is not None:
+            self.pixels, self.labels = view
+        else:
+            self.pixels, self.labels = self._own_pixels, self._own_labels
+            self.source.next_batch(self._np_pixels, self._np_labels)
         if self.ngroups > 1:
             self.source.skip((self.ngroups - 1) * self.batchsize)
 

@@ -103,7 +103,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
          out32: torch.Tensor | None = None, out16: torch.Tensor | None = None,
          bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
          aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None,
-         wait: tuple | None = None, split_k: int = 0):
+         wait: tuple | None = None, split_k: int = 0, tile: tuple | None = None):
     """Launch the sm_100a kernel.  ``a``/``b`` are 2-D bf16 CUDA tensors whose last dim is contiguous
     (row stride = leading dimension, multiple of 8).  Outputs are written in place."""
     lib = native.require()
@@ -139,8 +139,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
                               b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
         native.check(rc, "sg_gemm_bf16")
 
-    cfg = (0, 0)
-    if _TUNE:
+    cfg = tile or (0, 0)    # explicit (tile_bn, tile_pair) override, e.g. from a benchmark sweep
+    if _TUNE and tile is None:
         key = (M, N, K, bool(a_mn), bool(b_mn))
         cfg = _tuned.get(key)
         if cfg is None:

@@ -1,24 +1,49 @@
-"""Isolated timing of the MNIST-MLP GEMM shapes (CUDA events, back-to-back launches)."""
+"""Isolated timing of the MNIST-MLP GEMM shapes for every tile configuration: 20 dependent launches captured in
+one CUDA graph (so the host is out of the picture)."""
 import sys
 import torch
 from singa_b200.ops import kernels as K
 
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
+REP = 20
+CFGS = [(0, 0), (64, 1), (128, 1), (256, 1), (128, 2), (256, 2)]
 
-def bench(name, fn, n=300):
-    for _ in range(20):
-        fn()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(n):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    print(f"{name:40s} {e0.elapsed_time(e1) / n * 1000:8.2f} us")
 
-B = 1000
+def bench(fn, n=20):
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        for _ in range(2):
+            fn()
+        s.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(REP):
+                fn()
+        for _ in range(3):
+            g.replay()
+        s.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s)
+        for _ in range(n):
+            g.replay()
+        e1.record(s)
+        s.synchronize()
+    return e0.elapsed_time(e1) / (n * REP) * 1000
+
+
+def sweep(label, call, N):
+    out = []
+    for cfg in CFGS:
+        if cfg[0] > 64 and N <= cfg[0] // 2:
+            out.append("     -")
+            continue
+        out.append(f"{bench(lambda: call(cfg)):6.2f}")
+    print(f"{label:28s} " + " ".join(out))
+
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
+print(f"{'case (us per launch)':28s} " + " ".join(f"{str(c[0]) + ('p' if c[1] == 2 else ''):>6s}" for c in CFGS))
 for (kin, nout) in [(784, 2500), (2500, 2000), (2000, 1500), (1500, 1000), (1000, 500), (500, 10)]:
     ldk = (kin + 7) // 8 * 8
     ldn = (nout + 7) // 8 * 8
@@ -29,6 +54,7 @@ for (kin, nout) in [(784, 2500), (2500, 2000), (2000, 1500), (1500, 1000), (1000
     dy = torch.randn(B, ldn, device=dev).bfloat16()
     dw = torch.empty(kin, ldn, device=dev)
     dx = torch.empty(B, ldk, device=dev, dtype=torch.bfloat16)
-    bench(f"fwd  {B}x{nout}x{kin}", lambda: K.gemm(x[:, :kin], w[:, :nout], B, nout, kin, a_mn=False, b_mn=True, out16=y[:, :nout], bias=b, act=1))
-    bench(f"wgrd {kin}x{nout}x{B}", lambda: K.gemm(x[:, :kin], dy[:, :nout], kin, nout, B, a_mn=True, b_mn=True, out32=dw[:, :nout]))
-    bench(f"dgrd {B}x{kin}x{nout}", lambda: K.gemm(dy[:, :nout], w[:, :nout], B, kin, nout, a_mn=False, b_mn=False, out16=dx[:, :kin]))
+    xs, ws, dys = x[:, :kin], w[:, :nout], dy[:, :nout]
+    sweep(f"fwd  {B}x{nout}x{kin}", lambda c: K.gemm(xs, ws, B, nout, kin, a_mn=False, b_mn=True, out16=y[:, :nout], bias=b, act=2, tile=c), nout)
+    sweep(f"wgrd {kin}x{nout}x{B}", lambda c: K.gemm(xs, dys, kin, nout, B, a_mn=True, b_mn=True, out32=dw[:, :nout], tile=c), nout)
+    sweep(f"dgrd {B}x{kin}x{nout}", lambda c: K.gemm(dys, ws, B, kin, nout, a_mn=False, b_mn=False, out16=dx[:, :kin], tile=c), kin)
