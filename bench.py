@@ -224,6 +224,25 @@ def main():
     graph_launches = ex.graph_kernel_count * args.steps if ex._graph is not None else 0
     gpu_launches = eager_launches + graph_launches
 
+    # optional kernel timeline of a few extra (untimed) steps: SINGA_B200_TRACE_OUT=<prefix> writes
+    # <prefix>.rank<r>.txt with (start us, duration us, stream, kernel) per launch -- attribution only
+    trace_out = os.environ.get("SINGA_B200_TRACE_OUT")
+    if trace_out:
+        from torch.profiler import ProfilerActivity, profile
+        barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(5):
+                step_device(step); step += 1
+            torch.cuda.synchronize()
+        barrier()
+        evs_ = sorted((e for e in prof.events() if e.device_type is not None and "cuda" in str(e.device_type).lower()),
+                      key=lambda e: e.time_range.start)
+        t0_ = evs_[0].time_range.start if evs_ else 0
+        with open(f"{trace_out}.rank{rank}.txt", "w") as fh:
+            for e in evs_:
+                fh.write(f"{e.time_range.start - t0_:10.1f} {e.time_range.end - e.time_range.start:8.1f} "
+                         f"s{getattr(e, 'device_resource_id', -1)} {e.name[:110]}\n")
+
     # ---------------------------------------------------------------- end-to-end region (public API)
     h2d = sum(p.h2d_bytes for p in net.parserlayers)
     d2h = loss_layer.metric.numel() * loss_layer.metric.element_size()

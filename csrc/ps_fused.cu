@@ -31,6 +31,8 @@ namespace sg {
 constexpr int CHUNK = 1024;
 constexpr int MAX_WORLD = SG_PS_MAX_WORLD;
 
+constexpr int PUSH_UNROLL = 4;   // chunks per CTA iteration: bytes in flight per thread = U x world x 16 B
+
 struct PushParams {
   const float* grad[MAX_WORLD];
   __nv_bfloat16* w16[MAX_WORLD];
@@ -47,6 +49,8 @@ struct PushParams {
   int self_count;
   const float* grad_mc;                              // NVLS: multicast address of the gradient arenas (or null)
   __nv_bfloat16* w16_mc;                             // NVLS: multicast address of the bf16 mirrors (or null)
+  unsigned long long* bump_ready;                    // optional: this rank's own "gradients ready" flag, bumped by
+  unsigned long long* bump_seq;                      //   the kernel itself (+ the consumer-side wait sequence)
 };
 
 // NVLS (NVLink SHARP) accessors: one instruction reduces / broadcasts across every GPU bound to the multicast
@@ -126,6 +130,14 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
   const unsigned long long target = p.self_count
       ? p.scratch[1] + 1ull
       : static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
+  // 0. announce this rank's own gradients (folded in: saves a flag kernel + launch gap per push).  Stream order
+  //    guarantees the local gradients are complete when this kernel starts; the flag is set BEFORE any wait, so
+  //    two ranks' push kernels can never wait on each other.
+  if (p.bump_ready != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    if (p.bump_seq != nullptr) *p.bump_seq += 1ull;
+    __threadfence_system();
+    st_release_sys(p.bump_ready, *p.bump_ready + 1ull);
+  }
   // 1. wait for every rank's gradients of this layer
   if (threadIdx.x < p.world && p.ready[threadIdx.x] != nullptr) wait_flag_ge(p.ready[threadIdx.x], target);
   __syncthreads();
@@ -133,9 +145,9 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
   const float base_lr = p.lr_dev ? __ldg(p.lr_dev) : p.lr;
   const bool need_h = p.kind != SG_UPD_SGD || p.momentum > 0.f;
   const bool need_u = p.kind == SG_UPD_ADADELTA;
-  // Two chunks per iteration with every peer load issued before the first use: NVLink reads have ~2 us
-  // latency, so bandwidth comes from bytes in flight (2 x world x 16 B per thread).
-  constexpr int U = 2;
+  // PUSH_UNROLL chunks per iteration with every peer load issued before the first use: NVLink reads have ~2 us
+  // latency, so bandwidth comes from bytes in flight (U x world x 16 B per thread).
+  constexpr int U = PUSH_UNROLL;
   for (long long c0 = static_cast<long long>(blockIdx.x) * U; c0 < p.nchunks;
        c0 += static_cast<long long>(gridDim.x) * U) {
     float4 g[U];
@@ -270,7 +282,8 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   p.step_dev = a->step_dev; p.value_add = a->value_add;
   p.scratch = a->scratch; p.self_count = a->self_count;
   p.grad_mc = a->grad_mc; p.w16_mc = reinterpret_cast<__nv_bfloat16*>(a->w16_mc);
-  long long grid = (a->nchunks + 1) / 2;
+  p.bump_ready = a->bump_ready; p.bump_seq = a->bump_seq;
+  long long grid = (a->nchunks + PUSH_UNROLL - 1) / PUSH_UNROLL;
   const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward
   if (grid > cap) grid = cap;
   ps_push_update_kernel<<<static_cast<unsigned>(grid), 256, 0, s>>>(p);

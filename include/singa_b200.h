@@ -196,6 +196,10 @@ typedef struct SgPsPush {
                                                        the reduction then happens inside the NVSwitch (multimem.ld_reduce) */
   void* w16_mc;                                     /* optional NVLS multicast address of all ranks' bf16 mirrors:
                                                        one multimem.st broadcasts the fresh weights */
+  unsigned long long* bump_ready;                   /* optional: this rank's own ready flag; the kernel increments it
+                                                       (and *bump_seq, the consumer's wait sequence) before waiting,
+                                                       replacing a separate sg_ps_flag_bump launch */
+  unsigned long long* bump_seq;
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
 /* Allocation-free variant of sg_ps_push_update — no counterpart in the reference (its parameter server keeps

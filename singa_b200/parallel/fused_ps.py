@@ -49,6 +49,8 @@ class PsPush(ctypes.Structure):
         ("max_ctas", ctypes.c_int),
         ("grad_mc", ctypes.c_void_p),
         ("w16_mc", ctypes.c_void_p),
+        ("bump_ready", ctypes.c_void_p),
+        ("bump_seq", ctypes.c_void_p),
     ]
 
 
@@ -91,36 +93,65 @@ class FusedExchange:
         assert self.world <= MAX_WORLD, f"fused push/pull supports up to {MAX_WORLD} ranks per node"
         self.arena = pm.arena
         self.layers = list(pm._param_layers)
-        self.lidx = {l.name: i for i, l in enumerate(self.layers)}
         self.shards = shard_bounds(self.arena.nchunks, self.world)
-        self.comm = torch.cuda.Stream()
         import os
+        # two comm streams, alternating buckets: a push starts when ITS gradients are ready instead of queueing behind
+        # the previous bucket's rendezvous
+        self.comms = [torch.cuda.Stream() for _ in range(int(os.environ.get("SINGA_B200_COMM_STREAMS", "2")))]
         self.max_ctas = int(os.environ.get("SINGA_B200_PUSH_CTAS", "296"))
         # NVLS: in-switch reduction / broadcast when the heap has a multicast mapping (torch symmetric memory)
         # (measured on 8xB200, MNIST MLP: NVLS 0.520 ms/step vs peer loads 0.625 at 8 ranks; 0.469 vs 0.444 at 2)
         nvls_env = os.environ.get("SINGA_B200_NVLS", "auto")
         want = self.world >= 4 if nvls_env == "auto" else nvls_env != "0"
         self.use_nvls = want and bool(getattr(heap, "mc_ptr", None)) and heap.mc_ptr("grad") != 0
-        # per layer: push scratch (arrival counter + sequence number) and the consumer's wait sequence number;
-        # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
-        self.scratch = torch.zeros(max(len(self.layers), 1), 2, dtype=torch.int64, device=ctx().device)
-        self.wait_seq = torch.zeros(max(len(self.layers), 1), dtype=torch.int64, device=ctx().device)
-        self.lr_dev = step_state()["lr"]
-        # Ownership is striped PER LAYER: layer L's chunk range is cut into `world` contiguous pieces and rank r
-        # serves piece r, so every layer's push is spread over all GPUs (the last layers of backward would
-        # otherwise all land on the rank owning the head of the arena).
-        self.mine: Dict[str, Tuple[int, int]] = {}
-        self.owners: Dict[str, List[int]] = {}
-        for l in self.layers:
+        # Push BUCKETS: every push costs ~15-20 us of pure rendezvous latency (peer flag poll, system-scope fences,
+        # remote version stores) however small the layer is, and the pushes of a step serialise on the comm stream
+        # (measured at 2 GPUs: 6 pushes = 210 us against a 150 us backward pass).  Adjacent layers are therefore
+        # merged, walking in backward order, until a bucket holds SINGA_B200_PUSH_BUCKET parameters (default 6 M: measured
+        # 0.4425 ms at 8 GPUs / 0.374 at 2, against 0.454 / 0.380 with 2 M and 0.520 / 0.414 unbucketed); the bucket is
+        # pushed when its LAST-visited (lowest) layer has its gradient.
+        bucket_elems = int(os.environ.get("SINGA_B200_PUSH_BUCKET", str(6_000_000)))
+        self.buckets: List[List] = []
+        cur, cur_n = [], 0
+        for l in reversed(self.layers):
             lo, n = pm.layer_ranges[l.name]
+            contiguous = not cur or pm.layer_ranges[cur[-1].name][0] == lo + n
+            if cur and not contiguous:
+                self.buckets.append(cur)
+                cur, cur_n = [], 0
+            cur.append(l)
+            cur_n += n * 1024
+            if cur_n >= bucket_elems:
+                self.buckets.append(cur)
+                cur, cur_n = [], 0
+        if cur:
+            self.buckets.append(cur)
+        self.bucket_of = {l.name: b for b, ls in enumerate(self.buckets) for l in ls}
+        self.trigger = {ls[-1].name for ls in self.buckets}          # lowest layer: visited last in backward
+        self.lidx = dict(self.bucket_of)                             # flag / scratch index of a layer = its bucket
+        nb = max(len(self.buckets), 1)
+        # per bucket: push scratch (arrival counter + sequence number) and the consumer's wait sequence number;
+        # the flag values are self-counted on the device, so nothing depends on a host-updated step scalar
+        self.scratch = torch.zeros(nb, 2, dtype=torch.int64, device=ctx().device)
+        self.wait_seq = torch.zeros(nb, dtype=torch.int64, device=ctx().device)
+        self.lr_dev = step_state()["lr"]
+        # Ownership is striped PER BUCKET: its chunk range is cut into `world` contiguous pieces and rank r serves
+        # piece r, so every push is spread over all GPUs (the last layers of backward would otherwise all land on
+        # the rank owning the head of the arena).
+        self.bucket_mine: List[Tuple[int, int]] = []
+        self.bucket_owners: List[List[int]] = []
+        for ls in self.buckets:
+            lo = min(pm.layer_ranges[l.name][0] for l in ls)
+            n = sum(pm.layer_ranges[l.name][1] for l in ls)
             pieces = [(lo + a, b - a) for a, b in shard_bounds(n, self.world)]
-            self.mine[l.name] = pieces[self.rank]
-            self.owners[l.name] = [r for r, (_, cnt) in enumerate(pieces) if cnt > 0]
+            self.bucket_mine.append(pieces[self.rank])
+            self.bucket_owners.append([r for r, (_, cnt) in enumerate(pieces) if cnt > 0])
+        self.mine: Dict[str, Tuple[int, int]] = {ls[-1].name: self.bucket_mine[b] for b, ls in enumerate(self.buckets)}
         self._wait_arrays = {}
         for l in self.layers:
             i = self.lidx[l.name]
             arr = (ctypes.c_void_p * MAX_WAIT)()
-            owners = self.owners[l.name]
+            owners = self.bucket_owners[i]
             assert len(owners) <= MAX_WAIT
             addrs = []
             for k, o in enumerate(owners):
@@ -149,15 +180,19 @@ class FusedExchange:
         # everything below runs on the comm stream, which waits for BOTH gradients of the layer (data
         # gradient on the compute stream, parameter gradient on its side stream): the compute stream goes
         # straight on to the layer below
-        self.comm.wait_stream(main)
+        comm = self.comms[i % len(self.comms)]
+        comm.wait_stream(main)
         if side_stream is not None:
-            self.comm.wait_stream(side_stream)
-        native.check(self.lib.sg_ps_flag_bump(ctypes.c_void_p(self.heap.ptr("ready", self.rank, i * 8)),
-                                              ctypes.c_void_p(self.wait_seq[i:i + 1].data_ptr()),
-                                              self.comm.cuda_stream), "sg_ps_flag_bump")
-        native.count_launch()
-        first, n = self.mine[layer.name]
-        if n <= 0:
+            comm.wait_stream(side_stream)
+        if layer.name not in self.trigger:
+            return                 # the bucket is pushed by its lowest layer; the comm stream has this gradient's events
+        first, n = self.bucket_mine[i]
+        ready_own = self.heap.ptr("ready", self.rank, i * 8)
+        seq_own = self.wait_seq[i:i + 1].data_ptr()
+        if n <= 0:                 # no piece of this bucket to serve: only announce the local gradients
+            native.check(self.lib.sg_ps_flag_bump(ctypes.c_void_p(ready_own), ctypes.c_void_p(seq_own),
+                                                  comm.cuda_stream), "sg_ps_flag_bump")
+            native.count_launch()
             return
         # -- server side: my piece of this layer
         a = PsPush()
@@ -184,7 +219,8 @@ class FusedExchange:
         if self.use_nvls:
             a.grad_mc = self.heap.mc_ptr("grad")
             a.w16_mc = self.heap.mc_ptr("data16")
-        native.check(self.lib.sg_ps_push_update(ctypes.byref(a), self.comm.cuda_stream), "sg_ps_push_update")
+        a.bump_ready, a.bump_seq = ready_own, seq_own     # the kernel announces this rank's gradients itself
+        native.check(self.lib.sg_ps_push_update(ctypes.byref(a), comm.cuda_stream), "sg_ps_push_update")
         native.count_launch()
         self.launches += 1
 
@@ -202,11 +238,12 @@ class FusedExchange:
                 p.pack16()
 
     def end_step(self, step: int) -> None:
-        torch.cuda.current_stream().wait_stream(self.comm)
+        for c in self.comms:
+            torch.cuda.current_stream().wait_stream(c)
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
         """Element ranges of the arena whose fp32 master copy (and optimizer state) lives on this rank."""
-        return [(a * 1024, (a + n) * 1024) for a, n in self.mine.values() if n > 0]
+        return [(a * 1024, (a + n) * 1024) for a, n in self.bucket_mine if n > 0]
 
     def gather_master(self) -> None:
         """Collective: assemble the full fp32 master weights / history on every rank (checkpointing)."""
