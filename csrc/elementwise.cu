@@ -121,6 +121,64 @@ __global__ void colsum_kernel(const T* __restrict__ x, long long ld, int rows, i
   }
 }
 
+// bf16 input with cols % 8 == 0: every thread owns 8 adjacent columns (one 128-bit load per row, four rows in
+// flight), CVB column vectors x (256 / CVB) row lanes per block; the row lanes are merged through shared memory and
+// the block adds its partial sums with one atomicAdd per column.  (The 2-byte-per-lane kernel above reached
+// 1.4 TB/s; tall-skinny bias gradients of the first convolutions — 774 400 x 96 — took 25 % of all reduction time.)
+__global__ void __launch_bounds__(256)
+colsum_bf16_vec8_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int rows, int cvecs, int cvb,
+                        float* __restrict__ out) {
+  __shared__ float part[256 * 8];
+  const int lanes_r = 256 / cvb;                         // row lanes per block
+  const int cv_in = threadIdx.x % cvb;
+  const int ry = threadIdx.x / cvb;
+  const int cv = blockIdx.x * cvb + cv_in;
+  const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per;
+  const int r1 = min(rows, r0 + rows_per);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (cv < cvecs && ry < lanes_r) {
+    const __nv_bfloat16* base = x + static_cast<long long>(cv) * 8;
+    int r = r0 + ry;
+    for (; r + 3 * lanes_r < r1; r += 4 * lanes_r) {
+      uint4 u[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        u[i] = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r + i * lanes_r) * ld));
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t w[4] = {u[i].x, u[i].y, u[i].z, u[i].w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          acc[2 * t] += __uint_as_float(w[t] << 16);
+          acc[2 * t + 1] += __uint_as_float(w[t] & 0xFFFF0000u);
+        }
+      }
+    }
+    for (; r < r1; r += lanes_r) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * ld));
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        acc[2 * t] += __uint_as_float(w[t] << 16);
+        acc[2 * t + 1] += __uint_as_float(w[t] & 0xFFFF0000u);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[threadIdx.x * 8 + j] = acc[j];
+  __syncthreads();
+  // thread t < cvb * 8 owns column (t) of this block: sum over the row lanes
+  const int ncol = cvb * 8;
+  for (int t = threadIdx.x; t < ncol; t += 256) {
+    const int col = blockIdx.x * ncol + t;
+    if (col >= cvecs * 8) continue;
+    float sum = 0.f;
+    for (int k = 0; k < lanes_r; ++k) sum += part[(k * cvb + t / 8) * 8 + (t & 7)];
+    atomicAdd(out + col, sum);
+  }
+}
+
 // ---------------------------------------------------------------------------------- cast / pack
 // dst[r][c] (bf16, row stride ldd, padding columns zeroed) = src[r][pc] (fp32, row stride lds) where
 // pc = c for a plain cast, or for conv weights (perm_c = C, perm_kk = k*k): destination column
@@ -324,6 +382,20 @@ extern "C" int sg_colsum(const void* x, long long ld, int rows, int cols, float*
   if (rows <= 0 || cols <= 0) return 0;
   if (!accumulate) {
     if (check_cuda(cudaMemsetAsync(out, 0, sizeof(float) * cols, s), "colsum memset")) return 1;
+  }
+  if (is_bf16 && cols % 8 == 0 && ld % 8 == 0 && ((reinterpret_cast<uintptr_t>(x) & 15) == 0)) {
+    const int cvecs = cols / 8;
+    int cvb = 1;
+    while (cvb < 32 && cvb < cvecs) cvb <<= 1;           // power of two: 256 % cvb == 0
+    const int lanes_r = 256 / cvb;
+    const int gxv = (cvecs + cvb - 1) / cvb;
+    int gyv = (num_sms() * 8 + gxv - 1) / gxv;
+    const int max_gyv = (rows + lanes_r * 8 - 1) / (lanes_r * 8);
+    if (gyv > max_gyv) gyv = max_gyv;
+    if (gyv < 1) gyv = 1;
+    colsum_bf16_vec8_kernel<<<dim3(gxv, gyv), 256, 0, s>>>((const __nv_bfloat16*)x, ld, rows, cvecs, cvb, out);
+    SG_CHECK_LAUNCH("colsum_vec8");
+    return 0;
   }
   const int gx = (cols + 31) / 32;
   int gy = (num_sms() * 4 + gx - 1) / gx;

@@ -61,6 +61,19 @@ def test_colsum(dtype):
     torch.testing.assert_close(out, 2 * buf[:, :cols].float().sum(0), rtol=1e-3, atol=4e-2)
 
 
+@pytest.mark.parametrize("rows,cols,ld", [(5000, 96, 96), (777, 2000, 2000), (3000, 256, 264), (100, 8, 8),
+                                          (40000, 384, 384)])
+def test_colsum_vec8(rows, cols, ld):
+    """bf16 with cols % 8 == 0 takes the 128-bit kernel (tall-skinny conv bias gradients)."""
+    buf = torch.randn(rows, ld, device=DEV).to(torch.bfloat16)
+    out = torch.empty(cols, device=DEV)
+    K().colsum(buf, rows, cols, ld, out)
+    ref = buf[:, :cols].float().sum(0)
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=5e-2)
+    K().colsum(buf, rows, cols, ld, out, accumulate=True)
+    torch.testing.assert_close(out, 2 * ref, rtol=1e-3, atol=1e-1)
+
+
 def test_cast_pack_and_copy2d_and_convert():
     F_, C, kk = 20, 3, 25
     w = torch.randn(F_, C * kk, device=DEV)
@@ -197,7 +210,8 @@ def test_lrn_reference_matches_autograd():
 
 
 @pytest.mark.parametrize("N,C,H,W,k,s,pad", [(4, 16, 12, 12, 5, 1, 2), (2, 3, 32, 32, 5, 1, 2),
-                                              (2, 8, 27, 27, 11, 4, 0), (3, 1, 28, 28, 5, 1, 0)])
+                                              (2, 8, 27, 27, 11, 4, 0), (3, 1, 28, 28, 5, 1, 0),
+                                              (2, 3, 35, 35, 11, 4, 2)])
 def test_im2col_col2im(N, C, H, W, k, s, pad):
     OH, OW = (H + 2 * pad - k) // s + 1, (W + 2 * pad - k) // s + 1
     x = nhwc(torch.randn(N, C, H, W, device=DEV).to(torch.bfloat16))
