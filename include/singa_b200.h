@@ -245,6 +245,21 @@ void sg_shard_seek_to_first(void* shard);
 long long sg_shard_count(void* shard);
 int sg_shard_read_image_batch(void* shard, void* pixels_u8, int* labels, int batch, long long dim);
 
+/* ------------------------------------------------------------------------------------------------
+ * Read-only LMDB environment (host code, no liblmdb): B+tree walk over an mmap of <dir>/data.mdb in key order,
+ * Caffe Datum values decoded straight into batch buffers, wrap-around at the end (LMDBDataLayer,
+ * src/worker/layer.cc:237-328).  sg_lmdb_next: 1 = record current, 0 = end (next call restarts), -1 = corrupt.
+ * ---------------------------------------------------------------------------------------------- */
+void* sg_lmdb_open(const char* dir_or_file);
+void sg_lmdb_close(void* env);
+long long sg_lmdb_count(void* env);
+void sg_lmdb_seek_to_first(void* env);
+int sg_lmdb_next(void* env);
+const void* sg_lmdb_key(void* env, long long* len);
+const void* sg_lmdb_val(void* env, long long* len);
+int sg_lmdb_first_shape(void* env, int* chw);
+int sg_lmdb_read_datum_batch(void* env, void* pixels_u8, int* labels, int batch, long long dim);
+
 #ifdef __cplusplus
 }
 #endif

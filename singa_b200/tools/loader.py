@@ -112,6 +112,29 @@ def build(source, shard_folder: str, flush_every: int = 1000) -> int:
     return n
 
 
+def build_lmdb(source, folder: str) -> int:
+    """Same records as ``build`` but as an LMDB environment of Caffe ``Datum`` values (what the reference's
+    kLMDBData layer reads, src/worker/layer.cc:237-328), written by the in-tree writer (no liblmdb needed)."""
+    from ..io.lmdb_reader import write_lmdb
+    items = []
+    for key, rec in source:
+        r = rec
+        if isinstance(rec, (bytes, bytearray)):
+            r = S.Record()
+            r.ParseFromString(bytes(rec))
+        d = S.Datum()
+        shp = list(r.image.shape)
+        shp = [1] * (3 - len(shp)) + shp
+        d.channels, d.height, d.width = shp[-3:]
+        if r.image.pixel:
+            d.data = r.image.pixel
+        else:
+            d.float_data.extend(r.image.data)
+        d.label = r.image.label
+        items.append((key if isinstance(key, bytes) else str(key).encode(), d.SerializeToString()))
+    return write_lmdb(folder, items)
+
+
 def split(input_folder: str, prefix: str, n: int) -> List[int]:
     """Round-robin split of a shard into ``n`` shards ``<prefix><i>`` (data_loader.cc:43-94)."""
     outs = [Shard(f"{prefix}{i}", Shard.kAppend) for i in range(n)]
@@ -157,6 +180,8 @@ def main(argv=None) -> int:
     ap.add_argument("--shape", default="28,28")
     ap.add_argument("--classes", type=int, default=10)
     ap.add_argument("--shard_folder", default="")
+    ap.add_argument("--format", default="shard", choices=["shard", "lmdb"],
+                    help="output container: the Shard file (default) or an LMDB environment of Datum records")
     ap.add_argument("--input", default="")
     ap.add_argument("--prefix", default="")
     ap.add_argument("--n", type=int, default=2)
@@ -181,7 +206,8 @@ def main(argv=None) -> int:
         src = SyntheticRecords([int(x) for x in a.shape.split(",")], a.n if a.n > 2 else 1000, a.classes)
     else:
         ap.error("--datasource must be mnist, imagenet or synthetic (or use --input / --partition)")
-    print(f"inserted {build(src, a.shard_folder)} records into {a.shard_folder}")
+    n = build_lmdb(src, a.shard_folder) if a.format == "lmdb" else build(src, a.shard_folder)
+    print(f"inserted {n} records into {a.shard_folder}")
     return 0
 
 
