@@ -297,26 +297,33 @@ __global__ void mnist_parse_kernel(const uint8_t* __restrict__ src, D* __restric
 // RGB: per image random crop offset (train) + mirror flag, uint8 CHW record -> NHWC output * scale, minus
 // optional mean image (fp32 CHW, full size).  Intent of src/worker/layer.cc:573-624 (whose non-mirror path
 // never writes the output — defect §2.8 of the survey; the intended copy is implemented here).
+// One thread per OUTPUT PIXEL: consecutive threads read consecutive bytes of each colour plane (coalesced) and write
+// C adjacent channel values; the index arithmetic is done once per pixel instead of once per element (the
+// element-per-thread version took 213 us for a 256 x 3 x 227 x 227 batch, ~10x its memory time).
 template <typename D>
 __global__ void rgb_parse_kernel(const uint8_t* __restrict__ src, const float* __restrict__ mean,
                                  D* __restrict__ dst, int batch, int C, int H, int W, int crop,
                                  const int* __restrict__ off_h, const int* __restrict__ off_w,
                                  const int* __restrict__ mirror, float scale) {
   const int oh = crop > 0 ? crop : H, ow = crop > 0 ? crop : W;
-  const long long total = static_cast<long long>(batch) * oh * ow * C;
+  const long long pixels = static_cast<long long>(batch) * oh * ow;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
-    const int c = static_cast<int>(i % C);
-    long long t = i / C;
-    const int x = static_cast<int>(t % ow); t /= ow;
+  const long long plane = static_cast<long long>(H) * W;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < pixels; i += stride) {
+    const int x = static_cast<int>(i % ow);
+    const long long t = i / ow;
     const int y = static_cast<int>(t % oh);
     const int n = static_cast<int>(t / oh);
     const int sy = y + (off_h ? off_h[n] : 0);
     const int sx = (mirror && mirror[n] ? (ow - 1 - x) : x) + (off_w ? off_w[n] : 0);
-    const long long sidx = (static_cast<long long>(c) * H + sy) * W + sx;
-    float v = static_cast<float>(src[static_cast<long long>(n) * C * H * W + sidx]);
-    if (mean) v -= mean[sidx];
-    dst[i] = from_float<D>(v * scale);
+    const long long s0 = static_cast<long long>(sy) * W + sx;
+    const uint8_t* sp = src + static_cast<long long>(n) * C * plane + s0;
+    D* dp = dst + i * C;
+    for (int c = 0; c < C; ++c) {
+      float v = static_cast<float>(sp[c * plane]);
+      if (mean) v -= mean[c * plane + s0];
+      dp[c] = from_float<D>(v * scale);
+    }
   }
 }
 
@@ -513,7 +520,7 @@ extern "C" int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, in
   const int oh = crop > 0 ? crop : H, ow = crop > 0 ? crop : W;
   const long long total = static_cast<long long>(batch) * oh * ow * C;
   DTYPE_SWITCH(dst_bf16, T, {
-    rgb_parse_kernel<T><<<ew_grid(total, 256), 256, 0, s>>>((const uint8_t*)src_u8, mean, (T*)dst, batch, C, H, W,
+    rgb_parse_kernel<T><<<ew_grid(total / C, 256), 256, 0, s>>>((const uint8_t*)src_u8, mean, (T*)dst, batch, C, H, W,
                                                            crop, off_h, off_w, mirror, scale);
   })
   SG_CHECK_LAUNCH("rgb_parse");
