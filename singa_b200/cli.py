@@ -33,6 +33,8 @@ def build_parser() -> argparse.ArgumentParser:
     _flag(ap, "backend", default="", help="native | torch compute backend (default: native on a GPU)")
     _flag(ap, "device", default="", help="cpu | cuda | cuda:N")
     _flag(ap, "seed", type=int, default=0)
+    _flag(ap, "watchdog_s", type=float, default=float(os.environ.get("SINGA_B200_WATCHDOG", "300")),
+          help="terminate when no step completes / a peer rank is silent for this many seconds (0 = off)")
     _flag(ap, "debug_attach", action="store_true", help="spin until a debugger attaches (common.cc Debug())")
     return ap
 
@@ -46,6 +48,7 @@ def registry_classes(param_type: str) -> None:
 
 def main(argv=None) -> int:
     args = build_parser().parse_args(argv)
+    os.environ["SINGA_B200_WATCHDOG"] = str(args.watchdog_s)
     logging.basicConfig(level=logging.DEBUG if args.v >= 3 else (logging.INFO if args.v >= 1 else logging.ERROR),
                         format="%(levelname).1s%(asctime)s %(name)s] %(message)s", datefmt="%m%d %H:%M:%S")
     from .cluster import Cluster

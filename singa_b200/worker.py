@@ -89,6 +89,8 @@ class Executor:
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
         self._prefed_step = -1
+        self.progress_counter = 0          # bumped once per training step (watchdog / heartbeat, utils/watchdog.py)
+        self._nvtx = os.environ.get("SINGA_B200_NVTX") == "1" and ctx().device.type == "cuda"
         self._pipeline_feed = ctx().device.type == "cuda" and os.environ.get("SINGA_B200_PIPELINE_FEED", "1") != "0" \
             and pm.backend_name in ("local", "fused", "nccl")
         self._prefetch_q = None
@@ -203,7 +205,11 @@ class Executor:
                 for _p in layer.get_params():
                     self.pm.wait_update(layer, step)
                     break
+            if self._nvtx:
+                torch.cuda.nvtx.range_push(f"fwd/{layer.name}")
             layer.compute_feature(training)
+            if self._nvtx:
+                torch.cuda.nvtx.range_pop()
             if layer.is_bridgesrclayer:
                 self.bridge.send_data(layer)
         if training and self.display_debug_info(step):
@@ -225,6 +231,8 @@ class Executor:
             if layer.is_bridgesrclayer:
                 self.bridge.recv_grad(layer)
             has_params = bool(layer.get_params())
+            if self._nvtx:
+                torch.cuda.nvtx.range_push(f"bwd/{layer.name}")
             if split and has_params and getattr(layer, "split_backward", False):
                 side = self._side_streams[k % len(self._side_streams)]
                 k += 1
@@ -245,6 +253,8 @@ class Executor:
                 layer.compute_gradient()
                 if has_params:
                     self.pm.update_param(layer, step)
+            if self._nvtx:
+                torch.cuda.nvtx.range_pop()
             if layer.is_bridgedstlayer:
                 self.bridge.send_grad(layer)
         self.pm.end_step(step)
@@ -340,6 +350,7 @@ class Executor:
             log.error("Test at step %d", step)
             self.test(self.test_net, self.model.test_steps, perf is not None)
         self.train_one_batch(step)
+        self.progress_counter += 1
         if perf is not None:
             perf.update()
             if self.display_now(step):
@@ -367,11 +378,17 @@ class Executor:
 
     def run(self, perf: Optional[Performance], start_step: int = 0, on_step=None) -> int:
         step = start_step
-        while not self.stop_now(step):
-            self.run_one_batch(step, perf)
-            if on_step is not None:
-                on_step(step)
-            step += 1
+        from .utils import watchdog as _wd
+        guards = _wd.start_for(self, float(os.environ.get("SINGA_B200_WATCHDOG", "0") or 0))
+        try:
+            while not self.stop_now(step):
+                self.run_one_batch(step, perf)
+                if on_step is not None:
+                    on_step(step)
+                step += 1
+        finally:
+            for g in guards:
+                g.stop()
         self.step = step
         self._join_prefetch()
         return step
