@@ -250,15 +250,18 @@ def main():
     ex.setup()                         # stage batch 0, start the prefetch thread
     for _ in range(3):
         ex.ticks += 1
-        ex.train_one_batch(step); step += 1
-        loss_layer.metric.cpu()
+        ex.train_one_batch_async(step).result(); step += 1
     barrier()
     t0 = time.perf_counter()
-    last = None
+    last, pending = None, None
     for _ in range(args.steps):
         ex.ticks += 1
-        ex.train_one_batch(step); step += 1      # pinned host batch -> H2D -> parse -> fwd/bwd/update
-        last = loss_layer.metric.cpu()           # D2H read of the step's result (forces completion)
+        # pinned host batch -> H2D -> parse -> fwd/bwd/update, + D2H copy of this step's metrics into a pinned slot
+        h = ex.train_one_batch_async(step); step += 1
+        if pending is not None:
+            last = pending.result()              # host read of the PREVIOUS step's result: the GPU already runs step i
+        pending = h
+    last = pending.result()                      # ... and of the final step, inside the timed region
     barrier()
     e2e_s = time.perf_counter() - t0
     ex._join_prefetch()
@@ -302,6 +305,8 @@ def main():
             "clocks": clocks,
             "e2e": {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "result_read": "every step's metrics are copied to pinned memory and read by the host one step "
+                                   "later (Executor.train_one_batch_async); the last one inside the timed region",
                     "final_loss_sum_window": [round(float(x), 4) for x in last.tolist()] if last is not None else None},
             "gpu_launches": gpu_launches,
         }

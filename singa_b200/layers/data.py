@@ -175,6 +175,7 @@ class DataLayer(Layer):
         self.pixels = torch.zeros(self.batchsize, d, dtype=torch.uint8, pin_memory=pin)
         self.labels = torch.zeros(self.batchsize, dtype=torch.int32, pin_memory=pin)
         self._own_pixels, self._own_labels = self.pixels, self.labels
+        self._h2d_pending = []
         self._np_pixels = self.pixels.numpy()
         self._np_labels = self.labels.numpy()
         self.shape_ = [self.batchsize] + self.sample_shape
@@ -202,6 +203,11 @@ class DataLayer(Layer):
         if view is not None:
             self.pixels, self.labels = view
         else:
+            # the pinned batch buffers are about to be overwritten: the host->device copies that read the previous
+            # batch out of them (issued by the parser layers) must have finished
+            for ev in self._h2d_pending:
+                ev.synchronize()
+            self._h2d_pending.clear()
             self.pixels, self.labels = self._own_pixels, self._own_labels
             self.source.next_batch(self._np_pixels, self._np_labels)
         if self.ngroups > 1:
@@ -265,6 +271,9 @@ class ParserLayer(Layer):
                 ev = self.stage_events[slot] or torch.cuda.Event()
                 ev.record(st)
                 self.stage_events[slot] = ev
+                pend = getattr(self._data_layer(), "_h2d_pending", None)
+                if pend is not None and ev not in pend:
+                    pend.append(ev)
         else:
             self.staging[slot].copy_(host)
         return self.staging[slot]

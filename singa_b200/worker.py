@@ -260,7 +260,7 @@ class Executor:
         self.pm.end_step(step)
 
     # -- one training step --------------------------------------------------------------------------------
-    def train_one_batch(self, step: int) -> None:
+    def train_one_batch(self, step: int, _fetch: bool = False):
         """One training step.  On a GPU the host-side preparation of step+1 (LR/step scalars, parse kernels of the
         already staged batch, start of the next staging copy) is ENQUEUED right after this step's compute has been
         launched, so it overlaps the GPU work; stream order keeps it behind this step's kernels."""
@@ -269,6 +269,38 @@ class Executor:
             self._feed(self.train_net, True)
         self._prefed_step = -1
         self._run_compute(step)
+        res = self._fetch_metrics_async(step) if _fetch else None
+        self._prefeed_next(step)
+        return res
+
+    def train_one_batch_async(self, step: int) -> "StepResult":
+        """``train_one_batch`` that also starts a device->host copy of the loss layers' metrics (into a ring of
+        pinned slots, right behind the step's last kernel) and returns a handle; ``handle.result()`` blocks until
+        that copy has landed.  Calling it for step i+1 BEFORE asking for step i's result keeps the GPU busy while the
+        host reads: every step's result is still read, one step late (used by bench.py's end-to-end region)."""
+        return self.train_one_batch(step, _fetch=True)
+
+    def _fetch_metrics_async(self, step: int) -> "StepResult":
+        layers = self.train_net.losslayers
+        if not hasattr(self, "_metric_ring"):
+            n = sum(l.metric.numel() for l in layers)
+            pin = ctx().device.type == "cuda"
+            self._metric_ring = [torch.zeros(max(n, 1), dtype=torch.float32, pin_memory=pin) for _ in range(8)]
+            self._metric_events = [torch.cuda.Event() if pin else None for _ in range(8)]
+            self._metric_slot = 0
+        k = self._metric_slot
+        self._metric_slot = (k + 1) % len(self._metric_ring)
+        buf, off = self._metric_ring[k], 0
+        for l in layers:
+            m = l.metric.reshape(-1)
+            buf[off:off + m.numel()].copy_(m, non_blocking=True)
+            off += m.numel()
+        ev = self._metric_events[k]
+        if ev is not None:
+            ev.record()
+        return StepResult(step, buf, ev)
+
+    def _prefeed_next(self, step: int) -> None:
         if self._pipeline_feed and not self.stop_now(step + 1) and not self.test_now(step + 1) \
                 and not self.validate_now(step + 1):
             self.pm.begin_step(step + 1)
@@ -392,6 +424,22 @@ class Executor:
         self.step = step
         self._join_prefetch()
         return step
+
+
+class StepResult:
+    """Handle for the metrics of one step (``Executor.train_one_batch_async``).  At most 8 may be outstanding."""
+
+    def __init__(self, step: int, buf: torch.Tensor, event):
+        self.step, self._buf, self._event = step, buf, event
+
+    def ready(self) -> bool:
+        return self._event is None or self._event.query()
+
+    def result(self) -> torch.Tensor:
+        """Host tensor with the loss layers' metrics of this step (loss, accuracy, ...), blocking until it arrived."""
+        if self._event is not None:
+            self._event.synchronize()
+        return self._buf
 
 
 class HogwildGroup:

@@ -243,3 +243,31 @@ def test_checkpoint_roundtrip_with_optimizer_state(tmp_path):
     ck = S.ParamCheckpoint(); ck.ParseFromString(open(path, "rb").read())
     assert ck.step == 4 and ck.param[0].name == "fc1/weight" and len(ck.param[0].blob) > 1
     device.reset_context()
+
+
+def test_train_one_batch_async_matches_sync():
+    """The pipelined result handle returns the same per-step metrics as reading the loss layer after each step."""
+    from singa_b200 import device
+    from singa_b200.models import configs
+    from singa_b200.worker import Worker
+    device.set_context("cpu", "torch")
+    m = configs.mnist_mlp(batch=8, train_steps=5, hidden=(16,))
+    m.display_frequency = 0
+    ref = []
+    w = Worker(seed=3); w.build(m); w.executor.setup()
+    for step in range(5):
+        w.executor.ticks += 1
+        w.executor.train_one_batch(step)
+        ref.append(w.train_net.losslayers[0].metric.reshape(-1).clone())
+    w2 = Worker(seed=3); w2.build(m); w2.executor.setup()
+    got, pending = [], None
+    for step in range(5):
+        w2.executor.ticks += 1
+        h = w2.executor.train_one_batch_async(step)
+        if pending is not None:
+            got.append(pending.result().clone())
+        pending = h
+    got.append(pending.result().clone())
+    assert pending.ready() and pending.step == 4
+    for a, b in zip(ref, got):
+        torch.testing.assert_close(a, b[:a.numel()])
