@@ -443,7 +443,9 @@ class StepResult:
 
 
 class HogwildGroup:
-    """Several executor threads inside one process training ONE shared set of parameters (CPU path).
+    """Several executor threads inside one process training ONE shared set of parameters.  On a GPU every thread
+    issues its replica's kernels on its own CUDA stream (hogwild = unordered updates of the shared master weights
+    across streams; the bf16 operand mirror is refreshed right after each update).
 
     Reference: ``Worker::Start`` spawns ``nthreads_per_procs - 1`` extra ``Executor`` threads
     (src/worker/worker.cc:33-39) and ``ParamManager::UpdateParam`` either lets every thread update the shared
@@ -465,8 +467,30 @@ class HogwildGroup:
         self._agg = {}
         self._arrived = {}
         self.updates = 0
+        self._cuda = ctx().device.type == "cuda"
+        self._streams = [torch.cuda.Stream() for _ in range(nthreads)] if self._cuda else None
+        self.errors: List[BaseException] = []
+
+    def _apply(self, upd, step: int, o, grad_scale: float = 1.0) -> None:
+        upd.update(step, o, grad_scale=grad_scale)
+        if getattr(o, "data16", None) is not None:        # native path: GEMM operands are read from the bf16 mirror
+            o.data16.copy_(o.data)
+            if getattr(o, "pack16", None) is not None:
+                o.pack16()
 
     def _thread(self, tid: int, steps: int, start: int) -> None:
+        try:
+            if self._cuda:
+                torch.cuda.set_device(ctx().device)
+                with torch.cuda.stream(self._streams[tid]):
+                    self._thread_body(tid, steps, start)
+                    self._streams[tid].synchronize()
+            else:
+                self._thread_body(tid, steps, start)
+        except BaseException as e:  # noqa: BLE001 - surfaced by run()
+            self.errors.append(e)
+
+    def _thread_body(self, tid: int, steps: int, start: int) -> None:
         net = self.replicas[tid]
         upd = self.worker.pm.updater
         owners = [p if p.is_owner else p.owner for p in net.params]
@@ -485,9 +509,11 @@ class HogwildGroup:
                 for p, o in zip(l.get_params(), [q if q.is_owner else q.owner for q in l.get_params()]):
                     if self.hogwild:
                         o.grad = p.grad                   # lock-free: this thread's gradient, shared value
-                        upd.update(step, o)
+                        self._apply(upd, step, o)
                         self.updates += 1
                     else:
+                        if self._cuda:                    # this thread's gradient must be complete before it is
+                            torch.cuda.current_stream().synchronize()   # summed on whichever stream gets the lock
                         with self._lock:
                             acc = self._agg.get(id(o))
                             self._agg[id(o)] = p.grad.clone() if acc is None else acc.add_(p.grad)
@@ -495,8 +521,10 @@ class HogwildGroup:
                             if self._arrived[id(o)] == self.nthreads:
                                 o.grad = self._agg.pop(id(o))
                                 self._arrived[id(o)] = 0
-                                upd.update(step, o, grad_scale=1.0 / self.nthreads)
+                                self._apply(upd, step, o, grad_scale=1.0 / self.nthreads)
                                 self.updates += 1
+                            if self._cuda:
+                                torch.cuda.current_stream().synchronize()
 
     def run(self, steps: int, start: int = 0) -> None:
         ths = [threading.Thread(target=self._thread, args=(t, steps, start)) for t in range(self.nthreads)]
@@ -504,6 +532,8 @@ class HogwildGroup:
             t.start()
         for t in ths:
             t.join()
+        if self.errors:
+            raise self.errors[0]
 
 
 class Worker:
@@ -600,8 +630,7 @@ class Worker:
                 pm.get_params_from_servers()
         start = max(self.start_step, warm)
         nthreads = self.cluster.nthreads_per_procs if self.cluster is not None else 1
-        if nthreads > 1 and ctx().device.type == "cpu" and not self.train_net.param_shares \
-                and pm.backend_name == "local":
+        if nthreads > 1 and not self.train_net.param_shares and pm.backend_name == "local":
             group = HogwildGroup(self, nthreads, pm.hogwild and model.updater.hogwild)
             group.run(max(0, model.train_steps - start), start)
             log.error("\t%s", Performance(self.train_net).to_string())

@@ -91,3 +91,39 @@ def test_training_reduces_loss_native_graph():
     assert ex._graph is not None, "the step was not captured in a CUDA graph"
     assert losses[-1] < losses[0] * 0.7, losses
     device.reset_context()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hogwild", [True, False])
+def test_hogwild_threads_on_streams(tmp_path, hogwild):
+    """nthreads_per_procs > 1 on a GPU: one CUDA stream per executor thread, shared master weights + bf16 mirror."""
+    from singa_b200 import device
+    from singa_b200.cluster import Cluster
+    from singa_b200.models import configs
+    from singa_b200.proto import schema as S
+    from singa_b200.worker import HogwildGroup, Worker
+    device.set_context("cuda:0", "native")
+    m = configs.mnist_mlp(batch=64, train_steps=30, hidden=(64,))
+    m.display_frequency = 0
+    m.updater.base_learning_rate = 0.05
+    m.updater.hogwild = hogwild
+    cp = S.ClusterProto()
+    cp.nworkers, cp.nservers, cp.nthreads_per_procs = 1, 0, 3
+    cp.workspace = str(tmp_path)
+    Cluster.reset()
+    w = Worker(Cluster.get(cp, "", 0))
+    w.build(m)
+    p0 = w.train_net.params[0]
+    w0 = p0.data.clone()
+    g = HogwildGroup(w, 3, hogwild)
+    assert g.replicas[1].params[0].data.data_ptr() == p0.data.data_ptr()
+    assert g.replicas[1].params[0].data16.data_ptr() == p0.data16.data_ptr()
+    g.run(30)
+    torch.cuda.synchronize()
+    assert g.updates == (30 * 3 * len(w.train_net.params) if hogwild else 30 * len(w.train_net.params))
+    assert not torch.equal(p0.data, w0)
+    torch.testing.assert_close(p0.data16.float(), p0.data.to(torch.bfloat16).float())   # mirror follows the master
+    losses = [float(n.losslayers[0].metric[0]) / 30 for n in g.replicas]
+    assert all(l < 2.3 for l in losses), losses
+    Cluster.reset()
+    device.reset_context()
