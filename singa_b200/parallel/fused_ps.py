@@ -164,6 +164,7 @@ class FusedExchange:
                 flag_list = torch.tensor([int(a) for a in addrs], dtype=torch.int64, device=ctx().device)
                 l.pull_wait = (flag_list, self.wait_seq[i:i + 1].data_ptr())
         self.launches = 0
+        self._used_comms = set()
         # the fp32 master copy of a parameter is current only on its server; every other consumer (bias in the GEMM
         # epilogue, repacked conv weights) must read this rank's bf16 mirror
         if self.world > 1:
@@ -181,6 +182,7 @@ class FusedExchange:
         # gradient on the compute stream, parameter gradient on its side stream): the compute stream goes
         # straight on to the layer below
         comm = self.comms[i % len(self.comms)]
+        self._used_comms.add(i % len(self.comms))
         comm.wait_stream(main)
         if side_stream is not None:
             comm.wait_stream(side_stream)
@@ -238,8 +240,11 @@ class FusedExchange:
                 p.pack16()
 
     def end_step(self, step: int) -> None:
-        for c in self.comms:
-            torch.cuda.current_stream().wait_stream(c)
+        # only streams that took work this step: joining an idle stream during graph capture is an error
+        # ("dependency created on uncaptured work in another stream")
+        for k in sorted(self._used_comms):
+            torch.cuda.current_stream().wait_stream(self.comms[k])
+        self._used_comms.clear()
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
         """Element ranges of the arena whose fp32 master copy (and optimizer state) lives on this rank."""

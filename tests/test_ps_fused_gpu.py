@@ -102,3 +102,19 @@ def test_gemm_fused_wait_passes_when_version_reached():
                  seq.data_ptr()))
     torch.cuda.synchronize()
     torch.testing.assert_close(out, a.float() @ b.float(), rtol=2e-3, atol=2e-2)
+
+
+@pytest.mark.parametrize("config", ["lenet", "mnist_mlp"])
+def test_fused_exchange_graph_capture_world1(config):
+    """The whole fused step (forward with fused pull waits, backward, bucketed push) must capture into a CUDA graph —
+    a one-bucket net (lenet) once failed because an idle comm stream was joined during capture."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PYTHONPATH=root)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_PORT"):
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "fused_world1_check.py"), config], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "PASS fused world=1" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
