@@ -144,28 +144,40 @@ class Param:
     def to_bytes(self) -> bytes:
         return self.data.detach().to("cpu", torch.float32).contiguous().numpy().tobytes()
 
-    def from_bytes(self, payload: bytes) -> None:
+    def from_bytes(self, payload) -> None:
+        """``payload``: any buffer of ``size`` float32 values (bytes, memoryview, zmq.Frame.buffer).  One copy."""
         arr = np.frombuffer(payload, dtype=np.float32)
         if arr.size != self.size:
             raise ValueError(f"param {self.name}: payload has {arr.size} floats, expected {self.size}")
-        self.data.copy_(torch.from_numpy(arr.copy()).view(self.shape).to(self.data.device))
+        if self.data.device.type == "cpu" and self.data.is_contiguous() and self.data.dtype == torch.float32:
+            np.copyto(self.data.numpy().reshape(-1), arr)          # straight into the blob, no temporaries
+        else:
+            self.data.copy_(torch.from_numpy(arr.copy()).view(self.shape).to(self.data.device))
+
+    def to_buffer(self):
+        """The value as a buffer for a zero-copy send: a view of the blob itself on the CPU (the caller must send it
+        before the next update of this parameter), a host copy otherwise."""
+        if self.data.device.type == "cpu" and self.data.is_contiguous() and self.data.dtype == torch.float32:
+            return memoryview(self.data.detach().numpy().reshape(-1)).cast("B")
+        return self.to_bytes()
 
     # server side: kPut stores the payload, kGet returns the value, kUpdate replaces the value and echoes it
-    def handle_put_msg(self, payload: bytes, shape: Optional[Sequence[int]] = None) -> None:
-        n = len(payload) // 4
+    def handle_put_msg(self, payload, shape: Optional[Sequence[int]] = None) -> None:
+        n = memoryview(payload).nbytes // 4
         if self.data is None or self.size != n:
             self.shape = list(shape) if shape else [n]
             self.data = torch.zeros(self.shape, dtype=torch.float32, device="cpu")
         self.from_bytes(payload)
 
-    def handle_get_msg(self) -> bytes:
+    def handle_get_msg(self):
         return self.to_bytes()
 
-    def handle_update_msg(self, payload: bytes) -> bytes:
-        """Stack-B placeholder semantics: replace and echo (src/utils/param.cc:57-61)."""
+    def handle_update_msg(self, payload):
+        """Stack-B placeholder semantics: replace and echo (src/utils/param.cc:57-61).  The echo IS the received
+        buffer — identical bytes, so the reply needs no second copy of the tensor."""
         self.from_bytes(payload)
         self.version += 1
-        return self.to_bytes()
+        return payload
 
     # sync protocol (overridden)
     def handle_sync_msg(self, control: str, payload: bytes):

@@ -34,8 +34,10 @@ class PMClient:
         self.shard = shard
         self.results: Dict[int, bytes] = {}
 
-    def _send(self, mtype: int, pid: int, content: bytes = b"") -> None:
-        self.sock.send_multipart([str(mtype).encode(), str(pid).encode(), content])
+    def _send(self, mtype: int, pid: int, content=b"") -> None:
+        # zero-copy for tensor payloads: ``content`` may be bytes, a memoryview or a contiguous numpy array (the
+        # caller must not modify it until the matching Collect returned, as with the reference's zframe ownership)
+        self.sock.send_multipart([str(mtype).encode(), str(pid).encode(), content], copy=False)
 
     def put(self, pid: int, payload: bytes) -> None:
         if self.shard is not None and self.shard.is_local(pid):
@@ -60,8 +62,8 @@ class PMClient:
         if pid in self.results:
             return self.results.pop(pid)
         while self.sock.poll(timeout_ms):
-            frames = self.sock.recv_multipart()
-            mtype, rid, content = int(frames[0]), int(frames[1]), frames[2]
+            frames = self.sock.recv_multipart(copy=False)
+            mtype, rid, content = int(frames[0].bytes), int(frames[1].bytes), frames[2].buffer
             if mtype == kData:
                 self.results[rid] = content
             if rid == pid:
@@ -126,16 +128,17 @@ class SingaClient:
         while not self._stop.is_set():
             events = dict(poller.poll(20))
             if events.get(backend):
-                frames = backend.recv_multipart()          # [tid][type][paramId][content]
-                pid = int(frames[2])
-                if int(frames[1]) == kStop:
+                frames = backend.recv_multipart(copy=False)          # [tid][type][paramId][content]
+                pid = int(frames[2].bytes)
+                if int(frames[1].bytes) == kStop:
                     for s in servers:
-                        s.send_multipart([frames[0], frames[1], frames[2]])
+                        s.send_multipart([frames[0], frames[1], frames[2]], copy=False)
                 else:
-                    servers[pid % len(servers)].send_multipart(frames)
+                    servers[pid % len(servers)].send_multipart(frames, copy=False)   # frames forwarded, not copied
             for s in servers:
                 if events.get(s):
-                    backend.send_multipart(s.recv_multipart())   # [tid][kData][paramId][content] -> thread tid
+                    # [tid][kData][paramId][content] -> thread tid
+                    backend.send_multipart(s.recv_multipart(copy=False), copy=False)
         for s in (backend, *servers):
             s.close(0)
 
@@ -163,7 +166,7 @@ def client_thread(client: SingaClient, tid: int, sizes: List[int], rounds: int, 
     params = [rng.standard_normal(n, dtype=np.float32) * 0.01 for n in sizes]
     if is_putter:
         for i, p in enumerate(params):
-            pm.put(i, p.tobytes())
+            pm.put(i, p)
     for i in range(len(params)):
         pm.get(i)
     for i in range(len(params)):
@@ -172,7 +175,7 @@ def client_thread(client: SingaClient, tid: int, sizes: List[int], rounds: int, 
     for _ in range(rounds):
         t0 = time.monotonic()
         for i, p in enumerate(params):
-            pm.update(i, p.tobytes())
+            pm.update(i, p)
         for i in range(len(params)):
             pm.collect_blocking(i)
         times.append((time.monotonic() - t0) * 1e3)

@@ -106,12 +106,14 @@ class SingaServer:
         while not self._stop.is_set():
             if not dict(poller.poll(50)).get(backend):
                 continue
-            frames = backend.recv_multipart()
-            ident, tid = frames[0], frames[1]
+            # zero-copy: tensor payloads stay in the zmq frames they arrived in (a Put / Update copies them once,
+            # into the parameter blob; the echo of an Update re-sends the received frame)
+            frames = backend.recv_multipart(copy=False)
+            ident, tid = frames[0].bytes, frames[1].bytes
             rest = frames[2:]
             if tid == REQUEUE_ID:
-                ident, tid, rest = rest[0], rest[1], rest[2:]
-            mtype, pid = int(rest[0]), int(rest[1])
+                ident, tid, rest = rest[0].bytes, rest[1].bytes, rest[2:]
+            mtype, pid = int(rest[0].bytes), int(rest[1].bytes)
             content = rest[2] if len(rest) > 2 else b""
             if mtype == kStop:
                 self._stop.set()
@@ -119,9 +121,9 @@ class SingaServer:
             self.nrequests += 1
             to_backend, to_requeue = dispatch[mtype](pid, ident, tid, content)
             if to_backend is not None:
-                backend.send_multipart(to_backend)
+                backend.send_multipart(to_backend, copy=False)
             if to_requeue is not None:
-                frontend.send_multipart(to_requeue)
+                frontend.send_multipart(to_requeue, copy=False)
         backend.close(0)
         frontend.close(0)
 
@@ -149,18 +151,18 @@ class SingaServer:
         while not self._stop.is_set():
             events = dict(poller.poll(50))
             if events.get(frontend):
-                backend.send_multipart(frontend.recv_multipart())
+                backend.send_multipart(frontend.recv_multipart(copy=False), copy=False)
             if events.get(backend):
-                frames = backend.recv_multipart()
-                first, msg = frames[0], frames[1:]
+                frames = backend.recv_multipart(copy=False)
+                first, msg = frames[0].bytes, frames[1:]
                 if first == SYNC_MSG:
                     # [wid][tid][kData][pid][content] -> neighbours get [tid][kSyncRequest][pid][content]
                     for s in nbs:
-                        s.send_multipart([msg[1], str(kSyncRequest).encode(), *msg[3:]])
-                frontend.send_multipart(msg)
+                        s.send_multipart([msg[1], str(kSyncRequest).encode(), *msg[3:]], copy=False)
+                frontend.send_multipart(msg, copy=False)
             for s in nbs:
                 if events.get(s):
-                    backend.send_multipart(s.recv_multipart())
+                    backend.send_multipart(s.recv_multipart(copy=False), copy=False)
         for t in threads:
             t.join(2)
         for s in (frontend, backend, *nbs):
