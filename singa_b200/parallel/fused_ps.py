@@ -59,6 +59,30 @@ def shard_bounds(nchunks: int, world: int) -> List[Tuple[int, int]]:
     return [(min(r * per, nchunks), min((r + 1) * per, nchunks)) for r in range(world)]
 
 
+def make_buckets(layers, bucket_elems: int, chunk: int = 1024) -> List[List[str]]:
+    """Group parameter layers into push buckets.  ``layers``: [(name, first_chunk, nchunks)] in FORWARD order.  Walks
+    in backward order (last layer first) merging layers that are adjacent in the arena until a bucket holds at least
+    ``bucket_elems`` parameters; returns the buckets as lists of names in backward order, so ``bucket[-1]`` is the
+    layer whose gradient arrives last — the one that triggers the push.  A bucket always covers one contiguous chunk
+    range (a gap in the arena closes the current bucket)."""
+    buckets: List[List[str]] = []
+    cur: List[str] = []
+    cur_n, cur_lo = 0, None
+    for name, lo, n in reversed(list(layers)):
+        if cur and cur_lo != lo + n:
+            buckets.append(cur)
+            cur, cur_n = [], 0
+        cur.append(name)
+        cur_n += n * chunk
+        cur_lo = lo
+        if cur_n >= bucket_elems:
+            buckets.append(cur)
+            cur, cur_n = [], 0
+    if cur:
+        buckets.append(cur)
+    return buckets
+
+
 def symmetric_regions(total_elems: int, nlayers: int, world: int):
     """Regions of the symmetric heap for an arena of ``total_elems`` elements."""
     return [("grad", total_elems * 4), ("data16", total_elems * 2),
@@ -111,21 +135,9 @@ class FusedExchange:
         # 0.4425 ms at 8 GPUs / 0.374 at 2, against 0.454 / 0.380 with 2 M and 0.520 / 0.414 unbucketed); the bucket is
         # pushed when its LAST-visited (lowest) layer has its gradient.
         bucket_elems = int(os.environ.get("SINGA_B200_PUSH_BUCKET", str(6_000_000)))
-        self.buckets: List[List] = []
-        cur, cur_n = [], 0
-        for l in reversed(self.layers):
-            lo, n = pm.layer_ranges[l.name]
-            contiguous = not cur or pm.layer_ranges[cur[-1].name][0] == lo + n
-            if cur and not contiguous:
-                self.buckets.append(cur)
-                cur, cur_n = [], 0
-            cur.append(l)
-            cur_n += n * 1024
-            if cur_n >= bucket_elems:
-                self.buckets.append(cur)
-                cur, cur_n = [], 0
-        if cur:
-            self.buckets.append(cur)
+        names = make_buckets([(l.name, *pm.layer_ranges[l.name]) for l in self.layers], bucket_elems)
+        by_name = {l.name: l for l in self.layers}
+        self.buckets: List[List] = [[by_name[n] for n in b] for b in names]
         self.bucket_of = {l.name: b for b, ls in enumerate(self.buckets) for l in ls}
         self.trigger = {ls[-1].name for ls in self.buckets}          # lowest layer: visited last in backward
         self.lidx = dict(self.bucket_of)                             # flag / scratch index of a layer = its bucket
