@@ -54,11 +54,13 @@ def discover() -> dict:
     return info
 
 
-def launch(cluster_conf: str, model_conf: str, extra: List[str], workdir: str = ".", timeout: float = 0) -> int:
+def launch(cluster_conf: str, model_conf: str, extra: List[str], workdir: str = "", timeout: float = 0) -> int:
     from .proto import schema as S
     from .utils.common import read_proto_from_text_file
     pc = read_proto_from_text_file(cluster_conf, S.ClusterProto())
     nprocs = pc.nworkers + pc.nservers
+    workdir = workdir or pc.workspace or "."          # the generated hostfile lives with the job's other artefacts
+    os.makedirs(workdir, exist_ok=True)
     hostfile = os.path.join(workdir, "hostfile")
     with open(hostfile, "w") as f:
         f.write("\n".join(["127.0.0.1"] * nprocs) + "\n")
@@ -104,7 +106,7 @@ def main(argv=None) -> int:
     ap.add_argument("--discover", action="store_true")
     ap.add_argument("--cluster_conf", default="examples/mnist/cluster.conf")
     ap.add_argument("--model_conf", default="examples/mnist/mlp.conf")
-    ap.add_argument("--workdir", default=".")
+    ap.add_argument("--workdir", default="", help="where the generated hostfile goes (default: the cluster workspace)")
     ap.add_argument("--timeout", type=float, default=0)
     args, extra = ap.parse_known_args(argv)
     if args.discover:
