@@ -101,4 +101,6 @@ class ZmqExchange:
             self._handle(frames)
         for s in range(self.nservers):
             self.router.send([str(kStop).encode()], s)
-        self.router.close()
+        # bounded linger: a job shorter than the warm-up ends right after put_all, with the stop message queued behind
+        # the parameter payloads — closing with linger 0 dropped it and the servers never exited
+        self.router.close(linger_ms=10000)

@@ -86,5 +86,8 @@ class Router:
         self.last_recv_node = frames[0]
         return frames[1:]
 
-    def close(self) -> None:
-        self.sock.close(0)
+    def close(self, linger_ms: int = 0) -> None:
+        """``linger_ms`` > 0 lets queued messages (e.g. the final kStop behind 48 MB of kPut payloads) reach the peer
+        before the socket goes away; 0 drops whatever is still queued (the reference sets zsocket linger 0 to avoid
+        hangs on exit, src/worker/pm_client.cc:64)."""
+        self.sock.close(linger_ms)

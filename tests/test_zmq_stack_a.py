@@ -42,6 +42,25 @@ def test_two_workers_one_server(tmp_path, param_type, port):
     assert "Output from loss layer" in r.stderr
 
 
+def test_job_shorter_than_the_warmup_still_stops_the_server(tmp_path):
+    """train_steps < warmup_steps: the job ends right after the initial kPut of every parameter; the kStop queued behind
+    those payloads must still reach the server (it was dropped when the worker closed its socket with linger 0, and
+    the launcher then waited for the server forever)."""
+    big = MODEL.replace("train_steps: 24", "train_steps: 3").replace("warmup_steps: 4", "warmup_steps: 60") \
+               .replace("num_output: 32", "num_output: 4096") \
+               .replace("synthetic_shape: 12 synthetic_shape: 12", "synthetic_shape: 64 synthetic_shape: 64")
+    # 4096 x 4096 weights: 67 MB of kPut payload sit in the socket queue when the stop message is sent
+    (tmp_path / "model.conf").write_text(big % "Elastic")
+    (tmp_path / "cluster.conf").write_text(
+        f'nworkers: 1\nnservers: 1\nnthreads_per_server: 2\nstart_port: 17923\nworkspace: "{tmp_path}"\n')
+    env = dict(os.environ, PYTHONPATH=ROOT, SINGA_B200_BACKEND="torch", CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, "-m", "singa_b200.launch", f"--cluster_conf={tmp_path}/cluster.conf",
+                        f"--model_conf={tmp_path}/model.conf", "--timeout=90", "--device=cpu"],
+                       env=env, capture_output=True, text=True, timeout=150, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert (tmp_path / "hostfile").exists()          # generated hostfile lives in the job workspace by default
+
+
 def test_router_ping_pong_barrier():
     """dist_test/test_router.cc: the server's bind returns only after every worker pinged."""
     import threading
