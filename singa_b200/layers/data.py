@@ -191,6 +191,12 @@ class DataLayer(Layer):
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
                 self.group_id, self.ngroups = dist.get_rank(), dist.get_world_size()
+            else:
+                # ZeroMQ jobs have no process group: the Cluster singleton knows this worker's group
+                from ..cluster import Cluster
+                c = Cluster._instance
+                if c is not None and c.am_i_worker() and c.ngroups > 1:
+                    self.group_id, self.ngroups = c.groupid, c.ngroups
         except Exception:  # noqa: BLE001
             pass
         if self.group_id:
