@@ -592,6 +592,24 @@ class Worker:
         self.executor = Executor(0, model, self.cluster, self.pm, self.train_net, self.test_net,
                                  self.validation_net, self.use_graph)
         self.perf = Performance(self.train_net)
+        self._dump_graphs()
+
+    def _dump_graphs(self) -> None:
+        """Node-link JSON of every phase net into ``<workspace>/vis`` (the reference creates that folder,
+        src/utils/cluster.cc:29-32, and logs ``NeuralNet::ToString()`` at INFO, src/worker/neuralnet.cc:109,195);
+        ``python script/graph.py <workspace>/vis/train.json`` turns it into Graphviz DOT."""
+        if self.cluster is None or self.cluster.groupid != 0 or self.cluster.group_procsid != 0:
+            return
+        try:
+            folder = self.cluster.visualization_folder
+            folder = folder() if callable(folder) else folder
+            os.makedirs(folder, exist_ok=True)
+            for name, net in (("train", self.train_net), ("test", self.test_net), ("validation", self.validation_net)):
+                if net is not None:
+                    with open(os.path.join(folder, f"{name}.json"), "w") as fh:
+                        fh.write(net.to_string())
+        except Exception as e:  # noqa: BLE001 - visualisation must never stop a job
+            log.error("could not write the net graphs: %s", e)
 
     def resume(self) -> int:
         """Load the latest Param-proto checkpoint (if the model names one or the workspace holds one) and
