@@ -174,7 +174,8 @@ bool get_varint(const uint8_t*& p, const uint8_t* end, uint64_t* out) {
 
 // Caffe Datum { channels = 1, height = 2, width = 3, data = 4 (bytes), label = 5, float_data = 6, encoded = 7 }.
 // pixels may be null (shape / label query only).
-bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim, int* label, int* chw) {
+bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim, int* label, int* chw,
+                  bool* encoded = nullptr) {
   const uint8_t* end = p + len;
   long long nfloat = 0;
   bool got = false;
@@ -186,6 +187,7 @@ bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim
       if (!get_varint(p, end, &v)) return false;
       if (field >= 1 && field <= 3 && chw != nullptr) chw[field - 1] = static_cast<int>(v);
       if (field == 5 && label != nullptr) *label = static_cast<int>(v);
+      if (field == 7 && encoded != nullptr) *encoded = v != 0;
     } else if (wire == 2) {
       if (!get_varint(p, end, &v) || static_cast<uint64_t>(end - p) < v) return false;
       if (field == 4 && v > 0) {
@@ -300,9 +302,11 @@ extern "C" int sg_lmdb_first_shape(void* h, int* chw) {
   SG_REQUIRE(cursor_first(e), "sg_lmdb_first_shape: empty or corrupt database");
   chw[0] = chw[1] = chw[2] = 0;
   int label = 0;
-  SG_REQUIRE(decode_datum(e->val, e->vlen, nullptr, 0, &label, chw), "sg_lmdb_first_shape: first value is not a Datum");
+  bool encoded = false;
+  SG_REQUIRE(decode_datum(e->val, e->vlen, nullptr, 0, &label, chw, &encoded),
+             "sg_lmdb_first_shape: first value is not a Datum");
   e->positioned = false;
-  return 0;
+  return encoded ? 2 : 0;
 }
 
 // Decodes the next `batch` Datum records (wrapping around at the end of the database, layer.cc:300-306) into
@@ -316,8 +320,15 @@ extern "C" int sg_lmdb_read_datum_batch(void* h, void* pixels_u8, int* labels, i
     if (rc == 0) rc = cursor_next(e);   // wrapped: start over
     SG_REQUIRE(rc == 1, "sg_lmdb_read_datum_batch: corrupt page structure");
     int label = 0;
-    SG_REQUIRE(decode_datum(e->val, e->vlen, px + static_cast<long long>(i) * dim, dim, &label, nullptr),
+    bool encoded = false;
+    SG_REQUIRE(decode_datum(e->val, e->vlen, px + static_cast<long long>(i) * dim, dim, &label, nullptr, &encoded),
                "sg_lmdb_read_datum_batch: record %d is not a Datum with pixel data", i);
+    if (encoded) {
+      // compressed image bytes (Datum.encoded): not decodable here; the caller re-reads this record through an image
+      // decoder.  Step back so the record is not consumed.
+      set_error("sg_lmdb_read_datum_batch: record %d holds an encoded image", i);
+      return 2;
+    }
     labels[i] = label;
   }
   return 0;

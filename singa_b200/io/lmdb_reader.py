@@ -88,14 +88,33 @@ class LMDBEnv:
         return key, ctypes.string_at(vp, n.value)
 
     def first_shape(self) -> List[int]:
+        """{channels, height, width} declared by the first Datum; ``self.encoded`` tells whether its data field holds
+        a compressed image (``Datum.encoded``) instead of raw pixels."""
         chw = (ctypes.c_int * 3)()
-        native.check(self.lib.sg_lmdb_first_shape(self.h, chw), "sg_lmdb_first_shape")
+        rc = self.lib.sg_lmdb_first_shape(self.h, chw)
+        self.encoded = rc == 2
+        if rc not in (0, 2):
+            native.check(rc, "sg_lmdb_first_shape")
         return [int(chw[0]), int(chw[1]), int(chw[2])]
 
     def read_datum_batch(self, pixels: np.ndarray, labels: np.ndarray) -> None:
         assert pixels.dtype == np.uint8 and labels.dtype == np.int32 and pixels.flags.c_contiguous
         native.check(self.lib.sg_lmdb_read_datum_batch(self.h, pixels.ctypes.data, labels.ctypes.data,
                                                        pixels.shape[0], pixels.shape[1]), "sg_lmdb_read_datum_batch")
+
+
+def decode_image(buf: bytes) -> np.ndarray:
+    """Compressed image bytes -> {3, H, W} uint8 in Caffe's channel order (BGR), via OpenCV or Pillow."""
+    try:
+        import cv2
+        img = cv2.imdecode(np.frombuffer(buf, dtype=np.uint8), cv2.IMREAD_COLOR)
+        if img is None:
+            raise ValueError("cv2.imdecode failed")
+    except ImportError:
+        import io
+        from PIL import Image
+        img = np.asarray(Image.open(io.BytesIO(buf)).convert("RGB"))[:, :, ::-1]
+    return np.ascontiguousarray(img.transpose(2, 0, 1))
 
 
 class LMDBSource(BatchSource):
@@ -106,11 +125,31 @@ class LMDBSource(BatchSource):
                 "synthetic_shape: ... }` or export SINGA_B200_SYNTHETIC=1 to substitute synthetic records.")
         self.env = LMDBEnv(path)
         c, h, w = self.env.first_shape()
+        self.encoded = self.env.encoded
+        if self.encoded:                       # compressed images: the shape is that of the first decoded image
+            self.env.seek_to_first()
+            c, h, w = self._decode_record(self.env.next()[1])[0].shape
         self.sample_shape = [c, h, w] if c > 1 else [h, w]
         self.env.seek_to_first()
 
+    @staticmethod
+    def _decode_record(value: bytes):
+        d = S.Datum()
+        d.ParseFromString(value)
+        return decode_image(d.data), int(d.label)
+
     def next_batch(self, pixels, labels):
-        self.env.read_datum_batch(pixels, labels)
+        if not self.encoded:
+            self.env.read_datum_batch(pixels, labels)     # native: raw pixels memcpy'd into the batch buffers
+            return
+        shape = tuple(self.sample_shape) if len(self.sample_shape) == 3 else (1, *self.sample_shape)
+        for i in range(pixels.shape[0]):                  # encoded Datums: per-record image decode on the host
+            kv = self.env.next() or self.env.next()
+            img, labels[i] = self._decode_record(kv[1])
+            if img.shape != shape:
+                import cv2
+                img = cv2.resize(img.transpose(1, 2, 0), (shape[2], shape[1])).transpose(2, 0, 1)
+            pixels[i, :] = img.reshape(-1)
 
     def skip(self, n):
         for _ in range(n):

@@ -107,3 +107,28 @@ def test_loader_tool_writes_lmdb(tmp_path):
     lb = np.zeros(5, dtype=np.int32)
     src.next_batch(px, lb)
     assert px.any() and (lb >= 0).all() and (lb < 10).all()
+
+
+def test_encoded_datums_are_decoded_on_the_host(tmp_path):
+    """Datum.encoded = true (convert_imageset --encoded): the native batch path refuses, the source falls back to an
+    image decoder; PNG is lossless so the pixels must come back exactly (BGR channel order)."""
+    cv2 = pytest.importorskip("cv2")
+    from singa_b200.proto import schema as S
+    rng = np.random.default_rng(7)
+    imgs = [rng.integers(0, 256, size=(3, 10, 12), dtype=np.uint8) for _ in range(5)]
+    items = []
+    for i, im in enumerate(imgs):
+        ok, buf = cv2.imencode(".png", np.ascontiguousarray(im.transpose(1, 2, 0)))
+        assert ok
+        d = S.Datum()
+        d.data, d.label, d.encoded = buf.tobytes(), i % 3, True
+        items.append((f"{i:08d}".encode(), d.SerializeToString()))
+    path = str(tmp_path / "enc")
+    write_lmdb(path, items)
+    src = LMDBSource(path)
+    assert src.encoded and src.sample_shape == [3, 10, 12]
+    px = np.zeros((7, 360), dtype=np.uint8)
+    lb = np.zeros(7, dtype=np.int32)
+    src.next_batch(px, lb)                                           # 7 > 5 records: wraps around
+    for i in range(7):
+        assert lb[i] == (i % 5) % 3 and np.array_equal(px[i], imgs[i % 5].reshape(-1))
