@@ -132,3 +132,23 @@ def test_encoded_datums_are_decoded_on_the_host(tmp_path):
     src.next_batch(px, lb)                                           # 7 > 5 records: wraps around
     for i in range(7):
         assert lb[i] == (i % 5) % 3 and np.array_equal(px[i], imgs[i % 5].reshape(-1))
+
+
+def test_value_sizes_around_the_overflow_threshold_and_deep_trees(tmp_path):
+    """Leaf nodes larger than nodemax (2038 bytes at 4 KB pages) move their value to overflow pages; 20 000 small
+    records need a three-level tree.  Raw values (not Datums) are read back through the cursor."""
+    rng = np.random.default_rng(11)
+    items = []
+    for i, n in enumerate(list(range(2000, 2060)) + [1, 4079, 4080, 4081, 8176, 20000]):
+        items.append((f"a{i:06d}".encode(), rng.integers(0, 256, size=n, dtype=np.uint8).tobytes()))
+    for i in range(20000):
+        items.append((f"b{i:07d}".encode(), bytes([i % 251]) * (1 + i % 40)))
+    path = str(tmp_path / "db")
+    write_lmdb(path, items)
+    env = LMDBEnv(path)
+    assert env.count() == len(items)
+    expect = sorted(items)
+    for k, v in expect:
+        kv = env.next()
+        assert kv is not None and kv[0] == k and kv[1] == v, k
+    assert env.next() is None
