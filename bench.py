@@ -37,6 +37,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16", "fp32-strict"],
+                    help="compute precision. fp32 (default; the reference computes in fp32): fp32 storage, tf32 tensor-core "
+                         "products, fp32 accumulation - ours = tcgen05 kind::tf32, torch = cuBLAS/cuDNN with TF32 allowed. "
+                         "bf16: bf16 operands, fp32 accumulation - ours = kind::f16, torch = autocast(bf16). "
+                         "fp32-strict (torch only): TF32 off, plain fp32 FMA kernels")
     ap.add_argument("--config", default="mnist_mlp")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the config's own)")
     ap.add_argument("--push-pull", default=os.environ.get("SINGA_B200_PUSH_PULL", "fused"),
@@ -138,7 +143,16 @@ def main():
     from singa_b200.worker import Worker
 
     backend_kind = "torch" if args.impl == "torch" else "native"
-    device.set_context(f"cuda:{local_rank}", backend_kind)
+    if args.impl == "ours" and args.dtype == "fp32-strict":
+        raise SystemExit("--dtype fp32-strict is a library-arm setting (tensor cores off); ours runs fp32 (tf32) or bf16")
+    device.set_context(f"cuda:{local_rank}", backend_kind, "bf16" if args.dtype == "bf16" else "fp32")
+    if args.impl == "torch":
+        from singa_b200.ops import reference as R
+        tf32 = args.dtype == "fp32"
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        torch.backends.cudnn.allow_tf32 = tf32
+        torch.backends.cudnn.benchmark = True
+        R.AUTOCAST_BF16 = args.dtype == "bf16"
 
     kw = {}
     if args.batch:
@@ -192,7 +206,7 @@ def main():
     for _ in range(max(args.warmup, 3)):
         step_device(step); step += 1
     barrier()
-    ws_bytes = w.pm.arena.total * (4 + 4 + 2) + sum(
+    ws_bytes = w.pm.arena.total * (4 + 4 + (2 if args.dtype == "bf16" else 0)) + sum(
         l.data.numel() * l.data.element_size() for l in net.layers if l.data is not None and l.data.is_cuda)
     flush = None
     if ws_bytes < L2_BYTES:
@@ -286,7 +300,8 @@ def main():
             "higher_is_better": True,
             "scaling": "weak",
             "vs_baseline": None,
-            "dtype": "bf16" if backend_kind == "native" else "fp32",
+            "dtype": {"fp32": "fp32 (tf32 tensor-core products, fp32 accumulate)", "bf16": "bf16",
+                      "fp32-strict": "fp32 (no tensor cores)"}[args.dtype],
             "data": "synthetic",
             "impl": args.impl,
             "config": {
@@ -297,7 +312,9 @@ def main():
                 "seq_len": None,
                 "parallelism": f"dp{world} (1 worker group + 1 server shard per GPU, sync push/pull: "
                                f"{exchange or 'local'})",
-                "precision": "bf16 operands, fp32 accumulate, fp32 master weights + optimizer state",
+                "precision": {"fp32": "fp32 activations/gradients/weights, tf32 tensor-core products, fp32 accumulate",
+                              "bf16": "bf16 operands, fp32 accumulate, fp32 master weights + optimizer state",
+                              "fp32-strict": "fp32 FMA, TF32 off"}[args.dtype],
                 "cuda_graph": ex._graph is not None,
                 "l2": ("per-step working set %.0f MB > 126 MB L2 (no flush needed)" % (ws_bytes / 2**20))
                       if flush is None else "L2 flushed (252 MB write) between timed steps, per-step events",

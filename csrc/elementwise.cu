@@ -327,15 +327,16 @@ __global__ void rgb_parse_kernel(const uint8_t* __restrict__ src, const float* _
   }
 }
 
-// 2-D bf16 copy that changes the row stride (used to pad a [rows][cols] matrix to a TMA-legal ld).
-__global__ void copy2d_bf16_kernel(const __nv_bfloat16* __restrict__ src, long long lds,
-                                   __nv_bfloat16* __restrict__ dst, long long ldd, int rows, int cols) {
+// 2-D copy that changes the row stride (used to pad a [rows][cols] matrix to a TMA-legal ld); T = 2- or 4-byte words.
+template <typename T>
+__global__ void copy2d_kernel(const T* __restrict__ src, long long lds, T* __restrict__ dst, long long ldd,
+                              int rows, int cols) {
   const long long total = static_cast<long long>(rows) * ldd;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
     const int r = static_cast<int>(i / ldd);
     const int c = static_cast<int>(i - static_cast<long long>(r) * ldd);
-    dst[i] = c < cols ? src[static_cast<long long>(r) * lds + c] : __float2bfloat16_rn(0.f);
+    dst[i] = c < cols ? src[static_cast<long long>(r) * lds + c] : static_cast<T>(0);
   }
 }
 
@@ -527,13 +528,21 @@ extern "C" int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, in
   return 0;
 }
 
-extern "C" int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
-                              void* stream) {
+extern "C" int sg_copy2d(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
+                         int is_bf16, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (rows <= 0 || cols <= 0) return 0;
-  SG_REQUIRE(ldd >= cols && lds >= cols, "sg_copy2d_bf16: leading dimensions too small");
-  copy2d_bf16_kernel<<<ew_grid(static_cast<long long>(rows) * ldd, 256), 256, 0, s>>>(
-      (const __nv_bfloat16*)src, lds, (__nv_bfloat16*)dst, ldd, rows, cols);
-  SG_CHECK_LAUNCH("copy2d_bf16");
+  SG_REQUIRE(ldd >= cols && lds >= cols, "sg_copy2d: leading dimensions too small");
+  const int grid = ew_grid(static_cast<long long>(rows) * ldd, 256);
+  if (is_bf16)   // bit copies: bf16 moves as 16-bit words, fp32 as 32-bit words
+    copy2d_kernel<unsigned short><<<grid, 256, 0, s>>>((const unsigned short*)src, lds, (unsigned short*)dst, ldd, rows, cols);
+  else
+    copy2d_kernel<unsigned int><<<grid, 256, 0, s>>>((const unsigned int*)src, lds, (unsigned int*)dst, ldd, rows, cols);
+  SG_CHECK_LAUNCH("copy2d");
   return 0;
+}
+
+extern "C" int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
+                              void* stream) {
+  return sg_copy2d(src, lds, dst, ldd, rows, cols, 1, stream);
 }

@@ -19,14 +19,23 @@ __device__ unsigned long long g_gemm_trace[32];
 #define SG_TRACE_W(i) do { if (threadIdx.x == 64 && nb == 0) SG_TRACE(i); } while (0)
 
 constexpr int BM = 128;
-constexpr int BK = 64;                       // 64 bf16 = one 128-byte swizzle row
-constexpr int UMMA_K = 16;
-constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
+// Operand element types.  Everything in the main loop is sized in BYTES: a k-block is one 128-byte swizzle row
+// (64 bf16 or 32 tf32/fp32 elements) and one tcgen05.mma consumes 32 bytes of K (UMMA_K = 16 bf16 or 8 tf32), so
+// the two precisions share tile sizes, stage counts and descriptors and differ only in the element counts below,
+// the tensor-map data type and the MMA kind.  tf32 operands are plain fp32 in memory (the reference computes in
+// fp32, src/worker/layer.cc:186-213); the tensor core reads the upper 19 bits.
+template <int EB> struct Elem {                // EB = bytes per operand element: 2 (bf16) or 4 (tf32)
+  static constexpr int BK = 128 / EB;          // elements per k-block
+  static constexpr int UMMA_K = 32 / EB;       // elements per MMA instruction
+  static constexpr int MN_BOX = 128 / EB;      // MN-major operand: elements per 128-byte row of a smem box
+  static constexpr int MN_BOX_BYTES = BK * 128;  // one [BK k][MN_BOX mn] box
+};
+constexpr int A_STAGE_BYTES = BM * 128;      // 16 KB
 constexpr int GEMM_THREADS = 320;             // warp 0 TMA producer, warp 1 MMA issuer, warps 2..9 epilogue
 constexpr int SMEM_BUDGET = 200 * 1024;
 
 template <int BN> struct GemmCfg {
-  static constexpr int B_STAGE_BYTES = BN * BK * 2;
+  static constexpr int B_STAGE_BYTES = BN * 128;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // power of two for BN in {64,128,256}
@@ -69,6 +78,17 @@ __device__ __noinline__ void wait_param_versions(const unsigned long long* const
     } while (v < target);
   }
   asm volatile("fence.proxy.async;" ::: "memory");
+}
+
+// The bias a forward GEMM adds may be this GPU's weight mirror, which peer GPUs' push kernels overwrite while this
+// kernel is already resident (its producer lane is spinning in wait_param_versions).  Non-coherent loads
+// (ld.global.nc / __ldg) are only defined for memory that is read-only for the kernel's lifetime, so the bias goes
+// through ordinary coherent loads; they are ordered after the producer's acquire by the mbarrier chain
+// (acquire -> TMA -> full barrier -> MMA commit -> accumulator-full barrier -> this load).
+__device__ __forceinline__ uint4 ld_coherent_u4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
 }
 
 __device__ __forceinline__ float tanh_fast(float x) {
@@ -135,6 +155,12 @@ __device__ __forceinline__ void staged_store(const GemmParams& p, const float (&
         float4 o = *reinterpret_cast<const float4*>(stg + rr * 16 + 4 * (g ^ ((rr >> 1) & 3)));
         if (q * 8 < rows_left) {
           float4* dp = reinterpret_cast<float4*>(dbase + static_cast<long long>(q * 8) * p.ldd32);
+          if (AUXK == 2) {
+            const float4 y = __ldg(reinterpret_cast<const float4*>(
+                reinterpret_cast<const float*>(p.aux) + (row0 + rr) * p.ldaux + cb + 4 * g));
+            o.x *= act_grad_from_output(y.x, grad_act); o.y *= act_grad_from_output(y.y, grad_act);
+            o.z *= act_grad_from_output(y.z, grad_act); o.w *= act_grad_from_output(y.w, grad_act);
+          }
           if (ACC) {
             const float4 old = *dp;
             o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
@@ -206,7 +232,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
       if (nvalid == 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const uint4 u = __ldg(reinterpret_cast<const uint4*>(bp) + q);
+          const uint4 u = ld_coherent_u4(reinterpret_cast<const uint4*>(bp) + q);
           const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
@@ -217,20 +243,23 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (j < nvalid) v[j] += __bfloat162float(bp[j]);
+          if (j < nvalid)
+            v[j] += __uint_as_float(static_cast<uint32_t>(*reinterpret_cast<const volatile unsigned short*>(bp + j)) << 16);
       }
     } else {
       const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
       if (nvalid == 32 && (reinterpret_cast<uintptr_t>(bp) & 15) == 0) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp) + q);
+          const uint4 u = ld_coherent_u4(reinterpret_cast<const uint4*>(bp) + q);
+          const float4 b4 = make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z),
+                                        __uint_as_float(u.w));
           v[q * 4] += b4.x; v[q * 4 + 1] += b4.y; v[q * 4 + 2] += b4.z; v[q * 4 + 3] += b4.w;
         }
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (j < nvalid) v[j] += __ldg(bp + j);
+          if (j < nvalid) v[j] += *reinterpret_cast<const volatile float*>(bp + j);
       }
     }
   }
@@ -243,6 +272,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
     if (p.d32 != nullptr && p.d16 == nullptr && aux_none) {
       if (p.accumulate) staged_store<true, 0, true>(p, v, row0, lane, nb, stg);
       else staged_store<true, 0, false>(p, v, row0, lane, nb, stg);
+      return;
+    }
+    if (p.d32 != nullptr && p.d16 == nullptr && !p.aux_bf16 && !p.accumulate) {   // fp32 data gradient with act'
+      staged_store<true, 2, false>(p, v, row0, lane, nb, stg);
       return;
     }
     if (p.d16 != nullptr && p.d32 == nullptr && !p.accumulate) {

@@ -1,6 +1,6 @@
 // Persistent, warp-specialised tcgen05 GEMM for sm_100a.
 //
-//   acc[m][n] = sum_k A(m,k) * B(n,k)    (bf16 x bf16 -> fp32 in TMEM)
+//   acc[m][n] = sum_k A(m,k) * B(n,k)    (bf16 x bf16 or tf32 x tf32 -> fp32 in TMEM; template parameter EB)
 //
 // Roles inside one 192-thread CTA (one CTA per SM, static round-robin tile schedule):
 //   warp 0      TMA producer: cp.async.bulk.tensor tiles of A and B into a STAGES-deep smem ring
@@ -30,11 +30,16 @@
 namespace sg {
 
 
-template <int BN, bool A_MN, bool B_MN>
+template <int EB, int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
-                         const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+                    const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
+  using E = Elem<EB>;
+  constexpr int BK = E::BK;
+  constexpr int UMMA_K = E::UMMA_K;
+  constexpr int MN_BOX = E::MN_BOX;
+  constexpr int MN_BOX_BYTES = E::MN_BOX_BYTES;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int B_STAGE_BYTES = Cfg::B_STAGE_BYTES;
 
@@ -110,13 +115,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             tma_load_2d(sa, &tma_a, fb, k0, m0);
           } else {
 #pragma unroll
-            for (int b = 0; b < BM / 64; ++b) tma_load_2d(sa + b * 8192, &tma_a, fb, m0 + b * 64, k0);
+            for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
           }
           if (!B_MN) {
             tma_load_2d(sb, &tma_b, fb, k0, n0);
           } else {
 #pragma unroll
-            for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * 8192, &tma_b, fb, n0 + b * 64, k0);
+            for (int b = 0; b < BN / MN_BOX; ++b) tma_load_2d(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
           }
           if (kb == kb_lo) SG_TRACE(2);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -126,11 +131,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-    constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);  // bytes per UMMA_K step
-    constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
-    constexpr uint32_t A_LBO = A_MN ? 8192 : 16;
-    constexpr uint32_t B_LBO = B_MN ? 8192 : 16;
+    constexpr uint32_t idesc = make_idesc(EB == 2 ? 1u : 2u, BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : 32;  // bytes per UMMA_K step
+    constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : 32;
+    constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
+    constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
     uint32_t stage = 0, phase = 0;
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -152,7 +157,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
             const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
-            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
+            umma<EB>(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
           if (kb == kb_hi - 1) { umma_commit(tfull_bar(acc)); SG_TRACE(5); }
@@ -220,18 +225,23 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 //              leader's tmem-empty barrier
 // ------------------------------------------------------------------------------------------------
 template <int BN> struct PairCfg {
-  static constexpr int B_HALF_BYTES = (BN / 2) * BK * 2;
+  static constexpr int B_HALF_BYTES = (BN / 2) * 128;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_HALF_BYTES;       // per CTA
   static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + 16 * 1024 /*epilogue staging*/;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int EB, int BN, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
-                              const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
+                         const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
   using Cfg = PairCfg<BN>;
+  using E = Elem<EB>;
+  constexpr int BK = E::BK;
+  constexpr int UMMA_K = E::UMMA_K;
+  constexpr int MN_BOX = E::MN_BOX;
+  constexpr int MN_BOX_BYTES = E::MN_BOX_BYTES;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int B_HALF_BYTES = Cfg::B_HALF_BYTES;
   constexpr int BNH = BN / 2;
@@ -303,13 +313,13 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
             tma_load_2d_pair(sa, &tma_a, fb, k0, m0);
           } else {
 #pragma unroll
-            for (int b = 0; b < BM / 64; ++b) tma_load_2d_pair(sa + b * 8192, &tma_a, fb, m0 + b * 64, k0);
+            for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d_pair(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
           }
           if (!B_MN) {
             tma_load_2d_pair(sb, &tma_b, fb, k0, n0);
           } else {
 #pragma unroll
-            for (int b = 0; b < BNH / 64; ++b) tma_load_2d_pair(sb + b * 8192, &tma_b, fb, n0 + b * 64, k0);
+            for (int b = 0; b < BNH / MN_BOX; ++b) tma_load_2d_pair(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -318,11 +328,11 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
     if (leader) {
-      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-      constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
-      constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
-      constexpr uint32_t A_LBO = A_MN ? 8192 : 16;
-      constexpr uint32_t B_LBO = B_MN ? 8192 : 16;
+      constexpr uint32_t idesc = make_idesc(EB == 2 ? 1u : 2u, 2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : 32;
+      constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : 32;
+      constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
+      constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
       uint32_t stage = 0, phase = 0;
       int it = 0;
       for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
@@ -341,7 +351,7 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
               const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
-              umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_pair<EB>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
             }
             umma_commit_pair(empty_bar(stage), 3);                       // frees the slot in BOTH CTAs
             if (kb == num_kb - 1) umma_commit_pair(tfull_bar(acc), 3);   // accumulator ready in BOTH CTAs
@@ -412,30 +422,32 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row stride ld elements.
-static int make_tmap_bf16(CUtensorMap* out, const void* ptr, long long inner, long long outer,
-                          long long ld, int box_inner, int box_outer) {
+// 2-D tensor map over bf16 (eb = 2) or fp32 (eb = 4) elements: `inner` contiguous elements per row, `outer` rows,
+// row stride ld elements.
+static int make_tmap(CUtensorMap* out, int eb, const void* ptr, long long inner, long long outer,
+                     long long ld, int box_inner, int box_outer) {
   EncodeTiledFn enc = get_encode_fn();
   SG_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   SG_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "gemm operand base must be 16-byte aligned");
-  SG_REQUIRE((ld % 8) == 0, "gemm operand leading dimension (%lld) must be a multiple of 8 bf16", ld);
+  SG_REQUIRE((ld * eb) % 16 == 0, "gemm operand leading dimension (%lld elements of %d bytes) must be a multiple of 16 bytes",
+             ld, eb);
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
-  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * eb};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides,
-                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(out, eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                   const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SG_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld",
              static_cast<int>(r), inner, outer, ld);
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int EB, int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
                        cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_tcgen05_kernel<EB, BN, A_MN, B_MN>;
   static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -451,15 +463,15 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   const int tiles = m_tiles * n_tiles * p.split_k;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
-  SG_CHECK_LAUNCH("gemm_bf16_tcgen05");
+  SG_CHECK_LAUNCH("gemm_tcgen05");
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int EB, int BN, bool A_MN, bool B_MN>
 static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
                             cudaStream_t stream) {
   using Cfg = PairCfg<BN>;
-  auto kern = gemm_bf16_tcgen05_pair_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_tcgen05_pair_kernel<EB, BN, A_MN, B_MN>;
   static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -475,26 +487,40 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
   const int max_pairs = num_sms() / 2;
   const int pairs = tiles < max_pairs ? tiles : max_pairs;
   kern<<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
-  SG_CHECK_LAUNCH("gemm_bf16_tcgen05_pair");
+  SG_CHECK_LAUNCH("gemm_tcgen05_pair");
   return 0;
 }
 
-template <int BN>
+template <int EB, int BN>
 static int dispatch_major_pair(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
                                const GemmParams& p, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm_pair<BN, false, false>(ta, tb, p, s);
-  if (!a_mn && b_mn) return launch_gemm_pair<BN, false, true>(ta, tb, p, s);
-  if (a_mn && !b_mn) return launch_gemm_pair<BN, true, false>(ta, tb, p, s);
-  return launch_gemm_pair<BN, true, true>(ta, tb, p, s);
+  if (!a_mn && !b_mn) return launch_gemm_pair<EB, BN, false, false>(ta, tb, p, s);
+  if (!a_mn && b_mn) return launch_gemm_pair<EB, BN, false, true>(ta, tb, p, s);
+  if (a_mn && !b_mn) return launch_gemm_pair<EB, BN, true, false>(ta, tb, p, s);
+  return launch_gemm_pair<EB, BN, true, true>(ta, tb, p, s);
 }
 
-template <int BN>
+template <int EB, int BN>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
                           const GemmParams& p, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_gemm<BN, false, false>(ta, tb, p, s);
-  if (!a_mn && b_mn) return launch_gemm<BN, false, true>(ta, tb, p, s);
-  if (a_mn && !b_mn) return launch_gemm<BN, true, false>(ta, tb, p, s);
-  return launch_gemm<BN, true, true>(ta, tb, p, s);
+  if (!a_mn && !b_mn) return launch_gemm<EB, BN, false, false>(ta, tb, p, s);
+  if (!a_mn && b_mn) return launch_gemm<EB, BN, false, true>(ta, tb, p, s);
+  if (a_mn && !b_mn) return launch_gemm<EB, BN, true, false>(ta, tb, p, s);
+  return launch_gemm<EB, BN, true, true>(ta, tb, p, s);
+}
+
+template <int EB>
+static int dispatch_tile(bool pair, int bn, int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                         const GemmParams& p, cudaStream_t s) {
+  if (pair) {
+    if (bn == 256) return dispatch_major_pair<EB, 256>(a_mn, b_mn, ta, tb, p, s);
+    return dispatch_major_pair<EB, 128>(a_mn, b_mn, ta, tb, p, s);
+  }
+  switch (bn) {
+    case 256: return dispatch_major<EB, 256>(a_mn, b_mn, ta, tb, p, s);
+    case 128: return dispatch_major<EB, 128>(a_mn, b_mn, ta, tb, p, s);
+    default: return dispatch_major<EB, 64>(a_mn, b_mn, ta, tb, p, s);
+  }
 }
 
 // Tile-width choice from a small cost model (cycles).  Measured on B200: this kernel is bound by the
@@ -503,7 +529,7 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 //   per k-block:  mma = max(2*BN, 128 + BN) cycles   (tensor pipe vs. smem operand reads at 128 B/cycle)
 //                 l2  = (16 KB + BN*128 B) / min(64, 6300 / active CTAs)
 //   total = waves * (num_kb * max(mma, l2) + fixed per-tile overhead)
-static int pick_bn(int M, int N, int K) {
+static int pick_bn(int M, int N, int K, int BK) {
   const int sms = num_sms();
   const long long m_tiles = (M + BM - 1) / BM;
   const long long num_kb = (K + BK - 1) / BK;
@@ -550,32 +576,36 @@ extern "C" int sg_gemm_set_pair(int mode) {
   return 0;
 }
 
-extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B,
-                            int b_mn_major, long long ldb, int M, int N, int K,
-                            const SgGemmEpilogue* ep, void* stream) {
+extern "C" int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, const void* B,
+                       int b_mn_major, long long ldb, int M, int N, int K,
+                       const SgGemmEpilogue* ep, void* stream) {
   using namespace sg;
-  SG_REQUIRE(M > 0 && N > 0 && K > 0, "sg_gemm_bf16: empty problem %dx%dx%d", M, N, K);
+  SG_REQUIRE(dtype == SG_DTYPE_BF16 || dtype == SG_DTYPE_TF32, "sg_gemm: dtype must be SG_DTYPE_BF16 or SG_DTYPE_TF32");
+  const int eb = dtype == SG_DTYPE_BF16 ? 2 : 4;
+  const int BK = 128 / eb;          // elements per k-block
+  const int MN_BOX = 128 / eb;      // elements per row of an MN-major box
+  SG_REQUIRE(M > 0 && N > 0 && K > 0, "sg_gemm: empty problem %dx%dx%d", M, N, K);
   SG_REQUIRE(ep != nullptr && (ep->d32 != nullptr || ep->d16 != nullptr),
-             "sg_gemm_bf16: epilogue needs an output");
-  SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm_bf16: grad_act needs aux");
+             "sg_gemm: epilogue needs an output");
+  SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm: grad_act needs aux");
   // per-call tile choice (autotuner) > process-wide test hooks > built-in model
-  int bn = ep->tile_bn ? ep->tile_bn : (g_force_bn ? g_force_bn : pick_bn(M, N, K));
-  SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_gemm_bf16: tile_bn must be 0, 64, 128 or 256");
+  int bn = ep->tile_bn ? ep->tile_bn : (g_force_bn ? g_force_bn : pick_bn(M, N, K, BK));
+  SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_gemm: tile_bn must be 0, 64, 128 or 256");
   // CTA pairs need BN in {128, 256} (each CTA stages BN/2 columns of B in 64-column boxes)
   bool pair = ep->tile_pair == 2 || (ep->tile_pair == 0 &&
       (g_pair_mode == 1 || (g_pair_mode == 2 && static_cast<long long>(M) * N >= 4096LL * 4096LL)));
   if (pair && bn < 128) bn = 128;
   CUtensorMap ta, tb;
   int rc;
-  if (!a_mn_major) rc = make_tmap_bf16(&ta, A, K, M, lda, BK, BM);
-  else rc = make_tmap_bf16(&ta, A, M, K, lda, 64, BK);
+  if (!a_mn_major) rc = make_tmap(&ta, eb, A, K, M, lda, BK, BM);
+  else rc = make_tmap(&ta, eb, A, M, K, lda, MN_BOX, BK);
   if (rc) return rc;
-  if (!b_mn_major) rc = make_tmap_bf16(&tb, B, K, N, ldb, BK, pair ? bn / 2 : bn);
-  else rc = make_tmap_bf16(&tb, B, N, K, ldb, 64, BK);
+  if (!b_mn_major) rc = make_tmap(&tb, eb, B, K, N, ldb, BK, pair ? bn / 2 : bn);
+  else rc = make_tmap(&tb, eb, B, N, K, ldb, MN_BOX, BK);
   if (rc) return rc;
   GemmParams p;
   SG_REQUIRE(ep->ldd32 < (1LL << 31) && ep->ldd16 < (1LL << 31) && ep->ldaux < (1LL << 31),
-             "sg_gemm_bf16: leading dimensions must fit in 31 bits");
+             "sg_gemm: leading dimensions must fit in 31 bits");
   p.M = M; p.N = N; p.K = K;
   p.d32 = ep->d32; p.ldd32 = static_cast<int>(ep->ldd32);
   p.d16 = reinterpret_cast<__nv_bfloat16*>(ep->d16); p.ldd16 = static_cast<int>(ep->ldd16);
@@ -583,9 +613,9 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   p.act = static_cast<unsigned char>(ep->act); p.grad_act = static_cast<unsigned char>(ep->grad_act);
   p.aux = ep->aux; p.ldaux = static_cast<int>(ep->ldaux); p.aux_bf16 = ep->aux_bf16 != 0;
   p.accumulate = ep->accumulate != 0; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
-  SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 64, "sg_gemm_bf16: at most 64 wait flags");
+  SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 64, "sg_gemm: at most 64 wait flags");
   SG_REQUIRE(ep->nwait == 0 || (ep->wait_seq != nullptr && ep->wait_flags != nullptr),
-             "sg_gemm_bf16: wait flags need the flag list and wait_seq");
+             "sg_gemm: wait flags need the flag list and wait_seq");
   p.wait_flags = ep->wait_flags; p.nwait = static_cast<short>(ep->nwait); p.wait_seq = ep->wait_seq;
   p.split_k = 1; p.kb_per_split = (K + BK - 1) / BK;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
@@ -604,7 +634,7 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
         if (split > 64) split = 64;
         if (split > 1 && wide != bn) {
           bn = wide;   // the B tensor map depends on the tile width: rebuild it
-          if (!b_mn_major) { rc = make_tmap_bf16(&tb, B, K, N, ldb, BK, bn); if (rc) return rc; }
+          if (!b_mn_major) { rc = make_tmap(&tb, eb, B, K, N, ldb, BK, bn); if (rc) return rc; }
         }
       }
     }
@@ -613,21 +643,19 @@ extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
       p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
       if (!ep->accumulate) {
         if (check_cuda(cudaMemset2DAsync(ep->d32, ep->ldd32 * sizeof(float), 0, N * sizeof(float), M, s),
-                       "sg_gemm_bf16: zero the split-K output"))
+                       "sg_gemm: zero the split-K output"))
           return 1;
       }
       p.accumulate = 2;   // epilogue: atomic add of the partial tile
     }
   }
-  if (pair) {
-    if (bn == 256) return dispatch_major_pair<256>(a_mn_major, b_mn_major, ta, tb, p, s);
-    return dispatch_major_pair<128>(a_mn_major, b_mn_major, ta, tb, p, s);
-  }
-  switch (bn) {
-    case 256: return dispatch_major<256>(a_mn_major, b_mn_major, ta, tb, p, s);
-    case 128: return dispatch_major<128>(a_mn_major, b_mn_major, ta, tb, p, s);
-    default: return dispatch_major<64>(a_mn_major, b_mn_major, ta, tb, p, s);
-  }
+  if (eb == 2) return dispatch_tile<2>(pair, bn, a_mn_major, b_mn_major, ta, tb, p, s);
+  return dispatch_tile<4>(pair, bn, a_mn_major, b_mn_major, ta, tb, p, s);
+}
+
+extern "C" int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
+                            long long ldb, int M, int N, int K, const SgGemmEpilogue* ep, void* stream) {
+  return sg_gemm(SG_DTYPE_BF16, A, a_mn_major, lda, B, b_mn_major, ldb, M, N, K, ep, stream);
 }
 
 #ifdef SG_GEMM_TRACE

@@ -35,7 +35,7 @@ constexpr int PUSH_UNROLL = 4;   // chunks per CTA iteration: bytes in flight pe
 
 struct PushParams {
   const float* grad[MAX_WORLD];
-  __nv_bfloat16* w16[MAX_WORLD];
+  void* w16[MAX_WORLD];                              // every rank's operand mirror (bf16, or fp32 when mirror_fp32)
   const unsigned long long* ready[MAX_WORLD];
   unsigned long long* version[MAX_WORLD];
   int world;
@@ -48,7 +48,8 @@ struct PushParams {
                                                      // [1] launch sequence number (self-counting flag value)
   int self_count;
   const float* grad_mc;                              // NVLS: multicast address of the gradient arenas (or null)
-  __nv_bfloat16* w16_mc;                             // NVLS: multicast address of the bf16 mirrors (or null)
+  void* w16_mc;                                      // NVLS: multicast address of the mirrors (or null)
+  int mirror_fp32;                                   // mirrors hold fp32 (tf32 compute path) instead of bf16
   unsigned long long* bump_ready;                    // optional: this rank's own "gradients ready" flag, bumped by
   unsigned long long* bump_seq;                      //   the kernel itself (+ the consumer-side wait sequence)
 };
@@ -60,6 +61,10 @@ __device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
   return v;
+}
+__device__ __forceinline__ void multimem_st_f4(void* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ void multimem_st_b64(void* mc, uint2 v) {
   asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};"
@@ -198,17 +203,27 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
       *reinterpret_cast<float4*>(p.w + i) = wv;
       if (need_h) *reinterpret_cast<float4*>(p.h + i) = hv;
       if (need_u) *reinterpret_cast<float4*>(p.u + i) = uv;
-      // 4. broadcast the fresh bf16 weights into every rank's mirror
+      // 4. broadcast the fresh weights into every rank's mirror (fp32 on the tf32 compute path, else bf16)
+      if (p.mirror_fp32) {
+        if (p.w16_mc != nullptr) {
+          multimem_st_f4(reinterpret_cast<float*>(p.w16_mc) + i, wv);
+        } else {
+#pragma unroll
+          for (int r = 0; r < MAX_WORLD; ++r)
+            if (r < p.world && p.w16[r] != nullptr) *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.w16[r]) + i) = wv;
+        }
+        continue;
+      }
       const __nv_bfloat162 a = __floats2bfloat162_rn(wv.x, wv.y), b = __floats2bfloat162_rn(wv.z, wv.w);
       uint2 o;
       o.x = *reinterpret_cast<const uint32_t*>(&a);
       o.y = *reinterpret_cast<const uint32_t*>(&b);
       if (p.w16_mc != nullptr) {
-        multimem_st_b64(p.w16_mc + i, o);
+        multimem_st_b64(reinterpret_cast<__nv_bfloat16*>(p.w16_mc) + i, o);
       } else {
 #pragma unroll
         for (int r = 0; r < MAX_WORLD; ++r)
-          if (r < p.world) *reinterpret_cast<uint2*>(p.w16[r] + i) = o;
+          if (r < p.world && p.w16[r] != nullptr) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.w16[r]) + i) = o;
       }
     }
   }
@@ -268,10 +283,11 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   PushParams p;
   for (int r = 0; r < MAX_WORLD; ++r) {
     p.grad[r] = r < a->world ? a->grad[r] : nullptr;
-    p.w16[r] = r < a->world ? reinterpret_cast<__nv_bfloat16*>(a->w16[r]) : nullptr;
+    p.w16[r] = r < a->world ? a->w16[r] : nullptr;
     p.ready[r] = r < a->world ? a->ready[r] : nullptr;
     p.version[r] = r < a->world ? a->version[r] : nullptr;
-    SG_REQUIRE(r >= a->world || (p.grad[r] != nullptr && p.w16[r] != nullptr), "sg_ps_push_update: null peer pointer for rank %d", r);
+    // a null mirror pointer is allowed (that rank reads the master copy directly: single-rank fp32 jobs)
+    SG_REQUIRE(r >= a->world || p.grad[r] != nullptr, "sg_ps_push_update: null gradient pointer for rank %d", r);
   }
   p.world = a->world;
   p.w = a->w; p.h = a->h; p.u = a->u;
@@ -281,7 +297,7 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   p.delta = a->up.delta; p.rho = a->up.rho; p.grad_scale = a->up.grad_scale; p.lr_dev = a->up.lr_dev;
   p.step_dev = a->step_dev; p.value_add = a->value_add;
   p.scratch = a->scratch; p.self_count = a->self_count;
-  p.grad_mc = a->grad_mc; p.w16_mc = reinterpret_cast<__nv_bfloat16*>(a->w16_mc);
+  p.grad_mc = a->grad_mc; p.w16_mc = a->w16_mc; p.mirror_fp32 = a->mirror_fp32;
   p.bump_ready = a->bump_ready; p.bump_seq = a->bump_seq;
   long long grid = (a->nchunks + PUSH_UNROLL - 1) / PUSH_UNROLL;
   const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward

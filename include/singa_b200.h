@@ -64,6 +64,13 @@ typedef struct SgGemmEpilogue {
                             zeroed output), 1 = never, n > 1 = n slices */
 } SgGemmEpilogue;
 
+/* Operand precision.  SG_DTYPE_TF32: A and B hold fp32 values (lda/ldb multiples of 4) that the tensor core
+ * reads as tf32 (sign, 8-bit exponent, top 10 mantissa bits) with fp32 accumulation — the parity path for the
+ * reference's fp32 sgemm; outputs, bias and aux are fp32.  SG_DTYPE_BF16: bf16 operands (lda/ldb multiples of 8). */
+enum { SG_DTYPE_BF16 = 0, SG_DTYPE_TF32 = 1 };
+int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
+            long long ldb, int M, int N, int K, const SgGemmEpilogue* ep, void* stream);
+/* sg_gemm with SG_DTYPE_BF16 */
 int sg_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
                  long long ldb, int M, int N, int K, const SgGemmEpilogue* ep, void* stream);
 
@@ -96,7 +103,9 @@ int sg_cast_pack(const float* src, long long lds, void* dst, long long ldd, int 
 int sg_repack_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, int perm_c,
                    int perm_kk, void* stream);
 int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
-/* bf16 [rows][lds] -> bf16 [rows][ldd], padding columns zeroed (re-striding to a TMA-legal leading dimension). */
+/* [rows][lds] -> [rows][ldd] of one element type, padding columns zeroed (re-striding to a TMA-legal leading
+ * dimension). */
+int sg_copy2d(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, int is_bf16, void* stream);
 int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, void* stream);
 /* Per image [rows][cols] -> [cols][rows] (NCHW <-> NHWC). */
 int sg_transpose_planes(const void* src, int src_bf16, void* dst, int dst_bf16, int batch, int rows,
@@ -179,7 +188,8 @@ int sg_randomsync(float* w, float* snap, float* server, long long n, float ratio
 typedef struct SgPsPush {
   int world;
   const float* grad[SG_PS_MAX_WORLD];               /* every rank's gradient arena base */
-  void* w16[SG_PS_MAX_WORLD];                       /* every rank's bf16 weight mirror base */
+  void* w16[SG_PS_MAX_WORLD];                       /* every rank's weight mirror base: bf16, or fp32 when mirror_fp32
+                                                       (NULL = that rank keeps no mirror) */
   const unsigned long long* ready[SG_PS_MAX_WORLD]; /* rank r's "gradients of this layer are ready" flag (or NULL) */
   unsigned long long* version[SG_PS_MAX_WORLD];     /* rank r's version slot for (layer, this owner) (or NULL) */
   float* w; float* h; float* u;                     /* local fp32 master / history / update arenas */
@@ -200,6 +210,8 @@ typedef struct SgPsPush {
                                                        (and *bump_seq, the consumer's wait sequence) before waiting,
                                                        replacing a separate sg_ps_flag_bump launch */
   unsigned long long* bump_seq;
+  int mirror_fp32;                                  /* mirrors (w16, w16_mc) hold fp32 values: the tf32 compute path reads
+                                                       its GEMM operands in fp32 */
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
 /* Allocation-free variant of sg_ps_push_update — no counterpart in the reference (its parameter server keeps

@@ -1,6 +1,11 @@
 """Flat parameter arena: one contiguous fp32 buffer each for value / gradient / history (/ update /
-snapshot) of ALL parameters of a net plus a bf16 mirror of the values, with every parameter starting on a
+snapshot) of ALL parameters of a net plus an operand MIRROR of the values, with every parameter starting on a
 1024-element boundary.
+
+The mirror (``data16`` / ``Param.mirror16``; the names date from the bf16-only version) is what the GEMMs read:
+  * bf16 compute: a bf16 copy of the values, refreshed by the updater in the same pass;
+  * fp32 (tf32) compute: no copy at all on one GPU — the GEMMs read the fp32 master values directly — and an fp32
+    copy only when a sharded parameter server keeps the master elsewhere and broadcasts fresh values into it.
 
 Why: (1) one fused multi-tensor updater launch per step (or per layer) instead of one per parameter;
 (2) a "server shard" of the B200 parameter server is simply a chunk range of this arena on some GPU, so the
@@ -31,21 +36,26 @@ class ParamArena:
         self.params: List[Param] = [p for p in params if p.is_owner]
         self.offsets: Dict[int, int] = {}
         self.slot: Dict[int, int] = {}      # elements occupied in the arena (>= p.size when rows are padded)
-        self.use16 = self.device.type == "cuda" and ctx().is_native
+        self.use16 = self.device.type == "cuda" and ctx().is_native      # native kernels own the arena
+        self.mirror_dtype = ctx().act_dtype
         off = 0
         for p in self.params:
             self.offsets[id(p)] = off
-            # a 2-D GEMM weight whose row length is not a multiple of 8 is stored with a padded row stride so
-            # that the bf16 mirror is directly TMA-legal (padding stays zero: its gradient is never written)
+            # a 2-D GEMM weight whose row length is not a multiple of 16 bytes is stored with a padded row stride so
+            # that the operand is directly TMA-legal (padding stays zero: its gradient is never written)
             p.ld = p.shape[-1] if p.shape else 1
             if self.use16 and getattr(p, "want_padded_ld", False) and len(p.shape) == 2 and p.shape[1] % 8:
                 p.ld = (p.shape[1] + 7) // 8 * 8
                 self.slot[id(p)] = p.shape[0] * p.ld
             else:
                 self.slot[id(p)] = p.size
-            off += _round_up(self.slot[id(p)], CHUNK)
+            # every parameter occupies a multiple of `pad_chunks_to` chunks (= the number of server shards), so any run of
+            # adjacent layers splits into equal per-rank pieces: in-place NCCL reduce-scatter / all-gather and the fused
+            # push both address piece r as base + r * piece
+            off += _round_up(self.slot[id(p)], CHUNK * max(1, pad_chunks_to))
         self.total = _round_up(max(off, CHUNK), CHUNK * max(1, pad_chunks_to))
         self.nchunks = self.total // CHUNK
+        self.pad_chunks_to = max(1, pad_chunks_to)
 
         def default_alloc(name, n, dt):
             return torch.zeros(n, dtype=dt, device=self.device)
@@ -59,7 +69,12 @@ class ParamArena:
         self.history = make("history", torch.float32) if with_history else None
         self.update = make("update", torch.float32) if with_update else None
         self.snapshot = make("snapshot", torch.float32) if with_snapshot else None
-        self.data16 = make("data16", torch.bfloat16) if self.use16 else None
+        if not self.use16:
+            self.data16 = None
+        elif self.mirror_dtype == torch.bfloat16:
+            self.data16 = make("data16", torch.bfloat16)
+        else:   # fp32 compute: a mirror exists only if the exchange backend provides one (sharded master copies)
+            self.data16 = allocator("data16", self.total, torch.float32) if allocator is not None else None
         chunk_param = torch.full((self.nchunks,), -1, dtype=torch.int32)
         lr_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
         wd_mult = torch.ones(max(len(self.params), 1), dtype=torch.float32)
@@ -84,7 +99,7 @@ class ParamArena:
             n = p.size
             if use16 and getattr(p, "want_padded_ld", False) and len(p.shape) == 2 and p.shape[1] % 8:
                 n = p.shape[0] * ((p.shape[1] + 7) // 8 * 8)
-            off += _round_up(n, CHUNK)
+            off += _round_up(n, CHUNK * max(1, pad_chunks_to))
         return _round_up(max(off, CHUNK), CHUNK * max(1, pad_chunks_to))
 
     def adopt(self, all_params: Sequence[Param] = ()) -> None:
@@ -117,7 +132,11 @@ class ParamArena:
             if self.data16 is not None:
                 p.mirror16 = shaped(self.data16)     # always: the parameter server broadcasts into the mirror
                 if p.pack16 is None:
-                    p.data16 = p.mirror16            # GEMM operand = the arena's bf16 mirror
+                    p.data16 = p.mirror16            # GEMM operand = the arena's mirror
+            elif self.use16:
+                p.mirror16 = None
+                if p.pack16 is None:
+                    p.data16 = p.data                # fp32 compute on one GPU: the GEMMs read the master values
         for q in all_params:
             if not q.is_owner:
                 shared_grad = q.grad is not None and q.owner.grad is not None and getattr(q, "_shares_grad", False)
@@ -132,8 +151,11 @@ class ParamArena:
     def sync_mirror(self) -> None:
         """data16 <- data for the whole arena, then refresh every packed operand."""
         if self.data16 is not None:
-            from .ops import kernels as K
-            K.convert(self.data, self.data16)
+            if self.data16.dtype == self.data.dtype:
+                self.data16.copy_(self.data)
+            else:
+                from .ops import kernels as K
+                K.convert(self.data, self.data16)
         for p in self.params:
             if p.pack16 is not None:
                 p.pack16()
@@ -145,7 +167,7 @@ class ParamArena:
         if not owners:
             return 0, 0
         lo = min(self.offsets[id(p)] for p in owners)
-        hi = max(self.offsets[id(p)] + _round_up(self.slot[id(p)], CHUNK) for p in owners)
+        hi = max(self.offsets[id(p)] + _round_up(self.slot[id(p)], CHUNK * self.pad_chunks_to) for p in owners)
         return lo // CHUNK, (hi - lo) // CHUNK
 
     def param_index(self, p: Param) -> int:

@@ -1,7 +1,10 @@
 """Execution context: which device the worker runs on and which backend executes the layer math.
 
-* ``native`` — hand-written sm_100a kernels from ``libsinga_b200.so`` (bf16 activations, fp32 accumulation,
-  fp32 master parameters).  The product path; selected automatically when a GPU and the library exist.
+* ``native`` — hand-written sm_100a kernels from ``libsinga_b200.so``.  The product path; selected automatically
+  when a GPU and the library exist.  Two compute precisions (``Context.dtype``):
+    - ``fp32`` (default; the reference computes in fp32, src/worker/layer.cc:186-213): fp32 activations, gradients
+      and weights; the tcgen05 GEMMs multiply them as tf32 with fp32 accumulation; no low-precision weight copy.
+    - ``bf16``: bf16 activations and a bf16 weight mirror, fp32 accumulation and fp32 master parameters.
 * ``torch``  — plain PyTorch ops in fp32.  On CPU this is the oracle / plumbing path (BASELINE config 1);
   on a GPU it is the cuBLAS/cuDNN *library baseline* the product is compared against.
 """
@@ -15,18 +18,37 @@ import torch
 from .ops import native
 
 
+DTYPES = ("fp32", "bf16")
+
+
+def _default_dtype() -> str:
+    d = os.environ.get("SINGA_B200_DTYPE", "fp32")
+    if d not in DTYPES:
+        raise ValueError(f"SINGA_B200_DTYPE must be one of {DTYPES}, got {d!r}")
+    return d
+
+
 @dataclass
 class Context:
     device: torch.device
     backend: str  # "native" | "torch"
+    dtype: str = "fp32"  # compute precision of the native backend: "fp32" (tf32 tensor cores) | "bf16"
 
     @property
     def is_native(self) -> bool:
         return self.backend == "native"
 
     @property
+    def is_bf16(self) -> bool:
+        return self.is_native and self.dtype == "bf16"
+
+    @property
     def act_dtype(self) -> torch.dtype:
-        return torch.bfloat16 if self.is_native else torch.float32
+        return torch.bfloat16 if self.is_bf16 else torch.float32
+
+    def pad_ld(self, n: int) -> int:
+        """Row stride (elements) that is TMA-legal for an operand of the compute dtype: 16-byte multiple."""
+        return (n + 7) // 8 * 8 if self.is_bf16 else (n + 3) // 4 * 4
 
 
 def _default() -> Context:
@@ -34,10 +56,10 @@ def _default() -> Context:
     if torch.cuda.is_available():
         dev = torch.device("cuda", torch.cuda.current_device())
         if want == "torch":
-            return Context(dev, "torch")
+            return Context(dev, "torch", _default_dtype())
         native.require()  # on a GPU box a missing library is an error, never a silent fallback
-        return Context(dev, "native")
-    return Context(torch.device("cpu"), "torch")
+        return Context(dev, "native", _default_dtype())
+    return Context(torch.device("cpu"), "torch", _default_dtype())
 
 
 _ctx: Context | None = None
@@ -50,8 +72,10 @@ def ctx() -> Context:
     return _ctx
 
 
-def set_context(device: str | torch.device | None = None, backend: str | None = None) -> Context:
-    """Override the context (tests, ``--impl`` switches).  ``backend='native'`` requires CUDA + the library."""
+def set_context(device: str | torch.device | None = None, backend: str | None = None,
+                dtype: str | None = None) -> Context:
+    """Override the context (tests, ``--impl`` / ``--dtype`` switches).  ``backend='native'`` requires CUDA + the
+    library."""
     global _ctx
     cur = _default() if _ctx is None else _ctx
     dev = torch.device(device) if device is not None else cur.device
@@ -62,7 +86,10 @@ def set_context(device: str | torch.device | None = None, backend: str | None = 
         if dev.type != "cuda":
             raise RuntimeError("the native backend needs a CUDA device")
         native.require()
-    _ctx = Context(dev, be)
+    dt = dtype or cur.dtype
+    if dt not in DTYPES:
+        raise ValueError(f"dtype must be one of {DTYPES}, got {dt!r}")
+    _ctx = Context(dev, be, dt)
     return _ctx
 
 

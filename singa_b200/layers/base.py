@@ -4,9 +4,9 @@ Reference: include/worker/base_layer.h:38-563, src/worker/base_layer.cc.  The re
 Concate/Slice/Split bodies empty (base_layer.cc:108-110,172-173,186-191); here they move data (views where
 possible, one copy otherwise) so partitioned nets actually execute.
 
-Storage conventions (native backend): activations are bf16; 2-D activations ``[batch, dim]`` live in a
-buffer whose row stride is a multiple of 8 elements (TMA-legal), 4-D activations ``[N,C,H,W]`` are stored
-channels-last.  On the torch backend everything is plain fp32.
+Storage conventions (native backend): activations are fp32 or bf16 (``ctx().act_dtype``); 2-D activations
+``[batch, dim]`` live in a buffer whose row stride is a multiple of 16 bytes (TMA-legal), 4-D activations
+``[N,C,H,W]`` are stored channels-last.  On the torch backend everything is plain fp32.
 """
 from __future__ import annotations
 

@@ -57,6 +57,11 @@ class _Workspace:
 workspace = _Workspace()
 
 
+def _out(t: torch.Tensor) -> dict:
+    """GEMM output keyword for an activation / gradient tensor of either compute dtype."""
+    return {"out32": t} if t.dtype == torch.float32 else {"out16": t}
+
+
 class NeuronLayer(Layer):
     """Shared fusion plumbing."""
 
@@ -140,11 +145,12 @@ class InnerProductLayer(NeuronLayer):
         # a source whose row stride is not TMA-legal (multiple of 8) is re-strided into x_flat as well
         self.x_flat = None
         self.dx_flat = None
-        if self.src4d or self.vdim % 8 != 0:
+        self.ldq = 8 if ctx().is_bf16 else 4     # elements per 16 bytes: TMA row strides are multiples of this
+        if self.src4d or self.vdim % self.ldq != 0:
             self.x_flat = alloc_act([self.batchsize, self.vdim])
             self.dx_flat = alloc_act([self.batchsize, self.vdim])
-        # weight operand = the arena's bf16 mirror; when hdim is not a multiple of 8 the arena stores the rows
-        # with a padded stride (ParamArena honours want_padded_ld) so the mirror is TMA-legal as is
+        # weight operand = the arena's mirror (or, fp32 on one GPU, the master values); when hdim is not a multiple
+        # of 8 the arena stores the rows with a padded stride (ParamArena honours want_padded_ld): TMA-legal as is
         self.weight.want_padded_ld = True
 
     def get_params(self):
@@ -165,14 +171,14 @@ class InnerProductLayer(NeuronLayer):
         K = _K()
         if self.src4d:
             n, c, h, w = src.shape
-            if self.vdim % 8 == 0:
+            if self.vdim % self.ldq == 0:
                 K.transpose_planes(src, self.x_flat, n, h * w, c)      # NHWC -> (c,h,w) order
             else:
                 self.x_flat.copy_(src.reshape(self.batchsize, self.vdim))
             return self.x_flat
         x = self._flat2d(src)
-        if x.stride(0) % 8 != 0:
-            K.copy2d_bf16(x, x.stride(0), self.x_flat, self.x_flat.stride(0), self.batchsize, self.vdim)
+        if x.stride(0) % self.ldq != 0:
+            K.copy2d(x, x.stride(0), self.x_flat, self.x_flat.stride(0), self.batchsize, self.vdim)
             return self.x_flat
         return x
 
@@ -185,10 +191,8 @@ class InnerProductLayer(NeuronLayer):
         if self.native:
             K = _K()
             w16 = self._w16()
-            out32 = self.data if self.data.dtype == torch.float32 else None
-            out16 = self.data if self.data.dtype == torch.bfloat16 else None
-            K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, out32=out32,
-                   out16=out16, bias=self._bias_operand() if self.bias_term else None, act=self.fused_act,
+            K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, **_out(self.data),
+                   bias=self._bias_operand() if self.bias_term else None, act=self.fused_act,
                    wait=self.pull_wait if training else None)
             self._x_saved = x
         else:
@@ -238,9 +242,9 @@ class InnerProductLayer(NeuronLayer):
             K = _K()
             w16 = self._w16()
             if self.src4d:
-                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=self.dx_flat)
+                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, **_out(self.dx_flat))
                 n, c, h, w = self.srclayers[0].shape(self)
-                if self.vdim % 8 == 0:
+                if self.vdim % self.ldq == 0:
                     K.transpose_planes(self.dx_flat, dst, n, c, h * w)   # (c,h,w) -> NHWC
                 else:
                     dst.copy_(self.dx_flat.reshape(dst.shape))
@@ -249,10 +253,11 @@ class InnerProductLayer(NeuronLayer):
             else:
                 d2 = self._flat2d(dst)
                 a2 = self._flat2d(aux) if aux is not None else None
-                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, out16=d2,
-                       grad_act=self.src_grad_act, aux=a2)
+                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, grad_act=self.src_grad_act, aux=a2,
+                       **_out(d2))
         else:
-            dx = dy.float() @ self.weight.data.t()
+            with R._mm_ctx(dy):
+                dx = R._f(dy.float() @ self.weight.data.t())
             if aux is not None:
                 a = aux.reshape(self.batchsize, self.vdim).float()
                 dx = R.relu_bwd(dx, a) if self.src_grad_act == ACT_RELU else R.stanh_bwd(dx, a)
@@ -309,6 +314,8 @@ class ConvolutionLayer(NeuronLayer):
 
     def _setup_native(self):
         dev = ctx().device
+        if not ctx().is_bf16:
+            raise NotImplementedError("convolution on the fp32 (tf32) path arrives with the implicit-GEMM kernel")
         F_, K_ = self.num_filters, self.col_height
         self.P = self.batchsize * self.col_width
         self.Kpad = pad8(K_)

@@ -18,6 +18,7 @@ SIGNATURES = {
     "sg_repack_bf16": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
     "sg_convert": [vp, i32, vp, i32, i64, vp],
     "sg_copy2d_bf16": [vp, i64, vp, i64, i32, i32, vp],
+    "sg_copy2d": [vp, i64, vp, i64, i32, i32, i32, vp],
     "sg_transpose_planes": [vp, i32, vp, i32, i32, i32, i32, vp],
     "sg_asum": [vp, i64, vp, i32, vp],
     "sg_fill_random": [vp, i64, i32, f32, f32, f32, u64, vp],

@@ -1,4 +1,5 @@
-"""tcgen05 GEMM wrapper (``sg_gemm_bf16``) and its plain-PyTorch restatement used on CPU and as the oracle.
+"""tcgen05 GEMM wrapper (``sg_gemm``: bf16 or tf32 operands) and its plain-PyTorch restatement used on CPU and as
+the oracle.
 
 ``gemm(a, b, ...)`` computes ``acc[m][n] = sum_k A(m,k) B(n,k)`` where ``a`` is stored ``[M][K]`` (or
 ``[K][M]`` when ``a_mn``) and ``b`` is stored ``[N][K]`` (or ``[K][N]`` when ``b_mn``), followed by the fused
@@ -14,6 +15,7 @@ import torch
 from . import native
 
 ACT_NONE, ACT_RELU, ACT_STANH = 0, 1, 2
+DT_BF16, DT_TF32 = 0, 1
 STANH_A, STANH_B = 1.7159047, 0.66666667
 
 
@@ -104,10 +106,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
          bias: torch.Tensor | None = None, act=ACT_NONE, grad_act=ACT_NONE,
          aux: torch.Tensor | None = None, accumulate=False, perm: tuple[int, int] | None = None,
          wait: tuple | None = None, split_k: int = 0, tile: tuple | None = None):
-    """Launch the sm_100a kernel.  ``a``/``b`` are 2-D bf16 CUDA tensors whose last dim is contiguous
-    (row stride = leading dimension, multiple of 8).  Outputs are written in place."""
+    """Launch the sm_100a kernel.  ``a``/``b`` are 2-D CUDA tensors of one dtype whose last dim is contiguous:
+    bf16 (row stride a multiple of 8) or fp32 (multiple of 4; multiplied as tf32 — the fp32-parity path).
+    Outputs are written in place."""
     lib = native.require()
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dtype == b.dtype and a.dtype in (torch.bfloat16, torch.float32), (a.dtype, b.dtype)
+    dtype = DT_BF16 if a.dtype == torch.bfloat16 else DT_TF32
     assert a.stride(-1) == 1 and b.stride(-1) == 1
     ep = native.GemmEpilogue()
     if out32 is not None:
@@ -135,13 +139,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, a_mn=False
         ep.wait_flags, ep.nwait, ep.wait_seq = flags.data_ptr(), flags.numel(), seq
     def launch(bn=0, pair=0):
         ep.tile_bn, ep.tile_pair = bn, pair
-        rc = lib.sg_gemm_bf16(a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
-                              b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
-        native.check(rc, "sg_gemm_bf16")
+        rc = lib.sg_gemm(dtype, a.data_ptr(), 1 if a_mn else 0, a.stride(0), b.data_ptr(), 1 if b_mn else 0,
+                         b.stride(0), M, N, K, ctypes.byref(ep), native.stream_ptr())
+        native.check(rc, "sg_gemm")
 
     cfg = tile or (0, 0)    # explicit (tile_bn, tile_pair) override, e.g. from a benchmark sweep
     if _TUNE and tile is None:
-        key = (M, N, K, bool(a_mn), bool(b_mn))
+        key = (M, N, K, bool(a_mn), bool(b_mn), dtype)
         cfg = _tuned.get(key)
         if cfg is None:
             # tuning re-runs the kernel: only when that is harmless (no accumulation, no flag wait, not capturing)

@@ -58,8 +58,12 @@ def convert(src, dst):
     _call("sg_convert", src.data_ptr(), _bf(src), dst.data_ptr(), _bf(dst), src.numel())
 
 
-def copy2d_bf16(src, lds, dst, ldd, rows, cols):
-    _call("sg_copy2d_bf16", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols)
+def copy2d(src, lds, dst, ldd, rows, cols):
+    assert src.dtype == dst.dtype
+    _call("sg_copy2d", src.data_ptr(), lds, dst.data_ptr(), ldd, rows, cols, _bf(src))
+
+
+copy2d_bf16 = copy2d
 
 
 def transpose_planes(src, dst, batch, rows, cols):

@@ -44,6 +44,7 @@ def _declare(lib):
         ctypes.c_int, ctypes.c_int, ctypes.c_int,
         ctypes.POINTER(GemmEpilogue), ctypes.c_void_p,
     ]
+    lib.sg_gemm.argtypes = [ctypes.c_int] + list(lib.sg_gemm_bf16.argtypes)
     lib.sg_gemm_set_tile.argtypes = [ctypes.c_int]
     lib.sg_gemm_set_pair.argtypes = [ctypes.c_int]
 

@@ -14,6 +14,19 @@ import torch.nn.functional as F
 STANH_A, STANH_B = 1.7159047, 0.66666667
 FLT_MIN = 1.17549435e-38
 
+# Library-baseline precision knob (bench.py --impl torch --dtype bf16): run the matmul / convolution sites under
+# torch.autocast(bf16) — cuBLAS/cuDNN bf16 tensor-core kernels with fp32 accumulation, fp32 everywhere else — the
+# library counterpart of the native bf16 path.  Off (fp32, optionally TF32 via torch.backends) by default.
+AUTOCAST_BF16 = False
+
+
+def _f(t):
+    return t.float() if t.dtype == torch.bfloat16 else t
+
+
+def _mm_ctx(t):
+    return torch.autocast(device_type=t.device.type, dtype=torch.bfloat16, enabled=AUTOCAST_BF16 and t.is_cuda)
+
 
 # ------------------------------------------------------------------------------------------- activations
 def relu_fwd(x):
@@ -153,8 +166,9 @@ def conv_fwd(x, weight, bias, k, s, pad):
     """weight {F, C*k*k} with column (c*k + ky)*k + kx  (SURVEY A.1)."""
     f = weight.shape[0]
     c = x.shape[1]
-    y = F.conv2d(x, weight.view(f, c, k, k), bias, stride=s, padding=pad)
-    return y
+    with _mm_ctx(x):
+        y = F.conv2d(x, weight.view(f, c, k, k), bias, stride=s, padding=pad)
+    return _f(y)
 
 
 def conv_bwd(x, weight, dy, k, s, pad, need_dx=True):
@@ -162,6 +176,11 @@ def conv_bwd(x, weight, dy, k, s, pad, need_dx=True):
     c = x.shape[1]
     w4 = weight.view(f, c, k, k)
     db = dy.sum(dim=(0, 2, 3))
+    if AUTOCAST_BF16 and x.is_cuda:   # conv2d_weight / conv2d_input are not autocast-aware: cast explicitly
+        xb, wb, dyb = x.bfloat16(), w4.bfloat16(), dy.bfloat16()
+        dw = torch.nn.grad.conv2d_weight(xb, w4.shape, dyb, stride=s, padding=pad).float().reshape(f, -1)
+        dx = torch.nn.grad.conv2d_input(x.shape, wb, dyb, stride=s, padding=pad).float() if need_dx else None
+        return dx, dw, db
     dw = torch.nn.grad.conv2d_weight(x, w4.shape, dy, stride=s, padding=pad).reshape(f, -1)
     dx = torch.nn.grad.conv2d_input(x.shape, w4, dy, stride=s, padding=pad) if need_dx else None
     return dx, dw, db
@@ -169,14 +188,16 @@ def conv_bwd(x, weight, dy, k, s, pad, need_dx=True):
 
 def ip_fwd(x2d, weight, bias):
     """weight {vdim, hdim}: y = x W + b  (src/worker/layer.cc:186-196)."""
-    y = x2d @ weight
+    with _mm_ctx(x2d):
+        y = _f(x2d @ weight)
     return y + bias if bias is not None else y
 
 
 def ip_bwd(x2d, weight, dy, need_dx=True):
     db = dy.sum(dim=0)
-    dw = x2d.t() @ dy
-    dx = dy @ weight.t() if need_dx else None
+    with _mm_ctx(x2d):
+        dw = _f(x2d.t() @ dy)
+        dx = _f(dy @ weight.t()) if need_dx else None
     return dx, dw, db
 
 

@@ -51,6 +51,7 @@ class PsPush(ctypes.Structure):
         ("w16_mc", ctypes.c_void_p),
         ("bump_ready", ctypes.c_void_p),
         ("bump_seq", ctypes.c_void_p),
+        ("mirror_fp32", ctypes.c_int),
     ]
 
 
@@ -83,10 +84,13 @@ def make_buckets(layers, bucket_elems: int, chunk: int = 1024) -> List[List[str]
     return buckets
 
 
-def symmetric_regions(total_elems: int, nlayers: int, world: int):
-    """Regions of the symmetric heap for an arena of ``total_elems`` elements."""
-    return [("grad", total_elems * 4), ("data16", total_elems * 2),
-            ("ready", max(nlayers, 1) * 8), ("version", max(nlayers, 1) * world * 8)]
+def symmetric_regions(total_elems: int, nlayers: int, world: int, mirror_bytes: int = 2):
+    """Regions of the symmetric heap for an arena of ``total_elems`` elements.  ``mirror_bytes``: element size of the
+    operand mirror the servers broadcast into (2 = bf16, 4 = fp32, 0 = none: one fp32 rank reads its master copy)."""
+    regions = [("grad", total_elems * 4)]
+    if mirror_bytes:
+        regions.append(("data16", total_elems * mirror_bytes))
+    return regions + [("ready", max(nlayers, 1) * 8), ("version", max(nlayers, 1) * world * 8)]
 
 
 def gather_owned(arena, ranges, world: int) -> None:
@@ -116,6 +120,8 @@ class FusedExchange:
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         assert self.world <= MAX_WORLD, f"fused push/pull supports up to {MAX_WORLD} ranks per node"
         self.arena = pm.arena
+        self.has_mirror = self.arena.data16 is not None
+        self.mirror_fp32 = self.has_mirror and self.arena.data16.dtype == torch.float32
         self.layers = list(pm._param_layers)
         self.shards = shard_bounds(self.arena.nchunks, self.world)
         import os
@@ -213,7 +219,7 @@ class FusedExchange:
         a.world = self.world
         for r in range(self.world):
             a.grad[r] = self.heap.ptr("grad", r)
-            a.w16[r] = self.heap.ptr("data16", r)
+            a.w16[r] = self.heap.ptr("data16", r) if self.has_mirror else None
             a.ready[r] = self.heap.ptr("ready", r, i * 8)
             a.version[r] = self.heap.ptr("version", r, (i * self.world + self.rank) * 8)
         ar, u = self.arena, self.pm.updater
@@ -230,9 +236,10 @@ class FusedExchange:
         a.scratch = self.scratch[i].data_ptr()
         a.self_count = 1
         a.max_ctas = self.max_ctas
+        a.mirror_fp32 = 1 if self.mirror_fp32 else 0
         if self.use_nvls:
             a.grad_mc = self.heap.mc_ptr("grad")
-            a.w16_mc = self.heap.mc_ptr("data16")
+            a.w16_mc = self.heap.mc_ptr("data16") if self.has_mirror else None
         a.bump_ready, a.bump_seq = ready_own, seq_own     # the kernel announces this rank's gradients itself
         native.check(self.lib.sg_ps_push_update(ctypes.byref(a), comm.cuda_stream), "sg_ps_push_update")
         native.count_launch()

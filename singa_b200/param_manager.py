@@ -60,11 +60,13 @@ class ParamManager:
             from .parallel.symm import make_heap
             probe = ParamArena.layout_total(owners, pad_chunks_to=world)
             nlayers = sum(1 for l in net.layers if l.get_params())
-            heap = make_heap(symmetric_regions(probe, nlayers, world), dist.get_rank() if world > 1 else 0,
-                             world, ctx().device)
+            # operand mirror: bf16 always; fp32 only when the master copies are spread over several ranks
+            mirror_bytes = 2 if ctx().is_bf16 else (4 if world > 1 else 0)
+            heap = make_heap(symmetric_regions(probe, nlayers, world, mirror_bytes),
+                             dist.get_rank() if world > 1 else 0, world, ctx().device)
 
             def allocator(name, n, dt, heap=heap):
-                if name in ("grad", "data16"):
+                if name in heap.offsets and name in ("grad", "data16"):
                     return heap.tensor(name, dt)
                 return None
         if backend == "async":

@@ -80,11 +80,23 @@ class Router:
         self.sock.send_multipart([ident, *frames])
 
     def recv(self, timeout_ms: Optional[int] = None) -> Optional[List[bytes]]:
-        if timeout_ms is not None and not self.sock.poll(timeout_ms):
-            return None
-        frames = self.sock.recv_multipart()
-        self.last_recv_node = frames[0]
-        return frames[1:]
+        # Handshake leftovers are not traffic: a worker re-sends PING every retry interval until the barrier releases,
+        # so duplicates can still be queued behind it (answered here: a late pinger may really be waiting), and the
+        # answers to those duplicates reach the worker as extra PONGs (dropped).
+        deadline = None if timeout_ms is None else time.monotonic() + timeout_ms / 1000.0
+        while True:
+            if deadline is not None:
+                left = max(0.0, deadline - time.monotonic())
+                if not self.sock.poll(int(left * 1000)):
+                    return None
+            frames = self.sock.recv_multipart()
+            if len(frames) == 2 and frames[1] == b"PING":
+                self.sock.send_multipart([frames[0], b"PONG"])
+                continue
+            if len(frames) == 2 and frames[1] == b"PONG":
+                continue
+            self.last_recv_node = frames[0]
+            return frames[1:]
 
     def close(self, linger_ms: int = 0) -> None:
         """``linger_ms`` > 0 lets queued messages (e.g. the final kStop behind 48 MB of kPut payloads) reach the peer

@@ -200,3 +200,81 @@ def test_gemm_split_k_plain_and_timing():
         outs[split], times[split] = out, e0.elapsed_time(e1) / 5
     torch.testing.assert_close(outs[0], outs[1], rtol=2e-3, atol=5e-2)
     print(f"\n[wgrad 256x2400x46656] no split {times[1]*1e3:.0f} us, split-K {times[0]*1e3:.0f} us")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# tf32 operands (fp32 in memory): the fp32-parity path.  The oracle is the fp32 product of the same fp32 inputs;
+# the tensor core keeps 10 mantissa bits of each operand, so the tolerance is ~2^-10 relative per product term.
+# ---------------------------------------------------------------------------------------------------------
+def _mk32(rows, cols, dev, scale=1.0):
+    buf = torch.zeros(rows, (cols + 3) // 4 * 4, device=dev, dtype=torch.float32)
+    buf[:, :cols] = torch.randn(rows, cols, device=dev) * scale
+    return buf[:, :cols]
+
+
+def _run32(M, N, K, a_mn, b_mn, bn=0, pair=0, **kw):
+    dev = "cuda"
+    torch.manual_seed(M * 5 + N * 11 + K)
+    a = _mk32(K, M, dev) if a_mn else _mk32(M, K, dev)
+    b = _mk32(K, N, dev) if b_mn else _mk32(N, K, dev)
+    out32 = torch.full((M, (N + 3) // 4 * 4), float("nan"), device=dev)[:, :N]
+    G.gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn, out32=out32, tile=(bn, pair) if (bn or pair) else None, **kw)
+    torch.cuda.synchronize()
+    kwr = {k: v for k, v in kw.items() if k in ("bias", "act", "grad_act", "aux")}
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        ref = G.gemm_ref(a, b, a_mn, b_mn, **kwr)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    return out32, ref
+
+
+def _tf32_close(out, ref, K):
+    # per-term relative error <= 2^-10 (two truncated operands), random signs: error ~ 2^-10 * sqrt(K) * |a||b|
+    tol = 2.0 ** -10 * (K ** 0.5) * 3.0 + 1e-5
+    err = (out - ref).abs().max().item()
+    assert err <= tol, f"max abs error {err} > {tol}"
+    assert torch.isfinite(out).all()
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_tf32_majors_tiles(a_mn, b_mn, bn):
+    out, ref = _run32(256, 512, 384, a_mn, b_mn, bn, 1)
+    _tf32_close(out, ref, 384)
+
+
+@pytest.mark.parametrize("bn", [128, 256])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_tf32_pair(a_mn, b_mn, bn):
+    out, ref = _run32(512, 768, 416, a_mn, b_mn, bn, 2)
+    _tf32_close(out, ref, 416)
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 2500, 784), (1000, 10, 500), (64, 500, 800), (130, 70, 72), (1, 8, 8),
+                                   (777, 1500, 2000), (33, 36, 20)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (False, False), (True, True)])
+def test_gemm_tf32_ragged(M, N, K, a_mn, b_mn):
+    out, ref = _run32(M, N, K, a_mn, b_mn)
+    _tf32_close(out, ref, K)
+
+
+def test_gemm_tf32_epilogues():
+    dev = "cuda"
+    M, N, K = 300, 200, 136
+    bias = torch.randn(N, device=dev)
+    for act in (G.ACT_RELU, G.ACT_STANH):
+        out, ref = _run32(M, N, K, False, True, bias=bias, act=act)
+        _tf32_close(out, ref, K)
+    # data-gradient epilogue: fp32 output times act'(aux), aux fp32
+    aux = torch.tanh(torch.randn(M, N, device=dev)) * 1.7
+    for ga in (G.ACT_RELU, G.ACT_STANH):
+        out, ref = _run32(M, N, K, False, False, grad_act=ga, aux=aux)
+        _tf32_close(out, ref, K)
+    # accumulate and split-K
+    a, b = _mk32(4096, 96, dev), _mk32(4096, 200, dev)
+    out32 = torch.ones(96, 200, device=dev)
+    G.gemm(a, b, 96, 200, 4096, a_mn=True, b_mn=True, out32=out32, accumulate=True)
+    torch.cuda.synchronize()
+    _tf32_close(out32, a.t() @ b + 1.0, 4096)

@@ -11,9 +11,10 @@ from singa_b200.ops import reference as R
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("mirror", [torch.bfloat16, torch.float32, None])
 @pytest.mark.parametrize("world", [1, 2, 4])
 @pytest.mark.parametrize("kind,kid", [("kSGD", 0), ("kAdaGrad", 2)])
-def test_push_update_emulated(world, kind, kid):
+def test_push_update_emulated(world, kind, kid, mirror):
     from singa_b200.ops._decl import Updater as CUpdater
     from singa_b200.parallel.fused_ps import PsPush
     lib = native.require()
@@ -21,7 +22,7 @@ def test_push_update_emulated(world, kind, kid):
     nchunks = 40
     n = nchunks * 1024
     grads = [torch.randn(n, device=dev) for _ in range(world)]
-    mirrors = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(world)]
+    mirrors = [torch.zeros(n, device=dev, dtype=mirror) for _ in range(world)] if mirror is not None else []
     ready = torch.full((world,), 2, dtype=torch.int64, device=dev)
     version = torch.zeros(world, dtype=torch.int64, device=dev)
     w = torch.randn(n, device=dev)
@@ -37,7 +38,7 @@ def test_push_update_emulated(world, kind, kid):
     a.world = world
     for r in range(world):
         a.grad[r] = grads[r].data_ptr()
-        a.w16[r] = mirrors[r].data_ptr()
+        a.w16[r] = mirrors[r].data_ptr() if mirrors else None
         a.ready[r] = ready[r:r + 1].data_ptr()
         a.version[r] = version[r:r + 1].data_ptr()
     a.w, a.h, a.u = w.data_ptr(), h.data_ptr(), None
@@ -48,6 +49,7 @@ def test_push_update_emulated(world, kind, kid):
     a.scratch = scratch.data_ptr()
     a.self_count = 1
     a.max_ctas = 7
+    a.mirror_fp32 = 1 if mirror == torch.float32 else 0
     for launch in range(2):   # two launches: the arrival counter must be back to zero after the first
         native.check(lib.sg_ps_push_update(ctypes.byref(a), torch.cuda.current_stream().cuda_stream))
         torch.cuda.synchronize()
@@ -61,7 +63,7 @@ def test_push_update_emulated(world, kind, kid):
         torch.testing.assert_close(h, hr, rtol=1e-5, atol=1e-6)
         lo, hi = first * 1024, (first + cnt) * 1024
         for m in mirrors:
-            assert torch.equal(m[lo:hi], w[lo:hi].to(torch.bfloat16))
+            assert torch.equal(m[lo:hi], w[lo:hi].to(mirror))
             assert float(m[:lo].abs().sum()) == 0 and float(m[hi:].abs().sum()) == 0
         assert scratch.tolist() == [0, launch + 1]
         assert version.tolist() == [launch + 1] * world
