@@ -136,6 +136,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : 32;
     constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
     constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
+    // MN-major tf32 tiles use the 32-byte-atom swizzle: groups of 4 k-rows (512 bytes) instead of 8 (1024)
+    constexpr uint32_t A_LAYOUT = (A_MN && EB == 4) ? kLayoutSw128Base32 : kLayoutSw128;
+    constexpr uint32_t B_LAYOUT = (B_MN && EB == 4) ? kLayoutSw128Base32 : kLayoutSw128;
+    constexpr uint32_t A_SBO = (A_MN && EB == 4) ? 512 : 1024;
+    constexpr uint32_t B_SBO = (B_MN && EB == 4) ? 512 : 1024;
     uint32_t stage = 0, phase = 0;
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -155,8 +160,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
-            const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+            const uint64_t adesc = make_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO, A_LAYOUT);
+            const uint64_t bdesc = make_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO, B_LAYOUT);
             umma<EB>(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
@@ -333,6 +338,10 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
       constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) : 32;
       constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
       constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
+      constexpr uint32_t A_LAYOUT = (A_MN && EB == 4) ? kLayoutSw128Base32 : kLayoutSw128;
+      constexpr uint32_t B_LAYOUT = (B_MN && EB == 4) ? kLayoutSw128Base32 : kLayoutSw128;
+      constexpr uint32_t A_SBO = (A_MN && EB == 4) ? 512 : 1024;
+      constexpr uint32_t B_SBO = (B_MN && EB == 4) ? 512 : 1024;
       uint32_t stage = 0, phase = 0;
       int it = 0;
       for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
@@ -349,8 +358,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
             const uint32_t sb = sB0 + stage * B_HALF_BYTES;
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
-              const uint64_t adesc = make_smem_desc_sw128(sa + k * A_KSTEP, A_LBO, 1024);
-              const uint64_t bdesc = make_smem_desc_sw128(sb + k * B_KSTEP, B_LBO, 1024);
+              const uint64_t adesc = make_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO, A_LAYOUT);
+              const uint64_t bdesc = make_smem_desc(sb + k * B_KSTEP, B_LBO, B_SBO, B_LAYOUT);
               umma_pair<EB>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
             }
             umma_commit_pair(empty_bar(stage), 3);                       // frees the slot in BOTH CTAs
@@ -425,7 +434,7 @@ static EncodeTiledFn get_encode_fn() {
 // 2-D tensor map over bf16 (eb = 2) or fp32 (eb = 4) elements: `inner` contiguous elements per row, `outer` rows,
 // row stride ld elements.
 static int make_tmap(CUtensorMap* out, int eb, const void* ptr, long long inner, long long outer,
-                     long long ld, int box_inner, int box_outer) {
+                     long long ld, int box_inner, int box_outer, bool mn_major) {
   EncodeTiledFn enc = get_encode_fn();
   SG_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   SG_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "gemm operand base must be 16-byte aligned");
@@ -437,7 +446,8 @@ static int make_tmap(CUtensorMap* out, int eb, const void* ptr, long long inner,
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, eb == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                    const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   (mn_major && eb == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SG_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld",
              static_cast<int>(r), inner, outer, ld);
   return 0;
@@ -597,11 +607,11 @@ extern "C" int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, 
   if (pair && bn < 128) bn = 128;
   CUtensorMap ta, tb;
   int rc;
-  if (!a_mn_major) rc = make_tmap(&ta, eb, A, K, M, lda, BK, BM);
-  else rc = make_tmap(&ta, eb, A, M, K, lda, MN_BOX, BK);
+  if (!a_mn_major) rc = make_tmap(&ta, eb, A, K, M, lda, BK, BM, false);
+  else rc = make_tmap(&ta, eb, A, M, K, lda, MN_BOX, BK, true);
   if (rc) return rc;
-  if (!b_mn_major) rc = make_tmap(&tb, eb, B, K, N, ldb, BK, pair ? bn / 2 : bn);
-  else rc = make_tmap(&tb, eb, B, N, K, ldb, MN_BOX, BK);
+  if (!b_mn_major) rc = make_tmap(&tb, eb, B, K, N, ldb, BK, pair ? bn / 2 : bn, false);
+  else rc = make_tmap(&tb, eb, B, N, K, ldb, MN_BOX, BK, true);
   if (rc) return rc;
   GemmParams p;
   SG_REQUIRE(ep->ldd32 < (1LL << 31) && ep->ldd16 < (1LL << 31) && ep->ldaux < (1LL << 31),
@@ -634,7 +644,7 @@ extern "C" int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, 
         if (split > 64) split = 64;
         if (split > 1 && wide != bn) {
           bn = wide;   // the B tensor map depends on the tile width: rebuild it
-          if (!b_mn_major) { rc = make_tmap(&tb, eb, B, K, N, ldb, BK, bn); if (rc) return rc; }
+          if (!b_mn_major) { rc = make_tmap(&tb, eb, B, K, N, ldb, BK, bn, false); if (rc) return rc; }
         }
       }
     }

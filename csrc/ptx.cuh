@@ -216,18 +216,26 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar, uint16_t mask) {
 // ----------------------------------------------------------------------------------------------
 // Descriptors (bit layouts: PTX ISA "tcgen05 matrix descriptor" / "instruction descriptor")
 // ----------------------------------------------------------------------------------------------
-// Shared-memory matrix descriptor, 128-byte swizzle, sm_100 version field = 1.
+// Shared-memory matrix descriptor, sm_100 version field = 1.
 //   [0,14)  start address >> 4      [16,30) leading byte offset >> 4
-//   [32,46) stride byte offset >> 4 [46,48) version = 1       [61,64) layout: 2 = SWIZZLE_128B
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
+//   [32,46) stride byte offset >> 4 [46,48) version = 1       [61,64) layout: 2 = SWIZZLE_128B,
+//                                                                             1 = SWIZZLE_128B with 32-byte atoms
+// Layout 1 is the MN-major layout of 32-bit (tf32) operands: the tensor core transposes in 32-byte units, so the
+// swizzle permutes the four 32-byte chunks of a 128-byte row with the row index mod 4 (a 4-row, 512-byte pattern;
+// TMA writes it with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B) instead of eight 16-byte chunks with the row index mod 8.
+constexpr uint32_t kLayoutSw128 = 2, kLayoutSw128Base32 = 1;
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((saddr >> 4) & 0x3FFF);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= 1ull << 46;
-  d |= 2ull << 61;
+  d |= static_cast<uint64_t>(layout) << 61;
   return d;
+}
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return make_smem_desc(saddr, lbo_bytes, sbo_bytes, kLayoutSw128);
 }
 // Instruction descriptor for kind::f16 with bf16 inputs and fp32 accumulate.
 //   [4,6) D fmt: 1 = f32   [7,10) A fmt: 1 = bf16   [10,13) B fmt: 1 = bf16

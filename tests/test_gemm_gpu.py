@@ -231,8 +231,9 @@ def _run32(M, N, K, a_mn, b_mn, bn=0, pair=0, **kw):
 
 
 def _tf32_close(out, ref, K):
-    # per-term relative error <= 2^-10 (two truncated operands), random signs: error ~ 2^-10 * sqrt(K) * |a||b|
-    tol = 2.0 ** -10 * (K ** 0.5) * 3.0 + 1e-5
+    # the tensor core truncates each operand to 10 mantissa bits (relative error < 2^-10 each, < 2^-9 per product);
+    # products have random signs, so the sum's error grows like sqrt(K); the bound is ~8 sigma of that
+    tol = 2.0 ** -10 * (K ** 0.5) * 6.0 + 1e-5
     err = (out - ref).abs().max().item()
     assert err <= tol, f"max abs error {err} > {tol}"
     assert torch.isfinite(out).all()
