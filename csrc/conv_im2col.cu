@@ -18,9 +18,9 @@ namespace sg {
 // input (the k horizontally adjacent pixels with all their channels).  A warp-row (32 lanes, blockDim.y rows per
 // block) copies one such run; the pixel decomposition and the border clipping are computed once per run, not per
 // element.  VEC = elements per lane access (8 -> 128-bit; needs C % 8 == 0 and ld % 8 == 0).
-template <int VEC>
+template <typename T, int VEC>
 __global__ void __launch_bounds__(256)
-im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, long long ld, int N,
+im2col_nhwc_kernel(const T* __restrict__ x, T* __restrict__ col, long long ld, int N,
                    int H, int W, int C, int OH, int OW, int k, int s, int pad) {
   const long long rows = static_cast<long long>(N) * OH * OW * k;
   const int row_len = k * C;
@@ -40,8 +40,8 @@ im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
       e_lo = max(0, -x0) * C;
       e_hi = min(k, W - x0) * C;
     }
-    __nv_bfloat16* dst = col + p * ld + static_cast<long long>(ky) * row_len;
-    const __nv_bfloat16* src = x + ((static_cast<long long>(n) * H + yy) * W + x0) * C;
+    T* dst = col + p * ld + static_cast<long long>(ky) * row_len;
+    const T* src = x + ((static_cast<long long>(n) * H + yy) * W + x0) * C;
     if (VEC == 8) {
       for (int e = threadIdx.x * 8; e < row_len; e += 32 * 8) {
         const bool in = e >= e_lo && e < e_hi;   // C % 8 == 0: a vector never straddles the border
@@ -49,7 +49,7 @@ im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
       }
     } else {
       for (int e = threadIdx.x; e < row_len; e += 32)
-        dst[e] = (e >= e_lo && e < e_hi) ? src[e] : __float2bfloat16_rn(0.f);
+        dst[e] = (e >= e_lo && e < e_hi) ? src[e] : T(0.f);
     }
   }
 }
@@ -59,15 +59,17 @@ im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
 // step).  Here every thread builds ONE 16-byte vector of the column matrix — 8 consecutive k-indices of one output
 // pixel — from scalar (L1-resident) loads, walking (ky, kx, c) incrementally, and stores it with a single coalesced
 // 128-bit access.  Needs ld % 8 == 0 and a 16-byte aligned col (true for the padded column buffers).
+template <typename T>
 __global__ void __launch_bounds__(256)
-im2col_nhwc_gather8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int ld, int N, int H,
+im2col_nhwc_gather8_kernel(const T* __restrict__ x, T* __restrict__ col, int ld, int N, int H,
                            int W, int C, int OH, int OW, int k, int s, int pad, unsigned total_vecs) {
-  const int vpr = ld >> 3;                       // vectors per column-matrix row
+  constexpr int EPV = 16 / sizeof(T);            // elements per 16-byte vector (8 bf16, 4 fp32)
+  const int vpr = ld / EPV;                      // vectors per column-matrix row
   const int K = k * k * C;
   const unsigned stride = gridDim.x * blockDim.x;
   for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total_vecs; t += stride) {
     const unsigned p = t / vpr;
-    const int j0 = static_cast<int>(t - p * vpr) << 3;
+    const int j0 = static_cast<int>(t - p * vpr) * EPV;
     const int ox = static_cast<int>(p % OW);
     const unsigned q = p / OW;
     const int oy = static_cast<int>(q % OH);
@@ -77,13 +79,13 @@ im2col_nhwc_gather8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* _
     int ky = kk / k;
     int kx = kk - ky * k;
     const int y0 = oy * s - pad, x0 = ox * s - pad;
-    const __nv_bfloat16* img = x + static_cast<long long>(n) * H * W * C;
-    __align__(16) __nv_bfloat16 v[8];
+    const T* img = x + static_cast<long long>(n) * H * W * C;
+    __align__(16) T v[EPV];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
+    for (int e = 0; e < EPV; ++e) {
       const int yy = y0 + ky, xx = x0 + kx;
       const bool in = (j0 + e < K) && yy >= 0 && yy < H && xx >= 0 && xx < W;
-      v[e] = in ? img[(static_cast<long long>(yy) * W + xx) * C + c] : __float2bfloat16_rn(0.f);
+      v[e] = in ? img[(static_cast<long long>(yy) * W + xx) * C + c] : T(0.f);
       if (++c == C) { c = 0; if (++kx == k) { kx = 0; ++ky; } }
     }
     *reinterpret_cast<uint4*>(col + static_cast<long long>(p) * ld + j0) = *reinterpret_cast<const uint4*>(v);
@@ -99,10 +101,11 @@ __device__ __forceinline__ float actgrad(float y, int act) {
   return 1.f;
 }
 
-__global__ void col2im_nhwc_kernel(const __nv_bfloat16* __restrict__ dcol, long long ld,
-                                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int OH,
+template <typename T>
+__global__ void col2im_nhwc_kernel(const T* __restrict__ dcol, long long ld,
+                                   T* __restrict__ dx, int N, int H, int W, int C, int OH,
                                    int OW, int k, int s, int pad, int grad_act,
-                                   const __nv_bfloat16* __restrict__ aux) {
+                                   const T* __restrict__ aux) {
   const long long total = static_cast<long long>(N) * H * W * C;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
@@ -123,11 +126,11 @@ __global__ void col2im_nhwc_kernel(const __nv_bfloat16* __restrict__ dcol, long 
         const int ox = tx / s;
         if (ox >= OW) continue;
         const long long p = (static_cast<long long>(n) * OH + oy) * OW + ox;
-        g += __bfloat162float(dcol[p * ld + static_cast<long long>(ky * k + kx) * C + c]);
+        g += static_cast<float>(dcol[p * ld + static_cast<long long>(ky * k + kx) * C + c]);
       }
     }
-    if (grad_act != SG_ACT_NONE) g *= actgrad(__bfloat162float(aux[i]), grad_act);
-    dx[i] = __float2bfloat16_rn(g);
+    if (grad_act != SG_ACT_NONE) g *= actgrad(static_cast<float>(aux[i]), grad_act);
+    dx[i] = T(g);
   }
 }
 
@@ -186,49 +189,73 @@ static inline int grid_for(long long n, int threads) {
 
 using namespace sg;
 
-extern "C" int sg_im2col_nhwc(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH,
-                              int OW, int k, int stride, int pad, void* stream) {
+extern "C" int sg_im2col(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH,
+                         int OW, int k, int stride, int pad, int is_bf16, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0, "sg_im2col_nhwc: bad geometry");
-  SG_REQUIRE(ld >= static_cast<long long>(k) * k * C, "sg_im2col_nhwc: ld smaller than k*k*C");
-  const bool vec = (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)x & 15) == 0) && (((uintptr_t)col & 15) == 0);
+  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0, "sg_im2col: bad geometry");
+  SG_REQUIRE(ld >= static_cast<long long>(k) * k * C, "sg_im2col: ld smaller than k*k*C");
+  const int epv = is_bf16 ? 8 : 4;
+  const bool vec = is_bf16 && (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)x & 15) == 0) && (((uintptr_t)col & 15) == 0);
   const long long rows = static_cast<long long>(N) * OH * OW * k;
   if (rows <= 0) return 0;
   const dim3 block(32, 8);
   long long blocks = (rows + 7) / 8;
   const long long cap = static_cast<long long>(num_sms()) * 16;
   if (blocks > cap) blocks = cap;
-  const long long total_vecs = static_cast<long long>(N) * OH * OW * (ld / 8);
+  const long long total_vecs = static_cast<long long>(N) * OH * OW * (ld / epv);
+  const bool gather_ok = (ld % epv == 0) && (((uintptr_t)col & 15) == 0) && ld < (1LL << 30) && total_vecs < (1LL << 32);
+  const long long want = (total_vecs + 255) / 256;
+  const long long capv = static_cast<long long>(num_sms()) * 32;
+  const unsigned ggrid = static_cast<unsigned>(want < capv ? want : capv);
   if (vec) {
-    im2col_nhwc_kernel<8><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
-  } else if ((ld % 8 == 0) && (((uintptr_t)col & 15) == 0) && ld < (1LL << 30) && total_vecs < (1LL << 32)) {
-    const long long want = (total_vecs + 255) / 256;
-    const long long capv = static_cast<long long>(num_sms()) * 32;
-    im2col_nhwc_gather8_kernel<<<static_cast<unsigned>(want < capv ? want : capv), 256, 0, s>>>(
+    im2col_nhwc_kernel<__nv_bfloat16, 8><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
+  } else if (gather_ok && is_bf16) {
+    im2col_nhwc_gather8_kernel<__nv_bfloat16><<<ggrid, 256, 0, s>>>(
         (const __nv_bfloat16*)x, (__nv_bfloat16*)col, static_cast<int>(ld), N, H, W, C, OH, OW, k, stride, pad,
         static_cast<unsigned>(total_vecs));
-  } else
-    im2col_nhwc_kernel<1><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
-  SG_CHECK_LAUNCH("im2col_nhwc");
+  } else if (gather_ok) {
+    im2col_nhwc_gather8_kernel<float><<<ggrid, 256, 0, s>>>(
+        (const float*)x, (float*)col, static_cast<int>(ld), N, H, W, C, OH, OW, k, stride, pad,
+        static_cast<unsigned>(total_vecs));
+  } else if (is_bf16) {
+    im2col_nhwc_kernel<__nv_bfloat16, 1><<<static_cast<unsigned>(blocks), block, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
+  } else {
+    im2col_nhwc_kernel<float, 1><<<static_cast<unsigned>(blocks), block, 0, s>>>((const float*)x, (float*)col, ld, N, H, W, C, OH, OW, k, stride, pad);
+  }
+  SG_CHECK_LAUNCH("im2col");
+  return 0;
+}
+
+extern "C" int sg_im2col_nhwc(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH,
+                              int OW, int k, int stride, int pad, void* stream) {
+  return sg_im2col(x, col, ld, N, H, W, C, OH, OW, k, stride, pad, 1, stream);
+}
+
+extern "C" int sg_col2im(const void* dcol, long long ld, void* dx, int N, int H, int W, int C,
+                         int OH, int OW, int k, int stride, int pad, int grad_act, const void* aux,
+                         int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0, "sg_col2im: bad geometry");
+  SG_REQUIRE(grad_act == SG_ACT_NONE || aux != nullptr, "sg_col2im: grad_act needs aux");
+  const long long total = static_cast<long long>(N) * H * W * C;
+  if (total <= 0) return 0;
+  const bool vec = is_bf16 && (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)dcol & 15) == 0) && (((uintptr_t)dx & 15) == 0) &&
+                   (aux == nullptr || ((uintptr_t)aux & 15) == 0);
+  if (vec)
+    col2im_nhwc_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C,
+                                                                     OH, OW, k, stride, pad, grad_act, (const __nv_bfloat16*)aux);
+  else if (is_bf16)
+    col2im_nhwc_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k,
+                                                                          stride, pad, grad_act, (const __nv_bfloat16*)aux);
+  else
+    col2im_nhwc_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)dcol, ld, (float*)dx, N, H, W, C, OH, OW, k,
+                                                                  stride, pad, grad_act, (const float*)aux);
+  SG_CHECK_LAUNCH("col2im");
   return 0;
 }
 
 extern "C" int sg_col2im_nhwc(const void* dcol, long long ld, void* dx, int N, int H, int W, int C,
                               int OH, int OW, int k, int stride, int pad, int grad_act, const void* aux,
                               void* stream) {
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  SG_REQUIRE(k > 0 && stride > 0 && pad >= 0, "sg_col2im_nhwc: bad geometry");
-  SG_REQUIRE(grad_act == SG_ACT_NONE || aux != nullptr, "sg_col2im_nhwc: grad_act needs aux");
-  const long long total = static_cast<long long>(N) * H * W * C;
-  if (total <= 0) return 0;
-  const bool vec = (C % 8 == 0) && (ld % 8 == 0) && (((uintptr_t)dcol & 15) == 0) && (((uintptr_t)dx & 15) == 0) &&
-                   (aux == nullptr || ((uintptr_t)aux & 15) == 0);
-  if (vec)
-    col2im_nhwc_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C,
-                                                                     OH, OW, k, stride, pad, grad_act, (const __nv_bfloat16*)aux);
-  else
-    col2im_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)dcol, ld, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k,
-                                                           stride, pad, grad_act, (const __nv_bfloat16*)aux);
-  SG_CHECK_LAUNCH("col2im_nhwc");
-  return 0;
+  return sg_col2im(dcol, ld, dx, N, H, W, C, OH, OW, k, stride, pad, grad_act, aux, 1, stream);
 }

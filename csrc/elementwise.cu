@@ -201,6 +201,34 @@ __global__ void cast_pack_kernel(const S* __restrict__ src, long long lds,
   }
 }
 
+// Filter packing for the implicit-GEMM convolution (see sg_conv_pack in the header): one launch writes the forward
+// operand [F][(tap, c)] and the data-gradient operand [C][(flipped tap, f)], both zero padded.
+template <typename S, typename D>
+__global__ void conv_pack_kernel(const S* __restrict__ w, long long ldw, int F, int C, int k, D* __restrict__ fwd,
+                                 long long ldfwd, int cp_f, D* __restrict__ dgrad, long long lddgrad, int fp_d) {
+  const int kk = k * k;
+  const long long n_fwd = static_cast<long long>(F) * ldfwd;
+  const long long n_dg = dgrad != nullptr ? static_cast<long long>(C) * lddgrad : 0;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n_fwd + n_dg; i += stride) {
+    float v = 0.f;
+    if (i < n_fwd) {
+      const int f = static_cast<int>(i / ldfwd);
+      const int col = static_cast<int>(i - static_cast<long long>(f) * ldfwd);
+      const int tap = col / cp_f, c = col - tap * cp_f;
+      if (tap < kk && c < C) v = to_float(w[static_cast<long long>(f) * ldw + c * kk + tap]);
+      fwd[i] = from_float<D>(v);
+    } else {
+      const long long j = i - n_fwd;
+      const int c = static_cast<int>(j / lddgrad);
+      const int col = static_cast<int>(j - static_cast<long long>(c) * lddgrad);
+      const int tap = col / fp_d, f = col - tap * fp_d;
+      if (tap < kk && f < F) v = to_float(w[static_cast<long long>(f) * ldw + c * kk + (kk - 1 - tap)]);
+      dgrad[j] = from_float<D>(v);
+    }
+  }
+}
+
 // Generic dtype conversion of a flat buffer (fp32 <-> bf16).
 template <typename S, typename D>
 __global__ void convert_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
@@ -545,4 +573,21 @@ extern "C" int sg_copy2d(const void* src, long long lds, void* dst, long long ld
 extern "C" int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,
                               void* stream) {
   return sg_copy2d(src, lds, dst, ldd, rows, cols, 1, stream);
+}
+
+extern "C" int sg_conv_pack(const void* w, int w_bf16, long long ldw, int F, int C, int k, void* fwd, long long ldfwd,
+                            int cp_f, void* dgrad, long long lddgrad, int fp_d, int out_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  SG_REQUIRE(w != nullptr && fwd != nullptr && F > 0 && C > 0 && k > 0 && cp_f >= C, "sg_conv_pack: bad arguments");
+  SG_REQUIRE(dgrad == nullptr || fp_d >= F, "sg_conv_pack: data-gradient pack narrower than the filter count");
+  const long long total = static_cast<long long>(F) * ldfwd + (dgrad ? static_cast<long long>(C) * lddgrad : 0);
+  const int grid = ew_grid(total, 256);
+#define SG_PACK(S, D) conv_pack_kernel<S, D><<<grid, 256, 0, s>>>((const S*)w, ldw, F, C, k, (D*)fwd, ldfwd, cp_f, (D*)dgrad, lddgrad, fp_d)
+  if (w_bf16 && out_bf16) SG_PACK(__nv_bfloat16, __nv_bfloat16);
+  else if (w_bf16) SG_PACK(__nv_bfloat16, float);
+  else if (out_bf16) SG_PACK(float, __nv_bfloat16);
+  else SG_PACK(float, float);
+#undef SG_PACK
+  SG_CHECK_LAUNCH("conv_pack");
+  return 0;
 }

@@ -55,7 +55,8 @@ struct GemmParams {
   const unsigned long long* const* wait_flags;   // device array of nwait flag addresses
   const unsigned long long* wait_seq;
   int ldd32, ldd16, ldaux;
-  int perm_c, perm_kk;
+  int perm_c;                   // > 0: column n = (tap * perm_c + c) is stored at column c * perm_kk + tap ...
+  short perm_kk, perm_valid;    // ... and dropped when perm_valid > 0 and c >= perm_valid (zero-padded channel chunks)
   short nwait, split_k;
   unsigned char act, grad_act, aux_bf16, accumulate, bias_bf16;
 };
@@ -65,7 +66,7 @@ static_assert(sizeof(GemmParams) <= 96, "GemmParams grew: see the launch-latency
 // into this GPU's bf16 mirror by the server shards' push kernels (peer stores over NVLink).  The TMA producer thread
 // acquires their version counters here, then orders the generic-proxy acquire before the async-proxy (TMA) reads.
 // Kept out of line so the common (no wait) path carries no extra code or registers.
-__device__ __noinline__ void wait_param_versions(const unsigned long long* const* flags, int nwait,
+static __device__ __noinline__ void wait_param_versions(const unsigned long long* const* flags, int nwait,
                                                  const unsigned long long* seq) {
   const unsigned long long target = *seq;
   for (int i = 0; i < nwait; ++i) {
@@ -298,7 +299,12 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, const uint32
             : reinterpret_cast<const float*>(p.aux)[row * p.ldaux + n];
         x *= act_grad_from_output(y, p.grad_act);
       }
-      const int nout = p.perm_c > 0 ? (n % p.perm_c) * p.perm_kk + (n / p.perm_c) : n;
+      int nout = n;
+      if (p.perm_c > 0) {
+        const int tap = n / p.perm_c, c = n - tap * p.perm_c;
+        if (p.perm_valid > 0 && c >= p.perm_valid) continue;
+        nout = c * p.perm_kk + tap;
+      }
       if (p.d32 != nullptr) {
         float* dp = p.d32 + row * p.ldd32 + nout;
         if (p.accumulate == 2) {

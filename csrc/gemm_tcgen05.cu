@@ -622,7 +622,8 @@ extern "C" int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, 
   p.bias = ep->bias; p.bias_bf16 = ep->bias_bf16 != 0;
   p.act = static_cast<unsigned char>(ep->act); p.grad_act = static_cast<unsigned char>(ep->grad_act);
   p.aux = ep->aux; p.ldaux = static_cast<int>(ep->ldaux); p.aux_bf16 = ep->aux_bf16 != 0;
-  p.accumulate = ep->accumulate != 0; p.perm_c = ep->perm_c; p.perm_kk = ep->perm_kk;
+  SG_REQUIRE(ep->perm_kk >= 0 && ep->perm_kk < 32768, "sg_gemm: perm_kk out of range");
+  p.accumulate = ep->accumulate != 0; p.perm_c = ep->perm_c; p.perm_kk = static_cast<short>(ep->perm_kk); p.perm_valid = 0;
   SG_REQUIRE(ep->nwait >= 0 && ep->nwait <= 64, "sg_gemm: at most 64 wait flags");
   SG_REQUIRE(ep->nwait == 0 || (ep->wait_seq != nullptr && ep->wait_flags != nullptr),
              "sg_gemm: wait flags need the flag list and wait_seq");

@@ -142,13 +142,51 @@ int sg_lrn_fwd(const void* x, void* y, float* norm, long long pixels, int C, int
 int sg_lrn_bwd(const void* x, const float* norm, const void* dy, void* dx, long long pixels, int C,
                int lsize, float alpha, float beta, int is_bf16, void* stream);
 
-/* Convolution lowering (src/worker/layer.cc:63-123): bf16 NHWC patches -> col[pixels][ld] with column
- * (ky*k+kx)*C + c, and the gather-form inverse for the data gradient (optionally fused with the
- * activation gradient of the layer below; aux = that layer's output, bf16 NHWC). */
+/* Explicit convolution lowering (src/worker/layer.cc:63-123): NHWC patches -> col[pixels][ld] with column
+ * (ky*k+kx)*C + c, and the gather-form inverse for the data gradient (optionally fused with the activation gradient
+ * of the layer below; aux = that layer's output, NHWC).  Only two cases still use it — everything else runs as
+ * implicit GEMM (sg_conv_rows / sg_conv_wgrad): the weight gradient of convolutions whose pixels are narrower than
+ * 64 bytes (RGB / grey inputs), and the data gradient of strided convolutions. */
+int sg_im2col(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH, int OW,
+              int k, int stride, int pad, int is_bf16, void* stream);
+int sg_col2im(const void* dcol, long long ld, void* dx, int N, int H, int W, int C, int OH, int OW,
+              int k, int stride, int pad, int grad_act, const void* aux, int is_bf16, void* stream);
+/* the bf16 forms */
 int sg_im2col_nhwc(const void* x, void* col, long long ld, int N, int H, int W, int C, int OH, int OW,
                    int k, int stride, int pad, void* stream);
 int sg_col2im_nhwc(const void* dcol, long long ld, void* dx, int N, int H, int W, int C, int OH, int OW,
                    int k, int stride, int pad, int grad_act, const void* aux, void* stream);
+
+/* Implicit-GEMM convolution (src/worker/layer.cc:63-123): the patch matrix is built tile by tile inside the GEMM by
+ * im2col-mode TMA loads from the channels-last activation; nothing is materialised in global memory.
+ *   source tensor  [N][H][W][C] with pixels ldc elements apart (ldc * element size a multiple of 16 bytes)
+ *   row grid       OH x OW positions per image; position (oy, ox) reads source pixel (oy*stride - pad_lo + ky, ...)
+ * sg_conv_rows: acc[pixel][n] = sum_{ky,kx,c} src(pixel; ky,kx,c) * filt[n][(ky*k + kx) * Cp + c], followed by the
+ *   sg_gemm epilogue on D[pixels][ncols].  filt is packed K-major with Cp = nchunk * chunk channels per tap (zero
+ *   padded; rows padded to whole 128-byte k-blocks; ldf elements apart), chunk = chunk_bytes / element size,
+ *   chunk_bytes in {16, 32, 64, 128} (sg_conv_chunk_bytes picks one for a channel count).
+ *   forward:        src = X,  filt = W as [F][(ky,kx,c)],  pad_lo = pad
+ *   data gradient   (stride 1): src = dY, row grid = the input image, pad_lo = k-1-pad,
+ *                   filt = [C][(jy,jx,f)] with W's taps flipped
+ * sg_conv_wgrad: dw[f][c*k*k + ky*k + kx] (+)= sum_pixel dy[pixel][f] * src(pixel; ky,kx,c)   ({F, C*k*k} layout of
+ *   the reference), split over the pixels with fp32 atomics when there are few output tiles. */
+typedef struct SgConvGeom {
+  int N, H, W, C;        /* source tensor */
+  long long ldc;         /* elements between pixels of the source (>= C) */
+  int OH, OW;            /* row grid per image */
+  int k, stride, pad_lo;
+  int chunk_bytes;       /* sg_conv_rows only */
+} SgConvGeom;
+int sg_conv_chunk_bytes(int channels, int elem_bytes);
+int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, const void* filt, long long ldf, int ncols,
+                 const SgGemmEpilogue* ep, void* stream);
+int sg_conv_wgrad(int dtype, const void* src, const SgConvGeom* g, const void* dy, long long lddy, int F, float* dw,
+                  long long lddw, int accumulate, void* stream);
+/* Filter packing for sg_conv_rows from the reference layout w[F][C*k*k] (column (c*k + ky)*k + kx; fp32 or bf16 source,
+ * ldw elements per row): fwd[f][(ky*k+kx)*Cp_f + c] = w[f][c][ky][kx] and, when dgrad != NULL,
+ * dgrad[c][(jy*k+jx)*Fp_d + f] = w[f][c][k-1-jy][k-1-jx]; padding written as zeros; outputs bf16 or fp32 (out_bf16). */
+int sg_conv_pack(const void* w, int w_bf16, long long ldw, int F, int C, int k, void* fwd, long long ldfwd, int cp_f,
+                 void* dgrad, long long lddgrad, int fp_d, int out_bf16, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Updaters over the flat parameter arena (src/utils/updater.cc:54-182) and PS exchange rules

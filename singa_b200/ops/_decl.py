@@ -4,6 +4,11 @@ import ctypes as C
 vp, i32, i64, f32, u64 = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_ulonglong
 
 
+class ConvGeom(C.Structure):
+    _fields_ = [("N", i32), ("H", i32), ("W", i32), ("C", i32), ("ldc", i64), ("OH", i32), ("OW", i32),
+                ("k", i32), ("stride", i32), ("pad_lo", i32), ("chunk_bytes", i32)]
+
+
 class Updater(C.Structure):
     _fields_ = [("kind", i32), ("lr", f32), ("momentum", f32), ("weight_decay", f32), ("delta", f32),
                 ("rho", f32), ("grad_scale", f32), ("lr_dev", vp)]
@@ -29,6 +34,9 @@ SIGNATURES = {
     "sg_pool_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "sg_lrn_fwd": [vp, vp, vp, i64, i32, i32, f32, f32, f32, i32, vp],
     "sg_lrn_bwd": [vp, vp, vp, vp, i64, i32, i32, f32, f32, i32, vp],
+    "sg_im2col": [vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
+    "sg_col2im": [vp, i64, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, i32, vp],
+    "sg_conv_pack": [vp, i32, i64, i32, i32, i32, vp, i64, i32, vp, i64, i32, i32, vp],
     "sg_im2col_nhwc": [vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "sg_col2im_nhwc": [vp, i64, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp],
     "sg_update_arena": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.POINTER(Updater), vp],

@@ -115,12 +115,69 @@ def lrn_bwd(x, norm, dy, dx, pixels, C, lsize, alpha, beta):
 
 
 def im2col_nhwc(x, col, ld, N, H, W, C, OH, OW, k, s, pad):
-    _call("sg_im2col_nhwc", x.data_ptr(), col.data_ptr(), ld, N, H, W, C, OH, OW, k, s, pad)
+    _call("sg_im2col", x.data_ptr(), col.data_ptr(), ld, N, H, W, C, OH, OW, k, s, pad, _bf(x))
 
 
 def col2im_nhwc(dcol, ld, dx, N, H, W, C, OH, OW, k, s, pad, grad_act=ACT_NONE, aux=None):
-    _call("sg_col2im_nhwc", dcol.data_ptr(), ld, dx.data_ptr(), N, H, W, C, OH, OW, k, s, pad, grad_act,
-          native.ptr(aux))
+    _call("sg_col2im", dcol.data_ptr(), ld, dx.data_ptr(), N, H, W, C, OH, OW, k, s, pad, grad_act,
+          native.ptr(aux), _bf(dx))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Implicit-GEMM convolution (csrc/conv_implicit.cu)
+# ---------------------------------------------------------------------------------------------------------
+def conv_chunk_bytes(channels: int, elem_bytes: int) -> int:
+    return _lib().sg_conv_chunk_bytes(channels, elem_bytes)
+
+
+def conv_geom(N, H, W, C, ldc, OH, OW, k, stride, pad_lo, chunk_bytes=128):
+    from ._decl import ConvGeom
+    return ConvGeom(N, H, W, C, ldc, OH, OW, k, stride, pad_lo, chunk_bytes)
+
+
+def _epilogue(out, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None, wait=None):
+    ep = native.GemmEpilogue()
+    assert out.stride(-1) == 1 or out.shape[-1] == 1
+    if out.dtype == torch.float32:
+        ep.d32, ep.ldd32 = out.data_ptr(), out.stride(0)
+    else:
+        assert out.dtype == torch.bfloat16
+        ep.d16, ep.ldd16 = out.data_ptr(), out.stride(0)
+    if bias is not None:
+        ep.bias = bias.data_ptr()
+        ep.bias_bf16 = _bf(bias)
+    ep.act, ep.grad_act = act, grad_act
+    if grad_act != ACT_NONE:
+        assert aux is not None and (aux.stride(-1) == 1 or aux.shape[-1] == 1)
+        ep.aux, ep.ldaux, ep.aux_bf16 = aux.data_ptr(), aux.stride(0), _bf(aux)
+    if wait is not None:
+        flags, seq = wait
+        ep.wait_flags, ep.nwait, ep.wait_seq = flags.data_ptr(), flags.numel(), seq
+    return ep
+
+
+def conv_rows(src, geom, filt, ncols, out2d, *, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None, wait=None):
+    """out2d[pixel][n] = epilogue(sum_k patch(src; pixel, k) * filt[n][k]) — forward and stride-1 data gradient."""
+    ep = _epilogue(out2d, bias, act, grad_act, aux, wait)
+    assert filt.dtype == src.dtype and filt.stride(-1) == 1
+    rc = _lib().sg_conv_rows(0 if _bf(src) else 1, src.data_ptr(), ctypes.byref(geom), filt.data_ptr(), filt.stride(0),
+                             ncols, ctypes.byref(ep), native.stream_ptr())
+    native.check(rc, "sg_conv_rows")
+    native.count_launch()
+
+
+def conv_wgrad(src, geom, dy2d, F, dw, accumulate=False):
+    """dw[f][c*k*k + tap] (+)= sum_pixel dy2d[pixel][f] * patch(src; pixel, tap, c)."""
+    assert dy2d.dtype == src.dtype and dy2d.stride(-1) == 1 and dw.dtype == torch.float32 and dw.stride(-1) == 1
+    rc = _lib().sg_conv_wgrad(0 if _bf(src) else 1, src.data_ptr(), ctypes.byref(geom), dy2d.data_ptr(), dy2d.stride(0),
+                              F, dw.data_ptr(), dw.stride(0), 1 if accumulate else 0, native.stream_ptr())
+    native.check(rc, "sg_conv_wgrad")
+    native.count_launch(1 if accumulate else 2)
+
+
+def conv_pack(w, ldw, F, C, k, fwd, cp_f, dgrad=None, fp_d=0):
+    _call("sg_conv_pack", w.data_ptr(), _bf(w), ldw, F, C, k, fwd.data_ptr(), fwd.stride(0), cp_f,
+          native.ptr(dgrad), dgrad.stride(0) if dgrad is not None else 0, fp_d, _bf(fwd))
 
 
 UPD_SGD, UPD_NESTEROV, UPD_ADAGRAD, UPD_RMSPROP, UPD_ADADELTA = range(5)

@@ -45,6 +45,13 @@ def _declare(lib):
         ctypes.POINTER(GemmEpilogue), ctypes.c_void_p,
     ]
     lib.sg_gemm.argtypes = [ctypes.c_int] + list(lib.sg_gemm_bf16.argtypes)
+    from ._decl import ConvGeom
+    lib.sg_conv_chunk_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.sg_conv_rows.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ConvGeom), ctypes.c_void_p,
+                                 ctypes.c_longlong, ctypes.c_int, ctypes.POINTER(GemmEpilogue), ctypes.c_void_p]
+    lib.sg_conv_wgrad.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ConvGeom), ctypes.c_void_p,
+                                  ctypes.c_longlong, ctypes.c_int, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int,
+                                  ctypes.c_void_p]
     lib.sg_gemm_set_tile.argtypes = [ctypes.c_int]
     lib.sg_gemm_set_pair.argtypes = [ctypes.c_int]
 
