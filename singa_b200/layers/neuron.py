@@ -270,8 +270,9 @@ class InnerProductLayer(NeuronLayer):
 class ConvolutionLayer(NeuronLayer):
     """weight {F, C*k*k}, bias {F}; out = (H + 2p - k)/s + 1  (src/worker/layer.cc:18-123).
 
-    Native path: ONE batched GEMM over all images, D[pixels][F] = col[pixels][k*k*C] . W16[F][k*k*C]^T with
-    bias(+ReLU) in the epilogue, writing channels-last output directly; wgrad and dgrad are GEMMs too."""
+    Native path (``ops/conv.py``): implicit GEMM — ONE launch over all images per direction, the patch tiles built
+    by TMA im2col loads inside the tcgen05 kernel, bias(+ReLU/tanh) in the forward epilogue, act' of the layer below
+    in the data-gradient epilogue, channels-last output written directly."""
     type_id = "kConvolution"
 
     def connection_type(self, k):
@@ -313,36 +314,19 @@ class ConvolutionLayer(NeuronLayer):
             self._setup_native()
 
     def _setup_native(self):
-        dev = ctx().device
-        if not ctx().is_bf16:
-            raise NotImplementedError("convolution on the fp32 (tf32) path arrives with the implicit-GEMM kernel")
-        F_, K_ = self.num_filters, self.col_height
+        from ..ops.conv import ConvPlan
+        src = self.srclayers[0]
+        need_dgrad = not (src.is_datalayer or src.is_parserlayer)
         self.P = self.batchsize * self.col_width
-        self.Kpad = pad8(K_)
-        self.Fpad = pad8(F_)
-        self.pointwise = self.kernel == 1 and self.stride == 1 and self.pad == 0 and self.channels % 8 == 0
-        # per-layer column buffer kept from forward to backward (HBM is plentiful; no recompute)
-        self.col = None if self.pointwise else torch.zeros(self.P, self.Kpad, dtype=torch.bfloat16, device=dev)
-        # bf16 weights repacked to (ky,kx,c) column order to match the channels-last patches
-        self.w16_packed = torch.zeros(F_, self.Kpad, dtype=torch.bfloat16, device=dev)
-        self.weight.data16 = self.w16_packed[:, :K_]
-        kk = self.kernel * self.kernel
+        self.plan = ConvPlan(self.batchsize, self.channels, self.height, self.width, self.num_filters, self.kernel,
+                             self.stride, self.pad, ctx().act_dtype, ctx().device, need_dgrad=need_dgrad)
+        self.weight.data16 = self.plan.wf      # the forward GEMM's filter operand ([F][(ky,kx,c)], zero padded)
 
-        def pack(w=self.weight, dst=self.w16_packed):
-            # from the fp32 master copy, or — on a rank that is not this parameter's server — from the bf16
-            # mirror the parameter server broadcasts into
-            if getattr(w, "pack_from_mirror", False):
-                m = w.mirror16
-                _K().repack_bf16(m, m.stride(0), dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
-            else:
-                _K().cast_pack(w.data, K_, dst, dst.stride(0), F_, K_, perm=(self.channels, kk))
+        def pack(w=self.weight, plan=self.plan):
+            # from the fp32 master copy, or — on a rank that is not this parameter's server — from the mirror the
+            # parameter server broadcasts into
+            plan.pack(w.mirror16 if getattr(w, "pack_from_mirror", False) and w.mirror16 is not None else w.data)
         self.weight.pack16 = pack
-        # scratch: dcol [P][Kpad] in the workspace shared by all conv layers (used and consumed within one
-        # data-gradient step); a padded copy of dy [P][Fpad] per layer when F % 8 != 0 (read by both gradient GEMMs)
-        self.ws_bytes = self.P * self.Kpad * 2
-        workspace.reserve(self.ws_bytes)
-        self.dy_pad = [torch.zeros(self.P, self.Fpad, dtype=torch.bfloat16, device=dev) for _ in range(2)] \
-            if F_ % 8 else None
 
     def get_params(self):
         return [self.weight, self.bias] if self.bias_term else [self.weight]
@@ -360,19 +344,9 @@ class ConvolutionLayer(NeuronLayer):
     def compute_feature(self, training):
         src = self._src_nhwc()
         if self.native:
-            K = _K()
-            N, H, W, C = self.batchsize, self.height, self.width, self.channels
-            if self.pointwise:
-                col, ld = src.permute(0, 2, 3, 1).reshape(self.P, C), C
-            else:
-                K.im2col_nhwc(src, self.col, self.Kpad, N, H, W, C, self.conv_height, self.conv_width,
-                              self.kernel, self.stride, self.pad)
-                col = self.col[:, :self.col_height]
-            y2d = self.data.permute(0, 2, 3, 1).reshape(self.P, self.num_filters)   # view of NHWC storage
-            assert y2d.data_ptr() == self.data.data_ptr()
-            K.gemm(col, self._w16(), self.P, self.num_filters, self.col_height,
-                   out16=y2d, bias=self._bias_operand() if self.bias_term else None, act=self.fused_act)
-            self._col_saved = col
+            from ..ops.conv import _mat
+            y2d = _mat(self.data, self.P, self.num_filters, self.num_filters)    # view of the NHWC storage
+            self.plan.forward(src, y2d, bias=self._bias_operand() if self.bias_term else None, act=self.fused_act)
         else:
             x = src.float()
             if x.dim() == 3:
@@ -392,31 +366,14 @@ class ConvolutionLayer(NeuronLayer):
         self.compute_param_gradient()
         self.compute_data_gradient()
 
-    def _dy_operand(self, which: int = 0):
-        """dY as a [P][F] bf16 matrix with a TMA-legal row stride (a padded copy when F % 8).  The parameter
-        and the data gradient run on different streams, so each has its own padded buffer (``which``)."""
-        K = _K()
-        F_, P = self.num_filters, self.P
-        dy2d = self.grad.permute(0, 2, 3, 1).reshape(P, F_)
-        if F_ % 8:
-            dyp = self.dy_pad[which]
-            K.copy2d_bf16(dy2d, F_, dyp, self.Fpad, P, F_)
-            return dy2d, dyp[:, :F_]
-        return dy2d, dy2d
-
     def compute_param_gradient(self):
         if self.native:
-            K = _K()
-            F_, K_, P = self.num_filters, self.col_height, self.P
             accumulate = getattr(self, "_accumulate_wgrad", False)
-            dy2d, dy_op = self._dy_operand(0)
             if self.bias_term:
-                K.colsum(dy2d, P, F_, F_, self.bias.grad, accumulate=accumulate)
-            kk = self.kernel * self.kernel
-            # dW[F][K] = dY^T col : A = dY stored [K=P][M=F], B = col stored [K=P][N=K_]; columns come out in
-            # (ky,kx,c) order and are stored in the reference's (c,ky,kx) order by the epilogue permutation
-            K.gemm(dy_op, self._col_saved, F_, K_, P, a_mn=True, b_mn=True, out32=self.weight.grad,
-                   accumulate=accumulate, perm=(self.channels, kk) if kk > 1 and self.channels > 1 else None)
+                from ..ops.conv import _mat
+                F_ = self.num_filters
+                _K().colsum(_mat(self.grad, self.P, F_, F_), self.P, F_, F_, self.bias.grad, accumulate=accumulate)
+            self.plan.wgrad(self.grad, self.weight.grad, accumulate=accumulate)
         else:
             self._dx_ref, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
                                               self.stride, self.pad, self._need_src_grad())
@@ -434,20 +391,10 @@ class ConvolutionLayer(NeuronLayer):
             return
         dst, aux = self._src_grad()
         if self.native:
-            K = _K()
-            F_, K_, P = self.num_filters, self.col_height, self.P
-            N, H, W, C = self.batchsize, self.height, self.width, self.channels
-            dy_op = self._dy_operand(1)[1]
-            if self.pointwise:
-                d2 = dst.permute(0, 2, 3, 1).reshape(P, C)
-                a2 = aux.permute(0, 2, 3, 1).reshape(P, C) if aux is not None else None
-                K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=d2, grad_act=self.src_grad_act, aux=a2)
-            else:
-                dcol = workspace.view((P, self.Kpad), torch.bfloat16)
-                # dcol[P][K] = dY[P][F] . W16[F][K] : B(n=K idx, k=F idx) stored [K=F][N=K_]
-                K.gemm(dy_op, self._w16(), P, K_, F_, b_mn=True, out16=dcol[:, :K_])
-                K.col2im_nhwc(dcol, self.Kpad, dst, N, H, W, C, self.conv_height, self.conv_width,
-                              self.kernel, self.stride, self.pad, self.src_grad_act, aux)
+            from ..ops.conv import _mat
+            rows, C = self.batchsize * self.height * self.width, self.channels
+            self.plan.dgrad(self.grad, _mat(dst, rows, C, C), grad_act=self.src_grad_act,
+                            aux2d=_mat(aux, rows, C, C) if aux is not None else None)
         else:
             dx = self._dx_ref
             if aux is not None:
@@ -541,7 +488,9 @@ class DropoutLayer(NeuronLayer):
         if self.native:
             _K().dropout(x, self.data, self.pkeep, self.seed_base, step_state()["step"])
         else:
-            m = R.dropout_mask(self.seed_base + int(step_state()['host_step'][0]), x.numel(), self.pkeep, x.device).view(x.shape)
+            # same seed mixing as csrc/elementwise.cu::dropout_kernel, so both backends draw the same mask
+            mixed = self.seed_base ^ (((int(step_state()['host_step'][0]) + 1) * 0x9E3779B97F4A7C15) & (2**64 - 1))
+            m = R.dropout_mask(mixed, x.numel(), self.pkeep, x.device).view(x.shape)
             self._mask = m
             self.data.copy_(x.float() * m)
 
