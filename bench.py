@@ -196,6 +196,11 @@ def main():
 
     def step_device(step):
         ex.ticks += 1
+        if ex.rotate:                   # rotated schedule: backward(step) + push || forward(step + 1) per replay
+            for p in net.parserlayers:
+                p.reparse_next(True)
+            ex._run_rotated(step, feed=False)
+            return
         w.pm.begin_step(step)
         for p in net.parserlayers:      # re-parse the device-resident staged batch (no host traffic)
             p.reparse(True)
@@ -316,6 +321,8 @@ def main():
                               "bf16": "bf16 operands, fp32 accumulate, fp32 master weights + optimizer state",
                               "fp32-strict": "fp32 FMA, TF32 off"}[args.dtype],
                 "cuda_graph": ex._graph is not None,
+                "schedule": "rotated (backward(t) + push(t) || forward(t+1) per graph replay)" if ex.rotate
+                            else "forward(t), backward(t) + push(t) per graph replay",
                 "l2": ("per-step working set %.0f MB > 126 MB L2 (no flush needed)" % (ws_bytes / 2**20))
                       if flush is None else "L2 flushed (252 MB write) between timed steps, per-step events",
             },

@@ -121,14 +121,19 @@ __global__ void colsum_kernel(const T* __restrict__ x, long long ld, int rows, i
   }
 }
 
-// bf16 input with cols % 8 == 0: every thread owns 8 adjacent columns (one 128-bit load per row, four rows in
-// flight), CVB column vectors x (256 / CVB) row lanes per block; the row lanes are merged through shared memory and
-// the block adds its partial sums with one atomicAdd per column.  (The 2-byte-per-lane kernel above reached
-// 1.4 TB/s; tall-skinny bias gradients of the first convolutions — 774 400 x 96 — took 25 % of all reduction time.)
+// Vector form: every thread owns one 16-byte vector of adjacent columns (8 bf16 or 4 fp32; one 128-bit load per row,
+// four rows in flight), CVB column vectors x (256 / CVB) row lanes per block; the row lanes are merged through shared
+// memory and the block adds its partial sums with one atomicAdd per column.  Needs a 16-byte aligned base and a row
+// stride that is a multiple of 16 bytes (true for every activation / gradient buffer of the framework, whose rows are
+// padded); a ragged last vector reads the row padding and its extra columns are dropped.  (The 2- or 4-byte-per-lane
+// kernel above reaches 1.4 TB/s; tall-skinny bias gradients of the first convolutions — 774 400 x 96 — took 25 % of
+// all reduction time, and the 1000 x 2500 bias gradients of the MLP sat on the critical path of the last push.)
+template <typename T>
 __global__ void __launch_bounds__(256)
-colsum_bf16_vec8_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int rows, int cvecs, int cvb,
-                        float* __restrict__ out) {
-  __shared__ float part[256 * 8];
+colsum_vec_kernel(const T* __restrict__ x, long long ld, int rows, int cols, int cvecs, int cvb,
+                  float* __restrict__ out) {
+  constexpr int EPV = 16 / sizeof(T);
+  __shared__ float part[256 * EPV];
   const int lanes_r = 256 / cvb;                         // row lanes per block
   const int cv_in = threadIdx.x % cvb;
   const int ry = threadIdx.x / cvb;
@@ -136,9 +141,24 @@ colsum_bf16_vec8_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int r
   const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
   const int r0 = blockIdx.y * rows_per;
   const int r1 = min(rows, r0 + rows_per);
-  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float acc[EPV];
+#pragma unroll
+  for (int j = 0; j < EPV; ++j) acc[j] = 0.f;
+  auto add = [&](const uint4& u) {
+    if (EPV == 8) {
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        acc[(2 * t) % EPV] += __uint_as_float(w[t] << 16);
+        acc[(2 * t + 1) % EPV] += __uint_as_float(w[t] & 0xFFFF0000u);
+      }
+    } else {
+      acc[0] += __uint_as_float(u.x); acc[1] += __uint_as_float(u.y);
+      acc[2] += __uint_as_float(u.z); acc[3] += __uint_as_float(u.w);
+    }
+  };
   if (cv < cvecs && ry < lanes_r) {
-    const __nv_bfloat16* base = x + static_cast<long long>(cv) * 8;
+    const T* base = x + static_cast<long long>(cv) * EPV;
     int r = r0 + ry;
     for (; r + 3 * lanes_r < r1; r += 4 * lanes_r) {
       uint4 u[4];
@@ -146,35 +166,20 @@ colsum_bf16_vec8_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int r
       for (int i = 0; i < 4; ++i)
         u[i] = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r + i * lanes_r) * ld));
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const uint32_t w[4] = {u[i].x, u[i].y, u[i].z, u[i].w};
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          acc[2 * t] += __uint_as_float(w[t] << 16);
-          acc[2 * t + 1] += __uint_as_float(w[t] & 0xFFFF0000u);
-        }
-      }
+      for (int i = 0; i < 4; ++i) add(u[i]);
     }
-    for (; r < r1; r += lanes_r) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * ld));
-      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        acc[2 * t] += __uint_as_float(w[t] << 16);
-        acc[2 * t + 1] += __uint_as_float(w[t] & 0xFFFF0000u);
-      }
-    }
+    for (; r < r1; r += lanes_r) add(__ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * ld)));
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) part[threadIdx.x * 8 + j] = acc[j];
+  for (int j = 0; j < EPV; ++j) part[threadIdx.x * EPV + j] = acc[j];
   __syncthreads();
-  // thread t < cvb * 8 owns column (t) of this block: sum over the row lanes
-  const int ncol = cvb * 8;
+  // thread t < cvb * EPV owns column t of this block: sum over the row lanes
+  const int ncol = cvb * EPV;
   for (int t = threadIdx.x; t < ncol; t += 256) {
     const int col = blockIdx.x * ncol + t;
-    if (col >= cvecs * 8) continue;
+    if (col >= cols) continue;
     float sum = 0.f;
-    for (int k = 0; k < lanes_r; ++k) sum += part[(k * cvb + t / 8) * 8 + (t & 7)];
+    for (int k = 0; k < lanes_r; ++k) sum += part[(k * cvb + t / EPV) * EPV + (t % EPV)];
     atomicAdd(out + col, sum);
   }
 }
@@ -419,8 +424,9 @@ extern "C" int sg_colsum(const void* x, long long ld, int rows, int cols, float*
   if (!accumulate) {
     if (check_cuda(cudaMemsetAsync(out, 0, sizeof(float) * cols, s), "colsum memset")) return 1;
   }
-  if (is_bf16 && cols % 8 == 0 && ld % 8 == 0 && ((reinterpret_cast<uintptr_t>(x) & 15) == 0)) {
-    const int cvecs = cols / 8;
+  const int epv = is_bf16 ? 8 : 4;
+  if (ld % epv == 0 && ((reinterpret_cast<uintptr_t>(x) & 15) == 0)) {
+    const int cvecs = (cols + epv - 1) / epv;
     int cvb = 1;
     while (cvb < 32 && cvb < cvecs) cvb <<= 1;           // power of two: 256 % cvb == 0
     const int lanes_r = 256 / cvb;
@@ -429,8 +435,11 @@ extern "C" int sg_colsum(const void* x, long long ld, int rows, int cols, float*
     const int max_gyv = (rows + lanes_r * 8 - 1) / (lanes_r * 8);
     if (gyv > max_gyv) gyv = max_gyv;
     if (gyv < 1) gyv = 1;
-    colsum_bf16_vec8_kernel<<<dim3(gxv, gyv), 256, 0, s>>>((const __nv_bfloat16*)x, ld, rows, cvecs, cvb, out);
-    SG_CHECK_LAUNCH("colsum_vec8");
+    if (is_bf16)
+      colsum_vec_kernel<__nv_bfloat16><<<dim3(gxv, gyv), 256, 0, s>>>((const __nv_bfloat16*)x, ld, rows, cols, cvecs, cvb, out);
+    else
+      colsum_vec_kernel<float><<<dim3(gxv, gyv), 256, 0, s>>>((const float*)x, ld, rows, cols, cvecs, cvb, out);
+    SG_CHECK_LAUNCH("colsum_vec");
     return 0;
   }
   const int gx = (cols + 31) / 32;

@@ -108,36 +108,42 @@ _RING = 512      # pinned staging slots: the host may run hundreds of (graph-rep
 
 def step_state() -> dict:
     """Per-step scalars kept in DEVICE memory so that a captured CUDA graph follows them without
-    re-capture: ``lr`` (fp32[1], read by the fused updater) and ``step`` (int64[1], mixed into dropout seeds).
-    Both live in one 16-byte device buffer that the executor refreshes with ONE tiny async copy per step from a
-    ring of pinned host slots (a slot is not rewritten until ``_RING`` steps later, so a pending copy never reads
-    a newer step's values)."""
+    re-capture: ``lr`` (fp32[1], read by the fused updater), ``step`` (int64[1], mixed into the dropout seeds of the
+    forward pass) and ``step_bwd`` (int64[1], the same for the backward pass — it differs from ``step`` only when the
+    executor runs the rotated schedule, where one graph holds backward(t) and forward(t+1)).  All live in one 32-byte
+    device buffer that the executor refreshes with ONE tiny async copy per step from a ring of pinned host slots (a
+    slot is not rewritten until ``_RING`` steps later, so a pending copy never reads a newer step's values)."""
     global _step_state
     c = ctx()
     if _step_state is None or _step_state["lr"].device != c.device:
         pin = c.device.type == "cuda"
-        dev = torch.zeros(16, dtype=torch.uint8, device=c.device)
-        host = torch.zeros(_RING, 16, dtype=torch.uint8, pin_memory=pin)
+        dev = torch.zeros(32, dtype=torch.uint8, device=c.device)
+        host = torch.zeros(_RING, 32, dtype=torch.uint8, pin_memory=pin)
         _step_state = {
             "buf": dev,
             "step": dev.view(torch.int64)[0:1],
             "lr": dev.view(torch.float32)[2:3],
+            "step_bwd": dev.view(torch.int64)[2:3],
             "host": host,
-            "host_step_view": host.view(torch.int64).view(_RING, 2),
-            "host_lr_view": host.view(torch.float32).view(_RING, 4),
+            "host_step_view": host.view(torch.int64).view(_RING, 4),
+            "host_lr_view": host.view(torch.float32).view(_RING, 8),
             "host_step": torch.zeros(1, dtype=torch.int64),      # last values published (host-side readers)
+            "host_step_bwd": torch.zeros(1, dtype=torch.int64),
             "host_lr": torch.zeros(1, dtype=torch.float32),
             "slot": 0,
         }
     return _step_state
 
 
-def set_step_state(step: int, lr: float) -> None:
+def set_step_state(step: int, lr: float, step_bwd: int | None = None) -> None:
     st = step_state()
     k = st["slot"]
     st["slot"] = (k + 1) % _RING
+    sb = step if step_bwd is None else step_bwd
     st["host_step_view"][k, 0] = step
+    st["host_step_view"][k, 2] = sb
     st["host_lr_view"][k, 2] = lr
     st["host_step"][0] = step
+    st["host_step_bwd"][0] = sb
     st["host_lr"][0] = lr
     st["buf"].copy_(st["host"][k], non_blocking=True)

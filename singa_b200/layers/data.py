@@ -316,6 +316,29 @@ class ParserLayer(Layer):
             pe.record(torch.cuda.current_stream())
             self.parse_events[slot] = pe
 
+    # -- rotated schedule (Executor): batch t+1 is parsed into ``data_next`` while the graph of step t still needs
+    #    batch t; the graph copies it into ``data`` between backward(t) and forward(t+1)
+    def compute_feature_next(self, training: bool) -> None:
+        if getattr(self, "data_next", None) is None:
+            self.data_next = torch.empty_like(self.data)
+        cur, self.data = self.data, self.data_next
+        try:
+            self.compute_feature(training)
+        finally:
+            self.data = cur
+
+    def swap_in_next(self) -> None:
+        self.data.copy_(self.data_next)
+
+    def reparse_next(self, training: bool) -> None:
+        if getattr(self, "data_next", None) is None:
+            self.data_next = torch.empty_like(self.data)
+        cur, self.data = self.data, self.data_next
+        try:
+            self.parse(self.staging[self.last_slot], training)
+        finally:
+            self.data = cur
+
     def reparse(self, training: bool) -> None:
         """Parse the most recently consumed staged batch again (device-resident input, no host traffic)."""
         self.parse(self.staging[self.last_slot], training)

@@ -60,17 +60,20 @@ def shard_bounds(nchunks: int, world: int) -> List[Tuple[int, int]]:
     return [(min(r * per, nchunks), min((r + 1) * per, nchunks)) for r in range(world)]
 
 
-def make_buckets(layers, bucket_elems: int, chunk: int = 1024) -> List[List[str]]:
+def make_buckets(layers, bucket_elems: int, chunk: int = 1024, first_alone: bool = False) -> List[List[str]]:
     """Group parameter layers into push buckets.  ``layers``: [(name, first_chunk, nchunks)] in FORWARD order.  Walks
     in backward order (last layer first) merging layers that are adjacent in the arena until a bucket holds at least
     ``bucket_elems`` parameters; returns the buckets as lists of names in backward order, so ``bucket[-1]`` is the
     layer whose gradient arrives last — the one that triggers the push.  A bucket always covers one contiguous chunk
-    range (a gap in the arena closes the current bucket)."""
+    range (a gap in the arena closes the current bucket).  ``first_alone``: the first layer of the net — whose gradient
+    is the last one backward produces, so its push is the one nothing can hide — always forms its own bucket, keeping
+    the exposed push as small as possible."""
     buckets: List[List[str]] = []
     cur: List[str] = []
     cur_n, cur_lo = 0, None
-    for name, lo, n in reversed(list(layers)):
-        if cur and cur_lo != lo + n:
+    layers = list(layers)
+    for idx, (name, lo, n) in enumerate(reversed(layers)):
+        if cur and (cur_lo != lo + n or (first_alone and idx == len(layers) - 1)):
             buckets.append(cur)
             cur, cur_n = [], 0
         cur.append(name)
@@ -141,7 +144,9 @@ class FusedExchange:
         # 0.4425 ms at 8 GPUs / 0.374 at 2, against 0.454 / 0.380 with 2 M and 0.520 / 0.414 unbucketed); the bucket is
         # pushed when its LAST-visited (lowest) layer has its gradient.
         bucket_elems = int(os.environ.get("SINGA_B200_PUSH_BUCKET", str(6_000_000)))
-        names = make_buckets([(l.name, *pm.layer_ranges[l.name]) for l in self.layers], bucket_elems)
+        first_alone = os.environ.get("SINGA_B200_PUSH_FIRST_ALONE", "1") != "0"
+        names = make_buckets([(l.name, *pm.layer_ranges[l.name]) for l in self.layers], bucket_elems,
+                             first_alone=first_alone)
         by_name = {l.name: l for l in self.layers}
         self.buckets: List[List] = [[by_name[n] for n in b] for b in names]
         self.bucket_of = {l.name: b for b, ls in enumerate(self.buckets) for l in ls}
@@ -183,6 +188,10 @@ class FusedExchange:
                 l.pull_wait = (flag_list, self.wait_seq[i:i + 1].data_ptr())
         self.launches = 0
         self._used_comms = set()
+        # Rotated schedule (Executor.rotate): the next forward pass is enqueued while this step's pushes still run, so
+        # the consumer-side wait sequence must be advanced on the COMPUTE stream (pre_forward) — a forward GEMM that
+        # read it before the push kernel had started would accept the previous version of its weights.
+        self.main_bumps_seq = False
         # the fp32 master copy of a parameter is current only on its server; every other consumer (bias in the GEMM
         # epilogue, repacked conv weights) must read this rank's bf16 mirror
         if self.world > 1:
@@ -208,7 +217,7 @@ class FusedExchange:
             return                 # the bucket is pushed by its lowest layer; the comm stream has this gradient's events
         first, n = self.bucket_mine[i]
         ready_own = self.heap.ptr("ready", self.rank, i * 8)
-        seq_own = self.wait_seq[i:i + 1].data_ptr()
+        seq_own = None if self.main_bumps_seq else self.wait_seq[i:i + 1].data_ptr()
         if n <= 0:                 # no piece of this bucket to serve: only announce the local gradients
             native.check(self.lib.sg_ps_flag_bump(ctypes.c_void_p(ready_own), ctypes.c_void_p(seq_own),
                                                   comm.cuda_stream), "sg_ps_flag_bump")
@@ -257,6 +266,10 @@ class FusedExchange:
             if p.pack16 is not None:     # repacked operands (convolution weights) are re-derived from the mirror
                 p.pack_from_mirror = True
                 p.pack16()
+
+    def pre_forward(self, step: int) -> None:
+        assert self.main_bumps_seq, "pre_forward is part of the rotated schedule (the executor sets main_bumps_seq)"
+        self.wait_seq.add_(1)
 
     def end_step(self, step: int) -> None:
         # only streams that took work this step: joining an idle stream during graph capture is an error

@@ -34,7 +34,8 @@ class NcclExchange:
         assert self.arena.nchunks % self.world == 0, "arena must be padded to a multiple of the world size"
         self.layers = list(pm._param_layers)
         bucket_elems = int(os.environ.get("SINGA_B200_PUSH_BUCKET", str(6_000_000)))
-        names = make_buckets([(l.name, *pm.layer_ranges[l.name]) for l in self.layers], bucket_elems)
+        names = make_buckets([(l.name, *pm.layer_ranges[l.name]) for l in self.layers], bucket_elems,
+                             first_alone=os.environ.get("SINGA_B200_PUSH_FIRST_ALONE", "1") != "0")
         by_name = {l.name: l for l in self.layers}
         self.buckets: List[List] = [[by_name[n] for n in b] for b in names]
         self.bucket_of = {l.name: b for b, ls in enumerate(self.buckets) for l in ls}
@@ -48,6 +49,10 @@ class NcclExchange:
         on_gpu = ctx().device.type == "cuda"
         self.comm = torch.cuda.Stream() if on_gpu else None
         self._used = False
+        # per bucket: recorded on the comm stream behind the all-gather; a layer's forward waits for its bucket's event
+        # (needed by the executor's rotated schedule, where the next forward pass starts before the comm stream is joined)
+        self._gathered = [torch.cuda.Event() if on_gpu else None for _ in self.buckets]
+        self._gathered_valid = [False] * len(self.buckets)
         if self.world > 1 and self.arena.data16 is not None:
             for p in self.arena.params:
                 p.use_mirror = True
@@ -84,6 +89,9 @@ class NcclExchange:
                     for p in l.get_params():
                         if p.pack16 is not None:
                             p.pack16()
+            if self._gathered[b] is not None:
+                self._gathered[b].record(self.comm)
+                self._gathered_valid[b] = True
 
     def end_step(self, step: int) -> None:
         if self.comm is not None and self._used:
@@ -91,6 +99,11 @@ class NcclExchange:
         self._used = False
 
     def wait_layer(self, layer, step: int) -> None:
+        b = self.bucket_of.get(layer.name)
+        if b is not None and self._gathered[b] is not None and self._gathered_valid[b]:
+            torch.cuda.current_stream().wait_event(self._gathered[b])
+
+    def pre_forward(self, step: int) -> None:
         pass
 
     def owned_ranges(self) -> List[Tuple[int, int]]:

@@ -144,13 +144,19 @@ class ParamManager:
         if self.backend is not None:
             self.backend.get_all()
 
-    def begin_step(self, step: int) -> None:
-        """Publish LR(step) / step to device memory (keeps a captured graph valid across steps)."""
-        self.lr = self.updater.learning_rate(step)
+    def begin_step(self, step: int, lr_step: Optional[int] = None) -> None:
+        """Publish LR / step to device memory (keeps a captured graph valid across steps).  ``lr_step`` (rotated
+        schedule): the graph about to run holds backward + update of ``lr_step`` and the forward pass of ``step``."""
+        self.lr = self.updater.learning_rate(step if lr_step is None else lr_step)
         if self.use_device_lr:
-            set_step_state(step, self.lr)
+            set_step_state(step, self.lr, step if lr_step is None else lr_step)
         if self.backend is not None and hasattr(self.backend, "begin_step"):
             self.backend.begin_step(step)
+
+    def pre_forward(self, step: int) -> None:
+        """Rotated schedule: called between backward(step-1) and forward(step), on the compute stream."""
+        if self.backend is not None and hasattr(self.backend, "pre_forward"):
+            self.backend.pre_forward(step)
 
     def update_param(self, layer, step: int, side_stream=None) -> None:
         """Called right after ``layer``'s backward.  ``side_stream`` (optional) is the stream the layer's

@@ -98,6 +98,17 @@ class Executor:
         self._side_streams = [torch.cuda.Stream() for _ in range(nside)] \
             if (ctx().is_native and nside > 0) else None
         self.graph_kernel_count = 0
+        # Rotated schedule: one replayed unit = backward(t) + pushes(t) || forward(t+1).  The parameter pushes of step t
+        # then overlap the forward pass of step t+1 (each layer's forward waits for ITS weights only) instead of being
+        # joined at the end of backward, where nothing can hide the last bucket.  Used when parameters are exchanged
+        # between ranks (SINGA_B200_ROTATE=1/0 forces it on/off).
+        rot_env = os.environ.get("SINGA_B200_ROTATE", "auto")
+        multi = cluster is not None and pm.backend_name in ("fused", "nccl") and getattr(pm.backend, "world", 1) > 1
+        self.rotate = ctx().is_native and pm.backend_name in ("local", "fused", "nccl") and \
+            (rot_env == "1" or (rot_env == "auto" and multi))
+        self._primed_step = -1            # step whose forward pass has already run (rotated schedule)
+        if self.rotate and hasattr(pm.backend, "main_bumps_seq"):
+            pm.backend.main_bumps_seq = True
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
         from .parallel.bridge import BridgeTransport
         self.bridge = BridgeTransport(cluster, local_threadid) if self._has_bridges else None
@@ -215,7 +226,7 @@ class Executor:
         if training and self.display_debug_info(step):
             log.error("\n" + net.debug_info())
 
-    def backward(self, net: NeuralNet, step: int) -> None:
+    def backward(self, net: NeuralNet, step: int, join: bool = True) -> None:
         """Reverse-topological walk.  On the native path a layer's parameter gradient (wgrad GEMM + bias
         reduction) is independent of its data gradient, so it is issued on a side stream and the data
         gradient — the critical path to the layers below — continues on the main stream; the parameter
@@ -257,13 +268,17 @@ class Executor:
                 torch.cuda.nvtx.range_pop()
             if layer.is_bridgedstlayer:
                 self.bridge.send_grad(layer)
-        self.pm.end_step(step)
+        if join:
+            self.pm.end_step(step)
 
     # -- one training step --------------------------------------------------------------------------------
     def train_one_batch(self, step: int, _fetch: bool = False):
         """One training step.  On a GPU the host-side preparation of step+1 (LR/step scalars, parse kernels of the
         already staged batch, start of the next staging copy) is ENQUEUED right after this step's compute has been
         launched, so it overlaps the GPU work; stream order keeps it behind this step's kernels."""
+        if self.rotate and not self._has_bridges:
+            self._run_rotated(step)
+            return self._fetch_metrics_async(step) if _fetch else None
         if self._prefed_step != step:
             self.pm.begin_step(step)
             self._feed(self.train_net, True)
@@ -307,6 +322,52 @@ class Executor:
             self._feed(self.train_net, True)
             self._prefed_step = step + 1
 
+    # -- rotated schedule ---------------------------------------------------------------------------------
+    def _feed_next(self, net: NeuralNet, training: bool) -> None:
+        """Parse the staged batch into the parsers' ``data_next`` buffers (the current batch is still needed by the
+        backward pass of the running step), then start staging the batch after it."""
+        self._join_prefetch()
+        if not self.model.prefetch:
+            for d in net.datalayers:
+                if self._is_local(d):
+                    d.compute_feature(training)
+        for p in net.parserlayers:
+            if self._is_local(p):
+                p.compute_feature_next(training)
+        self._start_prefetch(net, training)
+
+    def _rotated_body(self, step: int) -> None:
+        """backward(step) with the pushes left running, then forward(step + 1) on the batch in ``data_next``; the
+        pushes are joined at the very end."""
+        net = self.train_net
+        self.backward(net, step, join=False)
+        for p in net.parserlayers:
+            if self._is_local(p):
+                p.swap_in_next()
+        self.pm.pre_forward(step + 1)
+        self.forward(net, step + 1, True, skip_inputs=True)
+        self.pm.end_step(step)
+
+    def _run_rotated(self, step: int, feed: bool = True) -> None:
+        net = self.train_net
+        if self._primed_step != step:
+            # first step (or after a test / resume): run this step's forward pass on its own
+            self.pm.begin_step(step)
+            self._feed(net, True)
+            self.forward(net, step, True, skip_inputs=True)
+        if feed:
+            self._feed_next(net, True)
+        self.pm.begin_step(step + 1, lr_step=step)     # dropout seeds of forward(step+1), LR of the pushes of `step`
+        if self.use_graph:
+            if self._graph is None and self.ticks > self._graph_warmup:
+                self._capture(step, rotated=True)
+            if self._graph is not None:
+                self._graph.replay()
+                self._primed_step = step + 1
+                return
+        self._rotated_body(step)
+        self._primed_step = step + 1
+
     def _run_compute(self, step: int) -> None:
         """forward + backward (+ per-layer parameter update / push) of one step on the already-parsed batch;
         replayed from a CUDA graph once captured."""
@@ -335,15 +396,18 @@ class Executor:
             self.t_forward += (t1 - t0) * 1e3
             self.t_backward += (time.monotonic() - t1) * 1e3
 
-    def _capture(self, step: int) -> None:
+    def _capture(self, step: int, rotated: bool = False) -> None:
         from .ops import native
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         n0 = native.launch_count
         try:
             with torch.cuda.graph(g):
-                self.forward(self.train_net, step, True, skip_inputs=True)
-                self.backward(self.train_net, step)
+                if rotated:
+                    self._rotated_body(step)
+                else:
+                    self.forward(self.train_net, step, True, skip_inputs=True)
+                    self.backward(self.train_net, step)
         except Exception as e:  # noqa: BLE001 - e.g. a library op that cannot be captured: run eagerly instead
             log.error("CUDA-graph capture failed (%s); continuing without graphs", str(e).splitlines()[0])
             torch.cuda.synchronize()

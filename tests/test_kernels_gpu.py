@@ -61,11 +61,12 @@ def test_colsum(dtype):
     torch.testing.assert_close(out, 2 * buf[:, :cols].float().sum(0), rtol=1e-3, atol=4e-2)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("rows,cols,ld", [(5000, 96, 96), (777, 2000, 2000), (3000, 256, 264), (100, 8, 8),
-                                          (40000, 384, 384)])
-def test_colsum_vec8(rows, cols, ld):
-    """bf16 with cols % 8 == 0 takes the 128-bit kernel (tall-skinny conv bias gradients)."""
-    buf = torch.randn(rows, ld, device=DEV).to(torch.bfloat16)
+                                          (40000, 384, 384), (1000, 2500, 2504), (513, 10, 16), (64, 50, 56)])
+def test_colsum_vec8(rows, cols, ld, dtype):
+    """Row strides of a 16-byte multiple take the 128-bit kernel (tall-skinny conv bias gradients, ragged widths)."""
+    buf = torch.randn(rows, ld, device=DEV).to(dtype)
     out = torch.empty(cols, device=DEV)
     K().colsum(buf, rows, cols, ld, out)
     ref = buf[:, :cols].float().sum(0)

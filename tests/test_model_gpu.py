@@ -184,3 +184,31 @@ def test_hogwild_threads_on_streams(tmp_path, hogwild):
     assert all(l < 2.3 for l in losses), losses
     Cluster.reset()
     device.reset_context()
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_rotated_schedule_equals_plain_schedule(dtype, monkeypatch):
+    """The rotated unit (backward(t) + update(t), then forward(t+1), replayed from one CUDA graph) must produce exactly
+    the weights of the plain forward/backward step: same kernels on the same batches in the same order."""
+    finals = {}
+    for rot in ("0", "1"):
+        monkeypatch.setenv("SINGA_B200_ROTATE", rot)
+        device.set_context("cuda", "native", dtype)
+        m = configs.mnist_mlp(batch=128, hidden=(256, 128))
+        m.display_frequency = 0
+        m.updater.base_learning_rate = 0.05
+        w = Worker(use_graph=True)
+        w.build(m)
+        ex = w.executor
+        assert ex.rotate == (rot == "1")
+        ex.setup()
+        for step in range(12):
+            ex.ticks += 1
+            ex.train_one_batch(step)
+        torch.cuda.synchronize()
+        assert ex._graph is not None
+        finals[rot] = [p.data.clone() for p in w.train_net.params]
+        w.pm.finish()
+        device.reset_context()
+    for a, b in zip(finals["0"], finals["1"]):
+        assert torch.equal(a, b)

@@ -39,3 +39,10 @@ def test_shard_bounds_cover_the_range():
             pieces = shard_bounds(n, world)
             assert len(pieces) == world and pieces[0][0] == 0 and pieces[-1][1] == n
             assert all(a <= b for a, b in pieces) and all(p[1] == q[0] for p, q in zip(pieces, pieces[1:]))
+
+
+def test_first_layer_alone_keeps_the_exposed_push_small():
+    # without the rule a huge bucket swallows fc1; with it fc1 is pushed on its own whatever the bucket size
+    assert make_buckets(MNIST, 10 ** 12, first_alone=True) == [["fc6", "fc5", "fc4", "fc3", "fc2"], ["fc1"]]
+    assert make_buckets(MNIST, 3_000_000, first_alone=True) == [["fc6", "fc5", "fc4", "fc3"], ["fc2"], ["fc1"]]
+    assert make_buckets([("only", 0, 5)], 10, first_alone=True) == [["only"]]
