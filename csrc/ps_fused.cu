@@ -50,9 +50,18 @@ struct PushParams {
   const float* grad_mc;                              // NVLS: multicast address of the gradient arenas (or null)
   void* w16_mc;                                      // NVLS: multicast address of the mirrors (or null)
   int mirror_fp32;                                   // mirrors hold fp32 (tf32 compute path) instead of bf16
+  unsigned long long* trace;                         // optional: phase time stamps (ns) of this launch (profiling tool)
   unsigned long long* bump_ready;                    // optional: this rank's own "gradients ready" flag, bumped by
   unsigned long long* bump_seq;                      //   the kernel itself (+ the consumer-side wait sequence)
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define PUSH_STAMP(i) do { if (p.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.trace[i] = globaltimer_ns(); } while (0)
+
 
 // NVLS (NVLink SHARP) accessors: one instruction reduces / broadcasts across every GPU bound to the multicast
 // object, inside the NVSwitch — the reduce-scatter costs each GPU 1/world of the bytes the peer-load version pulls.
@@ -132,6 +141,7 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
   // Flag value of this launch.  Self-counting mode (the default of the framework): the n-th launch for a
   // layer waits for ready >= n and publishes version = n, with n kept in scratch[1] — no dependence on a step
   // scalar that another stream may already have advanced.
+  PUSH_STAMP(0);
   const unsigned long long target = p.self_count
       ? p.scratch[1] + 1ull
       : static_cast<unsigned long long>((p.step_dev ? *p.step_dev : 0) + p.value_add);
@@ -143,9 +153,11 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
     __threadfence_system();
     st_release_sys(p.bump_ready, *p.bump_ready + 1ull);
   }
+  PUSH_STAMP(1);
   // 1. wait for every rank's gradients of this layer
   if (threadIdx.x < p.world && p.ready[threadIdx.x] != nullptr) wait_flag_ge(p.ready[threadIdx.x], target);
   __syncthreads();
+  PUSH_STAMP(2);
 
   const float base_lr = p.lr_dev ? __ldg(p.lr_dev) : p.lr;
   const bool need_h = p.kind != SG_UPD_SGD || p.momentum > 0.f;
@@ -228,16 +240,20 @@ __global__ void __launch_bounds__(256) ps_push_update_kernel(const PushParams p)
     }
   }
   // 5. publish: last CTA to arrive bumps the version flag on every rank
+  PUSH_STAMP(3);
   __threadfence_system();
   __syncthreads();
+  PUSH_STAMP(4);
   if (threadIdx.x == 0) {
     const unsigned long long done = atomicAdd(p.scratch, 1ull) + 1ull;
     if (done == gridDim.x) {
       p.scratch[0] = 0ull;   // arrival counter must read zero at the next launch
       p.scratch[1] = target; // every CTA has read the old sequence number by now (all have arrived)
+      if (p.trace != nullptr) p.trace[5] = globaltimer_ns();
       __threadfence_system();
       for (int r = 0; r < p.world; ++r)
         if (p.version[r] != nullptr) st_release_sys(p.version[r], target);
+      if (p.trace != nullptr) p.trace[6] = globaltimer_ns();
     }
   }
 }
@@ -297,7 +313,7 @@ extern "C" int sg_ps_push_update(const SgPsPush* a, void* stream) {
   p.delta = a->up.delta; p.rho = a->up.rho; p.grad_scale = a->up.grad_scale; p.lr_dev = a->up.lr_dev;
   p.step_dev = a->step_dev; p.value_add = a->value_add;
   p.scratch = a->scratch; p.self_count = a->self_count;
-  p.grad_mc = a->grad_mc; p.w16_mc = a->w16_mc; p.mirror_fp32 = a->mirror_fp32;
+  p.grad_mc = a->grad_mc; p.w16_mc = a->w16_mc; p.mirror_fp32 = a->mirror_fp32; p.trace = a->trace;
   p.bump_ready = a->bump_ready; p.bump_seq = a->bump_seq;
   long long grid = (a->nchunks + PUSH_UNROLL - 1) / PUSH_UNROLL;
   const long long cap = a->max_ctas > 0 ? a->max_ctas : 64;   // a small CTA budget: leave the SMs to backward

@@ -250,6 +250,10 @@ typedef struct SgPsPush {
   unsigned long long* bump_seq;
   int mirror_fp32;                                  /* mirrors (w16, w16_mc) hold fp32 values: the tf32 compute path reads
                                                        its GEMM operands in fp32 */
+  unsigned long long* trace;                        /* optional (profiling): 8 device words that receive %globaltimer
+                                                       stamps of the launch: [0] start, [1] own ready flag published,
+                                                       [2] every rank ready, [3] CTA 0 done with its chunks, [4] its stores
+                                                       fenced, [5] last CTA arrived, [6] version flags published */
 } SgPsPush;
 int sg_ps_push_update(const SgPsPush* args, void* stream);
 /* Allocation-free variant of sg_ps_push_update — no counterpart in the reference (its parameter server keeps

@@ -316,24 +316,27 @@ class ParserLayer(Layer):
             pe.record(torch.cuda.current_stream())
             self.parse_events[slot] = pe
 
-    # -- rotated schedule (Executor): batch t+1 is parsed into ``data_next`` while the graph of step t still needs
-    #    batch t; the graph copies it into ``data`` between backward(t) and forward(t+1)
+    # -- rotated schedule (Executor): the output is double buffered.  Batch t+1 is parsed into the buffer that is NOT
+    #    ``data`` while the graph of step t still reads batch t (weight gradient of the first layer); ``flip`` makes it
+    #    current between backward(t) and forward(t+1).  No copy: consumers fetch ``data`` at call time and keep the
+    #    tensor they read in forward for their backward pass.
+    def _other(self) -> torch.Tensor:
+        if getattr(self, "_bufs", None) is None:
+            self._bufs = [self.data, torch.empty_like(self.data)]
+        return self._bufs[1] if self.data is self._bufs[0] else self._bufs[0]
+
+    def flip(self) -> None:
+        self.data = self._other()
+
     def compute_feature_next(self, training: bool) -> None:
-        if getattr(self, "data_next", None) is None:
-            self.data_next = torch.empty_like(self.data)
-        cur, self.data = self.data, self.data_next
+        cur, self.data = self.data, self._other()
         try:
             self.compute_feature(training)
         finally:
             self.data = cur
 
-    def swap_in_next(self) -> None:
-        self.data.copy_(self.data_next)
-
     def reparse_next(self, training: bool) -> None:
-        if getattr(self, "data_next", None) is None:
-            self.data_next = torch.empty_like(self.data)
-        cur, self.data = self.data, self.data_next
+        cur, self.data = self.data, self._other()
         try:
             self.parse(self.staging[self.last_slot], training)
         finally:

@@ -216,11 +216,13 @@ class InnerProductLayer(NeuronLayer):
         if self.native:
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
+            # the (tiny) bias reduction goes first: issued behind the GEMM it would run while the previous bucket's
+            # push kernel occupies the SMs, and the push of THIS layer waits for both
+            if self.bias_term:
+                K.colsum(dy, self.batchsize, self.hdim, dy.stride(0), self.bias.grad, accumulate=accumulate)
             # dW[vdim][hdim] = X^T dY : A = X stored [K=batch][M=vdim], B = dY stored [K=batch][N=hdim]
             K.gemm(x, dy, self.vdim, self.hdim, self.batchsize, a_mn=True, b_mn=True,
                    out32=self.weight.grad, accumulate=accumulate)
-            if self.bias_term:   # after the GEMM: the weight gradient is what the parameter push waits for longest
-                K.colsum(dy, self.batchsize, self.hdim, dy.stride(0), self.bias.grad, accumulate=accumulate)
         else:
             _, dw, db = R.ip_bwd(x, self.weight.data, dy.float(), False)
             if getattr(self, "_accumulate_wgrad", False):
@@ -369,11 +371,11 @@ class ConvolutionLayer(NeuronLayer):
     def compute_param_gradient(self):
         if self.native:
             accumulate = getattr(self, "_accumulate_wgrad", False)
-            self.plan.wgrad(self.grad, self.weight.grad, accumulate=accumulate)
             if self.bias_term:
                 from ..ops.conv import _mat
                 F_ = self.num_filters
                 _K().colsum(_mat(self.grad, self.P, F_, F_), self.P, F_, F_, self.bias.grad, accumulate=accumulate)
+            self.plan.wgrad(self.grad, self.weight.grad, accumulate=accumulate)
         else:
             self._dx_ref, dw, db = R.conv_bwd(self._x_saved, self.weight.data, self.grad.float(), self.kernel,
                                               self.stride, self.pad, self._need_src_grad())

@@ -52,6 +52,7 @@ class PsPush(ctypes.Structure):
         ("bump_ready", ctypes.c_void_p),
         ("bump_seq", ctypes.c_void_p),
         ("mirror_fp32", ctypes.c_int),
+        ("trace", ctypes.c_void_p),
     ]
 
 
@@ -246,6 +247,7 @@ class FusedExchange:
         a.self_count = 1
         a.max_ctas = self.max_ctas
         a.mirror_fp32 = 1 if self.mirror_fp32 else 0
+        a.trace = self.trace_buf.data_ptr() if getattr(self, "trace_buf", None) is not None else None
         if self.use_nvls:
             a.grad_mc = self.heap.mc_ptr("grad")
             a.w16_mc = self.heap.mc_ptr("data16") if self.has_mirror else None

@@ -107,6 +107,8 @@ class Executor:
         self.rotate = ctx().is_native and pm.backend_name in ("local", "fused", "nccl") and \
             (rot_env == "1" or (rot_env == "auto" and multi))
         self._primed_step = -1            # step whose forward pass has already run (rotated schedule)
+        self._rot_parity = 0              # which of the parsers' two output buffers holds the current batch
+        self._rot_graphs = [None, None]
         if self.rotate and hasattr(pm.backend, "main_bumps_seq"):
             pm.backend.main_bumps_seq = True
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
@@ -324,7 +326,7 @@ class Executor:
 
     # -- rotated schedule ---------------------------------------------------------------------------------
     def _feed_next(self, net: NeuralNet, training: bool) -> None:
-        """Parse the staged batch into the parsers' ``data_next`` buffers (the current batch is still needed by the
+        """Parse the staged batch into the parsers' spare output buffers (the current batch is still needed by the
         backward pass of the running step), then start staging the batch after it."""
         self._join_prefetch()
         if not self.model.prefetch:
@@ -337,14 +339,14 @@ class Executor:
         self._start_prefetch(net, training)
 
     def _rotated_body(self, step: int) -> None:
-        """backward(step) with the pushes left running, then forward(step + 1) on the batch in ``data_next``; the
+        """backward(step) with the pushes left running, then forward(step + 1) on the batch in the parsers' spare buffers; the
         pushes are joined at the very end."""
         net = self.train_net
+        self.pm.pre_forward(step + 1)      # nothing in backward reads what this advances (off the critical path)
         self.backward(net, step, join=False)
         for p in net.parserlayers:
             if self._is_local(p):
-                p.swap_in_next()
-        self.pm.pre_forward(step + 1)
+                p.flip()                   # batch step+1 (parsed into the other buffer) becomes current: no copy
         self.forward(net, step + 1, True, skip_inputs=True)
         self.pm.end_step(step)
 
@@ -359,13 +361,26 @@ class Executor:
             self._feed_next(net, True)
         self.pm.begin_step(step + 1, lr_step=step)     # dropout seeds of forward(step+1), LR of the pushes of `step`
         if self.use_graph:
-            if self._graph is None and self.ticks > self._graph_warmup:
-                self._capture(step, rotated=True)
-            if self._graph is not None:
-                self._graph.replay()
+            # two graphs: the parsers' output buffers alternate, so consecutive steps capture different pointers
+            par = self._rot_parity
+            if self._rot_graphs[par] is None and self.ticks > self._graph_warmup:
+                self._graph = None
+                self._capture(step, rotated=True)      # runs nothing: the replay below performs this step
+                self._rot_graphs[par] = self._graph
+                if self._graph is not None:            # capturing walked the body once in Python: undo its flip
+                    for p in net.parserlayers:
+                        if self._is_local(p):
+                            p.flip()
+            if self._rot_graphs[par] is not None:
+                self._rot_graphs[par].replay()
+                for p in net.parserlayers:             # the capture flipped the Python-side pointers once; keep them
+                    if self._is_local(p):              # in step with what the replayed graph just did
+                        p.flip()
+                self._rot_parity ^= 1
                 self._primed_step = step + 1
                 return
         self._rotated_body(step)
+        self._rot_parity ^= 1
         self._primed_step = step + 1
 
     def _run_compute(self, step: int) -> None:

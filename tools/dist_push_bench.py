@@ -70,13 +70,22 @@ for b, layers in enumerate(be.buckets):
     outbound = shard * mirror_bytes * (world - 1) if not be.use_nvls else shard * mirror_bytes
     served = shard * 4 * (world - 1)          # my gradients read by the other owners (or by the switch)
     per_dir = max(inbound + shard * mirror_bytes * (world - 1) * (1 if be.use_nvls else 0), outbound + served)
-    rows.append({"bucket": [l.name for l in layers], "params": int(params), "us_per_push": round(us, 1),
+    # phase stamps of one more push (eager, after a barrier so both ranks start together)
+    be.trace_buf = torch.zeros(8, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize(); dist.barrier()
+    be.update_layer(trig, 0, None)
+    be.end_step(0)
+    torch.cuda.synchronize()
+    st = be.trace_buf.tolist()
+    be.trace_buf = None
+    phases = [round((st[i] - st[0]) / 1e3, 1) for i in range(1, 7)]
+    rows.append({"phases_us": phases, "bucket": [l.name for l in layers], "params": int(params), "us_per_push": round(us, 1),
                  "link_bytes_per_direction": int(per_dir), "GBps_per_direction": round(per_dir / us / 1e3, 1),
                  "link_floor_us_at_770GBps": round(per_dir / 770e3, 1)})
 if rank == 0:
     print(json.dumps({"world": world, "dtype": args.dtype, "nvls": be.use_nvls, "ctas": be.max_ctas,
                       "pushes": [[r["bucket"][0], r["params"], r["us_per_push"], r["GBps_per_direction"],
-                                  r["link_floor_us_at_770GBps"]] for r in rows]}))
+                                  r["link_floor_us_at_770GBps"], r["phases_us"]] for r in rows]}))
 dist.barrier()
 torch.cuda.synchronize()
 os._exit(0)
