@@ -318,8 +318,8 @@ __global__ void fill_random_kernel(float* __restrict__ dst, long long n, int kin
 
 // ---------------------------------------------------------------------------------- parsers
 // MNIST: uint8 pixel -> x / norm_a - norm_b  (src/worker/layer.cc:440-445)
-template <typename D>
-__global__ void mnist_parse_kernel(const uint8_t* __restrict__ src, D* __restrict__ dst, long long n,
+template <typename S, typename D>
+__global__ void mnist_parse_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n,
                                    float norm_a, float norm_b) {
   const float inv = 1.f / norm_a;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -333,8 +333,8 @@ __global__ void mnist_parse_kernel(const uint8_t* __restrict__ src, D* __restric
 // One thread per OUTPUT PIXEL: consecutive threads read consecutive bytes of each colour plane (coalesced) and write
 // C adjacent channel values; the index arithmetic is done once per pixel instead of once per element (the
 // element-per-thread version took 213 us for a 256 x 3 x 227 x 227 batch, ~10x its memory time).
-template <typename D>
-__global__ void rgb_parse_kernel(const uint8_t* __restrict__ src, const float* __restrict__ mean,
+template <typename S, typename D>
+__global__ void rgb_parse_kernel(const S* __restrict__ src, const float* __restrict__ mean,
                                  D* __restrict__ dst, int batch, int C, int H, int W, int crop,
                                  const int* __restrict__ off_h, const int* __restrict__ off_w,
                                  const int* __restrict__ mirror, float scale) {
@@ -350,7 +350,7 @@ __global__ void rgb_parse_kernel(const uint8_t* __restrict__ src, const float* _
     const int sy = y + (off_h ? off_h[n] : 0);
     const int sx = (mirror && mirror[n] ? (ow - 1 - x) : x) + (off_w ? off_w[n] : 0);
     const long long s0 = static_cast<long long>(sy) * W + sx;
-    const uint8_t* sp = src + static_cast<long long>(n) * C * plane + s0;
+    const S* sp = src + static_cast<long long>(n) * C * plane + s0;
     D* dp = dst + i * C;
     for (int c = 0; c < C; ++c) {
       float v = static_cast<float>(sp[c * plane]);
@@ -537,32 +537,49 @@ extern "C" int sg_fill_random(float* dst, long long n, int kind, float a, float 
   return 0;
 }
 
-extern "C" int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, float norm_b,
-                              int dst_bf16, void* stream) {
+// src_f32: the staged records are fp32 (float-valued shards / Datums, e.g. mean-subtracted images) instead of uint8
+extern "C" int sg_mnist_parse_src(const void* src, int src_f32, void* dst, long long n, float norm_a, float norm_b,
+                                  int dst_bf16, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (n <= 0) return 0;
   SG_REQUIRE(norm_a != 0.f, "sg_mnist_parse: norm_a must be non-zero");
   DTYPE_SWITCH(dst_bf16, T, {
-    mnist_parse_kernel<T><<<ew_grid(n, 256), 256, 0, s>>>((const uint8_t*)src_u8, (T*)dst, n, norm_a, norm_b);
+    if (src_f32) mnist_parse_kernel<float, T><<<ew_grid(n, 256), 256, 0, s>>>((const float*)src, (T*)dst, n, norm_a, norm_b);
+    else mnist_parse_kernel<uint8_t, T><<<ew_grid(n, 256), 256, 0, s>>>((const uint8_t*)src, (T*)dst, n, norm_a, norm_b);
   })
   SG_CHECK_LAUNCH("mnist_parse");
   return 0;
 }
 
-extern "C" int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H,
-                            int W, int crop, const int* off_h, const int* off_w, const int* mirror,
-                            float scale, int dst_bf16, void* stream) {
+extern "C" int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, float norm_b,
+                              int dst_bf16, void* stream) {
+  return sg_mnist_parse_src(src_u8, 0, dst, n, norm_a, norm_b, dst_bf16, stream);
+}
+
+extern "C" int sg_rgb_parse_src(const void* src, int src_f32, const float* mean, void* dst, int batch, int C, int H,
+                                int W, int crop, const int* off_h, const int* off_w, const int* mirror,
+                                float scale, int dst_bf16, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (batch <= 0) return 0;
   SG_REQUIRE(crop >= 0 && crop <= H && crop <= W, "sg_rgb_parse: crop larger than the image");
   const int oh = crop > 0 ? crop : H, ow = crop > 0 ? crop : W;
   const long long total = static_cast<long long>(batch) * oh * ow * C;
   DTYPE_SWITCH(dst_bf16, T, {
-    rgb_parse_kernel<T><<<ew_grid(total / C, 256), 256, 0, s>>>((const uint8_t*)src_u8, mean, (T*)dst, batch, C, H, W,
-                                                           crop, off_h, off_w, mirror, scale);
+    if (src_f32)
+      rgb_parse_kernel<float, T><<<ew_grid(total / C, 256), 256, 0, s>>>((const float*)src, mean, (T*)dst, batch, C, H, W,
+                                                                       crop, off_h, off_w, mirror, scale);
+    else
+      rgb_parse_kernel<uint8_t, T><<<ew_grid(total / C, 256), 256, 0, s>>>((const uint8_t*)src, mean, (T*)dst, batch, C, H, W,
+                                                                         crop, off_h, off_w, mirror, scale);
   })
   SG_CHECK_LAUNCH("rgb_parse");
   return 0;
+}
+
+extern "C" int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H,
+                            int W, int crop, const int* off_h, const int* off_w, const int* mirror,
+                            float scale, int dst_bf16, void* stream) {
+  return sg_rgb_parse_src(src_u8, 0, mean, dst, batch, C, H, W, crop, off_h, off_w, mirror, scale, dst_bf16, stream);
 }
 
 extern "C" int sg_copy2d(const void* src, long long lds, void* dst, long long ldd, int rows, int cols,

@@ -174,8 +174,11 @@ bool get_varint(const uint8_t*& p, const uint8_t* end, uint64_t* out) {
 
 // Caffe Datum { channels = 1, height = 2, width = 3, data = 4 (bytes), label = 5, float_data = 6, encoded = 7 }.
 // pixels may be null (shape / label query only).
+// `pixels` (uint8 row) or `pixels_f32` (fp32 row) receives the image; both may be null (shape / label query only).
+// Float-valued Datums (float_data: mean-subtracted images, src/worker/layer.cc:289-293) only fit an fp32 row: asked to
+// narrow them into bytes the decoder sets *saw_float and the batch reader fails instead of clamping.
 bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim, int* label, int* chw,
-                  bool* encoded = nullptr) {
+                  bool* encoded = nullptr, float* pixels_f32 = nullptr, bool* saw_float = nullptr) {
   const uint8_t* end = p + len;
   long long nfloat = 0;
   bool got = false;
@@ -191,18 +194,21 @@ bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim
     } else if (wire == 2) {
       if (!get_varint(p, end, &v) || static_cast<uint64_t>(end - p) < v) return false;
       if (field == 4 && v > 0) {
+        const long long c = static_cast<long long>(v) < dim ? static_cast<long long>(v) : dim;
         if (pixels != nullptr) {
-          const long long c = static_cast<long long>(v) < dim ? static_cast<long long>(v) : dim;
           memcpy(pixels, p, c);
           if (c < dim) memset(pixels + c, 0, dim - c);
+        } else if (pixels_f32 != nullptr) {
+          for (long long i = 0; i < c; ++i) pixels_f32[i] = static_cast<float>(p[i]);
+          for (long long i = c; i < dim; ++i) pixels_f32[i] = 0.f;
         }
         got = true;
       } else if (field == 6) {          // packed float_data
         for (uint64_t o = 0; o + 4 <= v; o += 4) {
           float f;
           memcpy(&f, p + o, 4);
-          if (pixels != nullptr && nfloat < dim)
-            pixels[nfloat] = static_cast<uint8_t>(f < 0.f ? 0.f : (f > 255.f ? 255.f : f));
+          if (pixels_f32 != nullptr) { if (nfloat < dim) pixels_f32[nfloat] = f; }
+          else if (saw_float != nullptr) *saw_float = true;
           ++nfloat;
         }
         got = got || v >= 4;
@@ -213,8 +219,8 @@ bool decode_datum(const uint8_t* p, uint64_t len, uint8_t* pixels, long long dim
       if (field == 6) {                 // unpacked float_data element
         float f;
         memcpy(&f, p, 4);
-        if (pixels != nullptr && nfloat < dim)
-          pixels[nfloat] = static_cast<uint8_t>(f < 0.f ? 0.f : (f > 255.f ? 255.f : f));
+        if (pixels_f32 != nullptr) { if (nfloat < dim) pixels_f32[nfloat] = f; }
+        else if (saw_float != nullptr) *saw_float = true;
         ++nfloat;
         got = true;
       }
@@ -311,17 +317,17 @@ extern "C" int sg_lmdb_first_shape(void* h, int* chw) {
 
 // Decodes the next `batch` Datum records (wrapping around at the end of the database, layer.cc:300-306) into
 // pixels_u8[batch][dim] and labels[batch].
-extern "C" int sg_lmdb_read_datum_batch(void* h, void* pixels_u8, int* labels, int batch, long long dim) {
+static int lmdb_read_batch(void* h, uint8_t* px8, float* px32, int* labels, int batch, long long dim) {
   LmdbEnv* e = static_cast<LmdbEnv*>(h);
   SG_REQUIRE(e->entries > 0, "sg_lmdb_read_datum_batch: empty database");
-  uint8_t* px = static_cast<uint8_t*>(pixels_u8);
   for (int i = 0; i < batch; ++i) {
     int rc = cursor_next(e);
     if (rc == 0) rc = cursor_next(e);   // wrapped: start over
     SG_REQUIRE(rc == 1, "sg_lmdb_read_datum_batch: corrupt page structure");
     int label = 0;
-    bool encoded = false;
-    SG_REQUIRE(decode_datum(e->val, e->vlen, px + static_cast<long long>(i) * dim, dim, &label, nullptr, &encoded),
+    bool encoded = false, saw_float = false;
+    SG_REQUIRE(decode_datum(e->val, e->vlen, px8 ? px8 + static_cast<long long>(i) * dim : nullptr, dim, &label, nullptr,
+                            &encoded, px32 ? px32 + static_cast<long long>(i) * dim : nullptr, &saw_float),
                "sg_lmdb_read_datum_batch: record %d is not a Datum with pixel data", i);
     if (encoded) {
       // compressed image bytes (Datum.encoded): not decodable here; the caller re-reads this record through an image
@@ -329,7 +335,35 @@ extern "C" int sg_lmdb_read_datum_batch(void* h, void* pixels_u8, int* labels, i
       set_error("sg_lmdb_read_datum_batch: record %d holds an encoded image", i);
       return 2;
     }
+    if (saw_float) {
+      set_error("sg_lmdb_read_datum_batch: record %d holds float_data (e.g. a mean-subtracted image); it does not fit a "
+                "uint8 batch - read it with sg_lmdb_read_datum_batch_f32", i);
+      return 3;
+    }
     labels[i] = label;
   }
   return 0;
+}
+
+// Decodes the next `batch` Datum records (wrapping around at the end of the database, layer.cc:300-306) into
+// pixels[batch][dim] and labels[batch]; the _f32 form takes byte- and float-valued records alike.
+extern "C" int sg_lmdb_read_datum_batch(void* h, void* pixels_u8, int* labels, int batch, long long dim) {
+  return lmdb_read_batch(h, static_cast<uint8_t*>(pixels_u8), nullptr, labels, batch, dim);
+}
+
+extern "C" int sg_lmdb_read_datum_batch_f32(void* h, float* pixels, int* labels, int batch, long long dim) {
+  return lmdb_read_batch(h, nullptr, pixels, labels, batch, dim);
+}
+
+// 1 when the first record carries float_data, 0 when bytes, <0 on error (lets a data layer size its batch buffers).
+extern "C" int sg_lmdb_first_is_float(void* h) {
+  LmdbEnv* e = static_cast<LmdbEnv*>(h);
+  if (!cursor_first(e)) { set_error("sg_lmdb_first_is_float: empty or corrupt database"); return -1; }
+  int label = 0;
+  bool encoded = false, saw_float = false;
+  uint8_t dummy = 0;
+  const bool ok = decode_datum(e->val, e->vlen, &dummy, 0, &label, nullptr, &encoded, nullptr, &saw_float);
+  e->positioned = false;
+  if (!ok) { set_error("sg_lmdb_first_is_float: first value is not a Datum"); return -1; }
+  return saw_float ? 1 : 0;
 }

@@ -395,6 +395,8 @@ extern "C" int sg_ipc_close_handle(void* p) {
 //    caller's stream before each launch.
 //  * All calls with the same slot share the same words: two launches that can overlap on the GPU (different
 //    streams, or the same slot used for two layers in flight) race.  Use one slot per concurrently pushed layer.
+//  * The looked-up address is cached per device ordinal for the life of the process; it does not survive
+//    cudaDeviceReset (or any teardown of the primary context): do not call this entry point again after one.
 //  * Only the explicit flag-value mode is available (self_count must be 0): the self-counted sequence number
 //    would be part of the cleared scratch.
 // Nothing here calls cudaMalloc, cudaFree or any allocating library routine.

@@ -81,8 +81,35 @@ static bool skip_field(const uint8_t*& p, const uint8_t* end, int wire) {
     default: return false;
   }
 }
-// Decodes one Record into `pixels` (dim bytes; float data is clamped to 0..255) and `label`.
-static bool decode_image_record(const std::string& rec, uint8_t* pixels, long long dim, int* label) {
+// Destination of one decoded image: a uint8 row or an fp32 row of `dim` values.  Byte-valued records widen losslessly
+// into an fp32 row; FLOAT-valued records (mean-subtracted images: negative and fractional values,
+// src/worker/layer.cc:595-598 copies them unchanged) only fit an fp32 row — asked to narrow them into bytes the
+// decoder records `saw_float` and the batch reader fails instead of clamping.
+struct PixelSink {
+  uint8_t* u8;
+  float* f32;
+  long long dim;
+  bool saw_float;
+  void put_bytes(const uint8_t* src, long long n) {
+    const long long c = n < dim ? n : dim;
+    if (u8 != nullptr) {
+      memcpy(u8, src, c);
+      if (c < dim) memset(u8 + c, 0, dim - c);
+    } else {
+      for (long long i = 0; i < c; ++i) f32[i] = static_cast<float>(src[i]);
+      for (long long i = c; i < dim; ++i) f32[i] = 0.f;
+    }
+  }
+  void put_float(long long idx, float v) {
+    if (f32 != nullptr) { if (idx < dim) f32[idx] = v; }
+    else saw_float = true;
+  }
+};
+
+// Decodes one Record into `sink` and `label`.
+static bool decode_image_record(const std::string& rec, PixelSink& sink, int* label) {
+  const long long dim = sink.dim;
+  (void)dim;
   const uint8_t* p = reinterpret_cast<const uint8_t*>(rec.data());
   const uint8_t* end = p + rec.size();
   bool got = false;
@@ -108,9 +135,7 @@ static bool decode_image_record(const std::string& rec, uint8_t* pixels, long lo
         } else if (f2 == 3 && w2 == 2) {
           uint64_t n;
           if (!get_varint(q, qend, &n) || static_cast<uint64_t>(qend - q) < n) return false;
-          const long long c = static_cast<long long>(n) < dim ? static_cast<long long>(n) : dim;
-          memcpy(pixels, q, c);
-          if (c < dim) memset(pixels + c, 0, dim - c);
+          sink.put_bytes(q, static_cast<long long>(n));
           q += n;
           got = true;
         } else if (f2 == 4 && (w2 == 5 || w2 == 2)) {
@@ -119,7 +144,7 @@ static bool decode_image_record(const std::string& rec, uint8_t* pixels, long lo
           for (uint64_t o = 0; o + 4 <= n; o += 4) {
             float v;
             memcpy(&v, q + o, 4);
-            if (nfloat < dim) pixels[nfloat++] = static_cast<uint8_t>(v < 0.f ? 0.f : (v > 255.f ? 255.f : v));
+            sink.put_float(nfloat++, v);
           }
           q += n;
           got = true;
@@ -245,10 +270,9 @@ extern "C" long long sg_shard_count(void* h) {
 
 // Fill pixels[batch][dim] (uint8) and labels[batch] from the next `batch` image records, wrapping around at
 // the end of the shard (ShardDataLayer semantics, src/worker/layer.cc:646-661).  Returns records read or <0.
-extern "C" int sg_shard_read_image_batch(void* h, void* pixels, int* labels, int batch, long long dim) {
+static int shard_read_batch(void* h, uint8_t* px8, float* px32, int* labels, int batch, long long dim) {
   Shard* s = static_cast<Shard*>(h);
   if (s == nullptr || s->mode != 'r') { set_error("sg_shard_read_image_batch: shard not opened for reading"); return -1; }
-  uint8_t* px = static_cast<uint8_t*>(pixels);
   for (int i = 0; i < batch; ++i) {
     int rc = read_tuple(s->f, &s->key, &s->val, true);
     if (rc != 1) {
@@ -257,11 +281,26 @@ extern "C" int sg_shard_read_image_batch(void* h, void* pixels, int* labels, int
       if (rc != 1) { set_error("sg_shard_read_image_batch: empty shard"); return -2; }
     }
     int label = 0;
-    if (!decode_image_record(s->val, px + static_cast<long long>(i) * dim, dim, &label)) {
+    PixelSink sink{px8 ? px8 + static_cast<long long>(i) * dim : nullptr, px32 ? px32 + static_cast<long long>(i) * dim : nullptr,
+                   dim, false};
+    if (!decode_image_record(s->val, sink, &label)) {
       set_error("sg_shard_read_image_batch: record %s is not a SingleLabelImageRecord", s->key.c_str());
       return -3;
+    }
+    if (sink.saw_float) {
+      set_error("sg_shard_read_image_batch: record %s holds float pixels (e.g. a mean-subtracted image); they do not fit a "
+                "uint8 batch - read it with sg_shard_read_image_batch_f32", s->key.c_str());
+      return -4;
     }
     labels[i] = label;
   }
   return batch;
+}
+
+extern "C" int sg_shard_read_image_batch(void* h, void* pixels, int* labels, int batch, long long dim) {
+  return shard_read_batch(h, static_cast<uint8_t*>(pixels), nullptr, labels, batch, dim);
+}
+
+extern "C" int sg_shard_read_image_batch_f32(void* h, float* pixels, int* labels, int batch, long long dim) {
+  return shard_read_batch(h, nullptr, pixels, labels, batch, dim);
 }

@@ -6,6 +6,11 @@
 // updates the whole model (or one layer's slice of it) and also refreshes the bf16 mirror that the GEMMs
 // read.  Math restates src/utils/updater.cc:54-182 (with the survey's §2.8 fixes: grad_scale is honoured
 // by SGD, Nesterov uses the configured momentum).
+// Deliberate deviation, shared by all three statements of the rules (this file, ps_fused.cu::upd and
+// ops/reference.py::update_ref): grad_scale multiplies the gradient ONCE, up front, for every updater.  The reference
+// applies it only inside the squared-history term of AdaGrad / RMSProp (updater.cc:126-131, 152-157) and squares
+// (g + wd*w)*scale for AdaDelta; with grad_scale = 1/world (how the sharded server averages worker gradients) that
+// would make the step size depend on the number of workers.
 #include <cuda_bf16.h>
 #include <stdint.h>
 

@@ -121,6 +121,13 @@ int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, flo
 int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H, int W,
                  int crop, const int* off_h, const int* off_w, const int* mirror, float scale,
                  int dst_bf16, void* stream);
+/* the same with src_f32 != 0: the staged records are fp32 (float-valued records such as mean-subtracted images,
+ * which the reference copies unchanged, layer.cc:595-598) */
+int sg_mnist_parse_src(const void* src, int src_f32, void* dst, long long n, float norm_a, float norm_b,
+                       int dst_bf16, void* stream);
+int sg_rgb_parse_src(const void* src, int src_f32, const float* mean, void* dst, int batch, int C, int H, int W,
+                     int crop, const int* off_h, const int* off_w, const int* mirror, float scale,
+                     int dst_bf16, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Softmax loss forward+backward in one pass (src/worker/layer.cc:718-764).
@@ -298,6 +305,9 @@ const void* sg_shard_val(void* shard, long long* len);
 void sg_shard_seek_to_first(void* shard);
 long long sg_shard_count(void* shard);
 int sg_shard_read_image_batch(void* shard, void* pixels_u8, int* labels, int batch, long long dim);
+/* fp32 batch: byte-valued and float-valued records alike, values unchanged.  The uint8 form fails (-4) on a
+ * float-valued record instead of narrowing it. */
+int sg_shard_read_image_batch_f32(void* shard, float* pixels, int* labels, int batch, long long dim);
 
 /* ------------------------------------------------------------------------------------------------
  * Read-only LMDB environment (host code, no liblmdb): B+tree walk over an mmap of <dir>/data.mdb in key order,
@@ -313,6 +323,10 @@ const void* sg_lmdb_key(void* env, long long* len);
 const void* sg_lmdb_val(void* env, long long* len);
 int sg_lmdb_first_shape(void* env, int* chw);
 int sg_lmdb_read_datum_batch(void* env, void* pixels_u8, int* labels, int batch, long long dim);
+/* fp32 batch (Datum.data bytes widened, Datum.float_data unchanged); the uint8 form returns 3 on float_data.
+ * sg_lmdb_first_is_float: 1 / 0 for the first record, <0 on error. */
+int sg_lmdb_read_datum_batch_f32(void* env, float* pixels, int* labels, int batch, long long dim);
+int sg_lmdb_first_is_float(void* env);
 
 #ifdef __cplusplus
 }

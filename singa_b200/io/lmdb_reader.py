@@ -44,6 +44,8 @@ def _lib():
             f.argtypes = [C.c_void_p, C.POINTER(C.c_longlong)]
         lib.sg_lmdb_first_shape.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         lib.sg_lmdb_read_datum_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong]
+        lib.sg_lmdb_read_datum_batch_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong]
+        lib.sg_lmdb_first_is_float.argtypes = [C.c_void_p]
         _declared = True
     return lib
 
@@ -98,9 +100,16 @@ class LMDBEnv:
         return [int(chw[0]), int(chw[1]), int(chw[2])]
 
     def read_datum_batch(self, pixels: np.ndarray, labels: np.ndarray) -> None:
-        assert pixels.dtype == np.uint8 and labels.dtype == np.int32 and pixels.flags.c_contiguous
-        native.check(self.lib.sg_lmdb_read_datum_batch(self.h, pixels.ctypes.data, labels.ctypes.data,
-                                                       pixels.shape[0], pixels.shape[1]), "sg_lmdb_read_datum_batch")
+        assert pixels.dtype in (np.uint8, np.float32) and pixels.flags.c_contiguous and labels.dtype == np.int32
+        fn = self.lib.sg_lmdb_read_datum_batch if pixels.dtype == np.uint8 else self.lib.sg_lmdb_read_datum_batch_f32
+        native.check(fn(self.h, pixels.ctypes.data, labels.ctypes.data, pixels.shape[0], pixels.shape[1]),
+                     "sg_lmdb_read_datum_batch")
+
+    def first_is_float(self) -> bool:
+        rc = self.lib.sg_lmdb_first_is_float(self.h)
+        if rc < 0:
+            raise IOError(self.lib.sg_last_error().decode())
+        return rc == 1
 
 
 def decode_image(buf: bytes) -> np.ndarray:
@@ -130,6 +139,8 @@ class LMDBSource(BatchSource):
             self.env.seek_to_first()
             c, h, w = self._decode_record(self.env.next()[1])[0].shape
         self.sample_shape = [c, h, w] if c > 1 else [h, w]
+        # Datum.float_data records (mean-subtracted images) are staged as float32, unchanged
+        self.is_float = (not self.encoded) and self.env.first_is_float()
         self.env.seek_to_first()
 
     @staticmethod
@@ -282,12 +293,16 @@ def write_lmdb(path: str, items: Iterable[Tuple[bytes, bytes]]) -> int:
 
 
 def datum_bytes(pixels: np.ndarray, label: int) -> bytes:
-    """Serialised Caffe Datum for a {C,H,W} (or {H,W}) uint8 image."""
+    """Serialised Caffe Datum for a {C,H,W} (or {H,W}) image: uint8 pixels go to ``data``, floating-point pixels
+    (e.g. a mean-subtracted image) to ``float_data``."""
     d = S.Datum()
     shp = list(pixels.shape)
     if len(shp) == 2:
         shp = [1] + shp
     d.channels, d.height, d.width = shp
-    d.data = np.ascontiguousarray(pixels, dtype=np.uint8).tobytes()
+    if np.issubdtype(np.asarray(pixels).dtype, np.floating):
+        d.float_data.extend(np.asarray(pixels, dtype=np.float32).reshape(-1).tolist())
+    else:
+        d.data = np.ascontiguousarray(pixels, dtype=np.uint8).tobytes()
     d.label = int(label)
     return d.SerializeToString()

@@ -33,6 +33,7 @@ def _lib():
         lib.sg_shard_count.argtypes = [C.c_void_p]
         lib.sg_shard_count.restype = C.c_longlong
         lib.sg_shard_read_image_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong]
+        lib.sg_shard_read_image_batch_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_longlong]
         _declared = True
     return lib
 
@@ -95,8 +96,11 @@ class Shard:
 
 
 def read_image_batch(shard: Shard, pixels: np.ndarray, labels: np.ndarray) -> None:
-    assert pixels.dtype == np.uint8 and pixels.flags.c_contiguous and labels.dtype == np.int32
+    """Decode the next ``batch`` image records into ``pixels`` — uint8 for byte-valued records, float32 for
+    float-valued ones (mean-subtracted images; a uint8 batch refuses them rather than clamping)."""
+    assert pixels.dtype in (np.uint8, np.float32) and pixels.flags.c_contiguous and labels.dtype == np.int32
     batch, dim = pixels.shape
-    rc = shard.lib.sg_shard_read_image_batch(shard.h, pixels.ctypes.data, labels.ctypes.data, batch, dim)
+    fn = shard.lib.sg_shard_read_image_batch if pixels.dtype == np.uint8 else shard.lib.sg_shard_read_image_batch_f32
+    rc = fn(shard.h, pixels.ctypes.data, labels.ctypes.data, batch, dim)
     if rc < 0:
         raise IOError(shard.lib.sg_last_error().decode())

@@ -106,6 +106,9 @@ class ShardSource(BatchSource):
         if rec is None:
             raise RuntimeError(f"shard {folder} is empty")
         self.sample_shape = list(rec.image.shape)
+        # float-valued records (Record.image.data: e.g. mean-subtracted images written by the loader tool) are staged
+        # as float32 and reach the parser unchanged, as in the reference (src/worker/layer.cc:595-598)
+        self.is_float = len(rec.image.data) > 0
         self.shard.seek_to_first()
 
     def _read_one(self):
@@ -172,7 +175,8 @@ class DataLayer(Layer):
         self.sample_shape = list(self.source.sample_shape)
         d = int(np.prod(self.sample_shape))
         pin = torch.cuda.is_available()
-        self.pixels = torch.zeros(self.batchsize, d, dtype=torch.uint8, pin_memory=pin)
+        px_dtype = torch.float32 if getattr(self.source, "is_float", False) else torch.uint8
+        self.pixels = torch.zeros(self.batchsize, d, dtype=px_dtype, pin_memory=pin)
         self.labels = torch.zeros(self.batchsize, dtype=torch.int32, pin_memory=pin)
         self._own_pixels, self._own_labels = self.pixels, self.labels
         self._h2d_pending = []

@@ -79,13 +79,18 @@ def fill_random(dst, kind: int, a: float, b: float, scale: float, seed: int):
           seed & (2**64 - 1))
 
 
-def mnist_parse(src_u8, dst, norm_a, norm_b):
-    _call("sg_mnist_parse", src_u8.data_ptr(), dst.data_ptr(), src_u8.numel(), float(norm_a), float(norm_b),
-          _bf(dst))
+def _src_f32(t: torch.Tensor) -> int:
+    assert t.dtype in (torch.uint8, torch.float32), t.dtype
+    return 1 if t.dtype == torch.float32 else 0
 
 
-def rgb_parse(src_u8, mean, dst, batch, C, H, W, crop, off_h, off_w, mirror, scale):
-    _call("sg_rgb_parse", src_u8.data_ptr(), native.ptr(mean), dst.data_ptr(), batch, C, H, W, crop,
+def mnist_parse(src, dst, norm_a, norm_b):
+    _call("sg_mnist_parse_src", src.data_ptr(), _src_f32(src), dst.data_ptr(), src.numel(), float(norm_a),
+          float(norm_b), _bf(dst))
+
+
+def rgb_parse(src, mean, dst, batch, C, H, W, crop, off_h, off_w, mirror, scale):
+    _call("sg_rgb_parse_src", src.data_ptr(), _src_f32(src), native.ptr(mean), dst.data_ptr(), batch, C, H, W, crop,
           native.ptr(off_h), native.ptr(off_w), native.ptr(mirror), float(scale), _bf(dst))
 
 

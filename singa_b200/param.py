@@ -95,7 +95,8 @@ class Param:
         p = self.proto
         method = INIT[p.init_method]
         v = p.value
-        vs = v if v != 0 else 1.0
+        # value == 0 skips the WHOLE multiplier, fan-in factors included (src/utils/param.cc:97-123)
+        skip = v == 0
         if method == "kPretrained":
             return
         if method == "kConstant":
@@ -104,17 +105,19 @@ class Param:
         s0 = self.shape[0]
         s1 = self.shape[1] if len(self.shape) > 1 else 0
         if method == "kUniform":
-            kind, a, b, scale = 0, p.low, p.high, vs
+            kind, a, b, scale = 0, p.low, p.high, v
         elif method == "kUniformSqrtFanIn":
-            kind, a, b, scale = 0, p.low, p.high, vs / math.sqrt(max(self.fan_in, 1) / 3.0)
+            kind, a, b, scale = 0, p.low, p.high, v / math.sqrt(max(self.fan_in, 1) / 3.0)
         elif method == "kUniformSqrtFanInOut":
-            kind, a, b, scale = 0, p.low, p.high, vs / math.sqrt(s0 + s1)
+            kind, a, b, scale = 0, p.low, p.high, v / math.sqrt(s0 + s1)
         elif method == "kGaussain":
-            kind, a, b, scale = 1, p.mean, p.std, vs
+            kind, a, b, scale = 1, p.mean, p.std, v
         elif method == "kGaussainSqrtFanIn":
-            kind, a, b, scale = 1, p.mean, p.std, vs / math.sqrt(s0)
+            kind, a, b, scale = 1, p.mean, p.std, v / math.sqrt(s0)
         else:
             raise ValueError(f"unknown init method {p.init_method}")
+        if skip:
+            scale = 1.0
         if self.data.is_cuda and ctx().is_native:
             from .ops import kernels as K
             sd = seed * 1000003 + (self.id if self.id >= 0 else 0) + 12345

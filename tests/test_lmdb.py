@@ -152,3 +152,21 @@ def test_value_sizes_around_the_overflow_threshold_and_deep_trees(tmp_path):
         kv = env.next()
         assert kv is not None and kv[0] == k and kv[1] == v, k
     assert env.next() is None
+
+
+def test_float_datums_keep_negative_and_fractional_values(tmp_path):
+    """Datum.float_data (mean-subtracted images, the reference's own LMDB conversion) is staged as float32 unchanged;
+    a uint8 batch refuses it instead of clamping."""
+    vals = [np.array([[[-3.5, 10.25], [300.0, 0.75]]], dtype=np.float32),
+            np.array([[[1e-3, -255.0], [127.5, 2.0]]], dtype=np.float32)]
+    path = str(tmp_path / "fdb")
+    write_lmdb(path, [(b"k%d" % i, datum_bytes(v, i + 5)) for i, v in enumerate(vals)])
+    src = LMDBSource(path)
+    assert src.is_float and src.sample_shape == [2, 2]
+    px = np.zeros((3, 4), dtype=np.float32)
+    lb = np.zeros(3, dtype=np.int32)
+    src.next_batch(px, lb)
+    assert lb.tolist() == [5, 6, 5]
+    assert np.array_equal(px[0], vals[0].reshape(-1)) and np.array_equal(px[1], vals[1].reshape(-1))
+    with pytest.raises(RuntimeError, match="float_data"):
+        src.next_batch(np.zeros((2, 4), dtype=np.uint8), lb[:2].copy())

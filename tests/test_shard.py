@@ -78,8 +78,37 @@ def test_native_image_batch_decoder_wraps_around(tmp_path):
             sh.insert(f"img{i}", r)
         sh.flush()
     with Shard(folder, Shard.kRead) as sh:
-        px = np.zeros((7, 784), dtype=np.uint8)
+        # byte- and float-valued records mixed: an fp32 batch takes both
+        px = np.zeros((7, 784), dtype=np.float32)
         lab = np.zeros(7, dtype=np.int32)
         read_image_batch(sh, px, lab)
         assert lab.tolist() == [3, 4, 5, 6, 7, 3, 4]
-        assert np.array_equal(px[:5], imgs) and np.array_equal(px[5:], imgs[:2])
+        assert np.array_equal(px[:5], imgs.astype(np.float32)) and np.array_equal(px[5:], imgs[:2].astype(np.float32))
+
+
+def test_float_records_keep_negative_and_fractional_values(tmp_path):
+    """Mean-subtracted images (the loader tool's ImageNet path) are float records with negative and fractional values:
+    they must reach the batch unchanged (src/worker/layer.cc:595-598 memcpy's them), never clamped into bytes."""
+    import pytest
+    folder = str(tmp_path / "flt")
+    vals = np.array([[-3.5, 10.25, 300.0, 0.75], [1e-3, -255.0, 127.5, 2.0]], dtype=np.float32)
+    with Shard(folder, Shard.kCreate) as sh:
+        for i, v in enumerate(vals):
+            r = S.Record()
+            r.image.shape.extend([2, 2])
+            r.image.label = i
+            r.image.data.extend(v.tolist())
+            sh.insert(f"f{i}", r)
+        sh.flush()
+    with Shard(folder, Shard.kRead) as sh:
+        px = np.zeros((2, 4), dtype=np.float32)
+        lab = np.zeros(2, dtype=np.int32)
+        read_image_batch(sh, px, lab)
+        assert np.array_equal(px, vals) and lab.tolist() == [0, 1]
+        sh.seek_to_first()
+        with pytest.raises(IOError, match="float pixels"):          # a uint8 batch refuses instead of clamping
+            read_image_batch(sh, np.zeros((2, 4), dtype=np.uint8), lab)
+    # the data layer stages such a shard as float32 and the parser passes the values through
+    from singa_b200.layers.data import ShardSource
+    src = ShardSource(folder)
+    assert src.is_float and src.sample_shape == [2, 2]
