@@ -51,17 +51,56 @@ def parse_args():
 
 
 class ClockSampler:
-    """Samples nvidia-smi SM clocks / throttle reasons during the timed region (profiling recipe)."""
+    """Samples SM clocks and throttle reasons of one GPU DURING the timed region: an in-process NVML poll at ~1 kHz
+    (the timed region of the small configs lasts tens of milliseconds - an `nvidia-smi -lms` child process delivers
+    one or two samples in that time, or none), with `nvidia-smi` as the fallback when NVML cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
         self.proc = None
         self.lines = []
+        self.samples = []          # (sm_mhz, reasons bitmask) from NVML
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+
+    def _physical_index(self) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[self.gpu])
+            except (ValueError, IndexError):
+                pass
+        return self.gpu
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index())
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            self._nvml = pynvml
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        self.samples.append((float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                             int(get_reasons(h))))
+                    except Exception:  # noqa: BLE001
+                        pass
+                    time.sleep(0.001)
+            self._thread = threading.Thread(target=poll, daemon=True)
+            self._thread.start()
+            return
+        except Exception:  # noqa: BLE001 - no NVML binding / library: fall back to the nvidia-smi child process
+            self._nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
@@ -76,6 +115,16 @@ class ClockSampler:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self._nvml is not None:
+            self._stop.set()
+            self._thread.join(timeout=1)
+            sm = sorted(s for s, _ in self.samples)
+            mask = 0
+            for _, r in self.samples:
+                mask |= r
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
+                    "reasons": sorted(n for b, n in self.REASONS.items() if mask & b), "samples": len(sm),
+                    "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         time.sleep(0.15)
@@ -99,7 +148,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 def reference_arm(args):

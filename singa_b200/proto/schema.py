@@ -220,6 +220,7 @@ MESSAGES = {
         ("opt", "int32", "width", 4, 0),
         ("rep", "float", "data", 5, None, True),
         ("rep", "float", "diff", 6, None, True),
+        ("opt", "int64", "offset", 7, 0),      # addition: first element of this segment within the flattened parameter
     ]),
     # ---- checkpoint container (addition) -----------------------------------------------------
     "ParamCheckpoint": ({}, [

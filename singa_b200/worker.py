@@ -146,7 +146,9 @@ class Executor:
             self._every(step, self.model.validation_frequency, self.model.validation_after_steps)
 
     def checkpoint_now(self, step) -> bool:
-        return self._group0() and step > 0 and \
+        # with sharded servers every rank owns a piece of the master copy and writes its own shard file
+        sharded = getattr(self.pm.backend, "world", 1) > 1 and hasattr(self.pm.backend, "owned_ranges")
+        return (self._group0() or sharded) and step > 0 and \
             self._every(step, self.model.checkpoint_frequency, self.model.checkpoint_after_steps)
 
     # -- data --------------------------------------------------------------------------------------------
@@ -741,6 +743,8 @@ class Worker:
     def _maybe_checkpoint(self, step: int) -> None:
         if self.executor.checkpoint_now(step + 1) and self.cluster is not None:
             from . import checkpoint
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()      # the step's pushes have published every owner's master copy
             path = checkpoint.save(self.cluster.checkpoint_folder, self.train_net, self.pm, step + 1,
                                    self.model.name)
             log.error("Checkpoint written to %s", path)

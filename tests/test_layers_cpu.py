@@ -2,6 +2,7 @@
 updaters against hand-written recurrences, LR schedules, init statistics (the kept parts of the reference's legacy
 test_param.cc:25-126), sync rules and the checkpoint round trip."""
 import math
+import os
 
 import numpy as np
 import pytest
@@ -271,3 +272,51 @@ def test_train_one_batch_async_matches_sync():
     assert pending.ready() and pending.step == 4
     for a, b in zip(ref, got):
         torch.testing.assert_close(a, b[:a.numel()])
+
+
+def test_sharded_checkpoint_written_per_owner_and_resharded_on_load(tmp_path):
+    """Every shard owner writes only the element ranges it owns (offset-tagged segments, no gather); loading reads all
+    shard files, so a job with a different number of ranks can resume.  Ownership is emulated on one process."""
+    from singa_b200 import checkpoint, device
+    from singa_b200.models import configs
+    from singa_b200.worker import Worker
+    device.set_context("cpu", "torch")
+    m = configs.mnist_mlp(batch=8, train_steps=3, hidden=(40, 24))
+    m.display_frequency = 0
+    m.updater.momentum = 0.9
+    w = Worker(); w.build(m); w.executor.setup()
+    for step in range(3):
+        w.executor.ticks += 1
+        w.executor.train_one_batch(step)
+    for p in w.train_net.params:
+        p.proto.split_threshold = 700
+    total = w.pm.arena.total
+    cut = [0, 3 * 1024, 3 * 1024 + 512 * 33, total]      # three owners, boundaries inside parameters
+
+    class Owner:
+        world = 3
+
+        def __init__(self, r):
+            self.rank = r
+
+        def owned_ranges(self):
+            return [(cut[self.rank], cut[self.rank + 1])]
+
+    paths = []
+    for r in range(3):
+        w.pm.backend = Owner(r)
+        paths.append(checkpoint.save(str(tmp_path), w.train_net, w.pm, 3, m.name))
+    w.pm.backend = None
+    assert [os.path.basename(p) for p in paths] == [f"step3.shard{r}of3.bin" for r in range(3)]
+    assert checkpoint.latest(str(tmp_path)) == paths[0]
+    sizes = [os.path.getsize(p) for p in paths]
+    assert max(sizes) < 8 * total * 0.9                  # no file holds the whole model (value + history = 8 B/param)
+    w2 = Worker(seed=7); w2.build(m)
+    assert checkpoint.load(paths[1], w2.train_net, w2.pm) == 3          # any shard file names the checkpoint
+    for a, b in zip(w.train_net.params, w2.train_net.params):
+        assert torch.equal(a.data, b.data) and torch.equal(a.history, b.history)
+    os.remove(paths[2])                                                  # an incomplete checkpoint is not "latest"
+    assert checkpoint.latest(str(tmp_path)) is None
+    with pytest.raises(FileNotFoundError):
+        checkpoint.load(paths[0], w2.train_net, w2.pm)
+    device.reset_context()

@@ -1,9 +1,14 @@
 """Multi-GPU checkpoint check (run under torch.distributed.run): with a sharded parameter server the fp32 master copy
-is spread over the ranks; `checkpoint.save` must gather it, and the saved values must round to the bf16 mirrors every
-rank computes with.  A fresh job then resumes from the file."""
+and the optimizer state are spread over the ranks; every owner writes its own shard file (no gather), and a fresh job
+— with the same or a different exchange backend — resumes from the set of files.  Reports the save / load times.
+
+    torchrun ... tools/dist_ckpt_check.py [config] [--dtype fp32|bf16] [--batch N]
+"""
+import argparse
 import os
 import shutil
 import sys
+import time
 
 import torch
 import torch.distributed as dist
@@ -11,12 +16,15 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def build(push_pull, world, rank, folder):
+def build(push_pull, world, rank, folder, config, batch):
     from singa_b200.cluster import Cluster
     from singa_b200.models import configs
     from singa_b200.proto import schema as S
     from singa_b200.worker import Worker
-    model = configs.mnist_mlp(batch=64, hidden=(256, 136))
+    if config == "mnist_mlp":
+        model = configs.mnist_mlp(batch=batch or 64, hidden=(256, 136))
+    else:
+        model = configs.CONFIGS[config](**({"batch": batch} if batch else {}))
     model.display_frequency = 0
     model.prefetch = False
     model.updater.momentum = 0.9
@@ -30,44 +38,69 @@ def build(push_pull, world, rank, folder):
     return w, model
 
 
+def weights_everyone_sees(p):
+    return (p.mirror16 if getattr(p, "mirror16", None) is not None else p.data).float().clone()
+
+
 def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("config", nargs="?", default="mnist_mlp")
+    ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--batch", type=int, default=0)
+    args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from singa_b200 import checkpoint, device
-    device.set_context(f"cuda:{local}", "native")
+    device.set_context(f"cuda:{local}", "native", args.dtype)
     folder = "/tmp/singa_b200_ckpt_check"
     if rank == 0:
         shutil.rmtree(folder, ignore_errors=True)
     dist.barrier()
     ok = True
-    for pp in ("fused", "nccl"):
-        w, model = build(pp, world, rank, folder)
-        for step in range(5):
+    for pp, pp_resume in (("fused", "fused"), ("nccl", "fused")):
+        w, model = build(pp, world, rank, folder, args.config, args.batch)
+        for step in range(3):
             w.executor.ticks += 1
             w.executor.train_one_batch(step)
         torch.cuda.synchronize()
         dist.barrier()
-        path = checkpoint.save(os.path.join(folder, pp), w.train_net, w.pm, 5, model.name)   # collective
-        mirrors = {p.id: p.mirror16.float().clone() for p in w.pm.arena.params}
-        hist_norm = sum(float(p.history.norm()) for p in w.pm.arena.params)
+        sub = os.path.join(folder, pp)
+        t0 = time.monotonic()
+        path = checkpoint.save(sub, w.train_net, w.pm, 3, model.name)        # every owner writes its shard
+        t_save = time.monotonic() - t0
+        seen = {p.id: weights_everyone_sees(p) for p in w.pm.arena.params}
+        nparams = sum(p.size for p in w.pm.arena.params)
         dist.barrier()
+        nbytes = sum(os.path.getsize(f) for f in checkpoint.step_files(path))
         w.pm.finish()
-        w2, _ = build(pp, world, rank, folder)
-        step = checkpoint.load(os.path.join(folder, pp, "step5.bin"), w2.train_net, w2.pm)
+        del w
+        torch.cuda.empty_cache()
+        w2, _ = build(pp_resume, world, rank, folder, args.config, args.batch)
+        t0 = time.monotonic()
+        step = checkpoint.load(checkpoint.latest(sub), w2.train_net, w2.pm)
+        t_load = time.monotonic() - t0
         worst = 0.0
         for p in w2.pm.arena.params:
-            worst = max(worst, float((p.data.to(torch.bfloat16).float() - mirrors[p.id]).abs().max()))
+            ref = seen[p.id]
+            got = p.data.float() if ref.dtype == p.data.dtype and getattr(p, "mirror16", None) is None else \
+                weights_everyone_sees(p)
+            worst = max(worst, float((got - ref).abs().max()))
         h2 = sum(float(p.history.norm()) for p in w2.pm.arena.params)
-        good = step == 5 and worst == 0.0 and h2 > 0 and (rank != 0 or path is not None)
-        flag = torch.tensor([1 if good else 0], device="cuda")
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        good = step == 3 and worst == 0.0 and h2 > 0 and os.path.basename(path).startswith("step3.shard")
+        t = torch.tensor([1.0 if good else 0.0, t_save, t_load], device="cuda")
+        dist.all_reduce(t[:1], op=dist.ReduceOp.MIN)
+        dist.all_reduce(t[1:], op=dist.ReduceOp.MAX)
         if rank == 0:
-            print(f"{'PASS' if int(flag) else 'FAIL'} checkpoint {pp}: world={world} resumed step {step}, "
-                  f"max |bf16(saved master) - mirror| = {worst:.3e}, history norm saved {hist_norm:.3f} / loaded {h2:.3f}")
-        ok = ok and bool(int(flag))
+            print(f"{'PASS' if int(t[0]) else 'FAIL'} checkpoint {pp} -> resume {pp_resume} [{args.config} {args.dtype}]: "
+                  f"world={world}, {nparams / 1e6:.1f} M parameters, {world} shard files, {nbytes / 2**20:.0f} MiB total; "
+                  f"save {float(t[1]):.2f} s, load {float(t[2]):.2f} s (max over ranks); "
+                  f"max |resumed weights - weights at save| = {worst:.3e}")
+        ok = ok and bool(int(t[0]))
         w2.pm.finish()
+        del w2
+        torch.cuda.empty_cache()
         dist.barrier()
     sys.stdout.flush()
     os._exit(0 if ok else 1)
