@@ -155,9 +155,136 @@ __global__ void randomsync_kernel(float* __restrict__ w, float* __restrict__ sna
   if (nsel != nullptr && local) atomicAdd(nsel, static_cast<unsigned long long>(local));
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Sharded forms: ONE launch exchanges the whole arena with all server shards.  Shard k = elements
+// [k * per, (k+1) * per) and lives behind table.server[k] (a peer-mapped arena base: the same element index is used
+// on every GPU).  `seed_dev` (optional) is mixed into the RandomSync seed on the device so a captured graph draws a
+// new subset per replay.
+// ---------------------------------------------------------------------------------------------------------
+struct ShardTable {
+  float* server[SG_PS_MAX_WORLD];
+  int nshards;
+  long long per;
+};
+
+__global__ void easgd_sharded_kernel(float* __restrict__ w, const ShardTable t, long long n, float alpha,
+                                     __nv_bfloat16* __restrict__ w16) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += stride) {
+    const int k = static_cast<int>(i / t.per);
+    float* s = t.server[k < t.nshards ? k : t.nshards - 1];
+    const float wi = w[i];
+    const float d = (wi - s[i]) * alpha;
+    atomicAdd(s + i, d);
+    const float nw = wi - d;
+    w[i] = nw;
+    if (w16) w16[i] = __float2bfloat16_rn(nw);
+  }
+}
+
+__global__ void randomsync_sharded_kernel(float* __restrict__ w, float* __restrict__ snap, const ShardTable t,
+                                          long long n, float ratio, unsigned long long seed,
+                                          const unsigned long long* __restrict__ seed_dev,
+                                          __nv_bfloat16* __restrict__ w16, unsigned long long* __restrict__ nsel) {
+  if (seed_dev != nullptr) seed ^= (*seed_dev + 1ull) * 0x9E3779B97F4A7C15ull;
+  const long long n4 = (n + 3) / 4;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  unsigned int local = 0;
+  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < n4; q += stride) {
+    float uu[4];
+    philox_uniform4(seed, static_cast<unsigned long long>(q), uu);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long i = q * 4 + j;
+      if (i < n && (ratio >= 1.f || uu[j] < ratio)) {
+        const int k = static_cast<int>(i / t.per);
+        float* s = t.server[k < t.nshards ? k : t.nshards - 1];
+        const float sn = snap[i];
+        const float delta = w[i] - sn;
+        const float old = atomicAdd(s + i, delta);
+        const float nw = w[i] + old - sn;
+        w[i] = nw;
+        snap[i] = nw;
+        if (w16) w16[i] = __float2bfloat16_rn(nw);
+        ++local;
+      }
+    }
+  }
+  if (nsel != nullptr && local) atomicAdd(nsel, static_cast<unsigned long long>(local));
+}
+
+// Server-group neighbour synchronisation (src/server/pm_server.cc:105-127,296-354, src/utils/param_shard.cc:52-58):
+// the owner of a shard pulls the same shard of every neighbour group over peer memory and moves its own copy to the
+// mean of the group copies.  The move is applied as an atomic add of (mean - mine) so that worker groups exchanging
+// with this shard at the same time are not overwritten.
+__global__ void group_average_kernel(float* __restrict__ mine, const ShardTable peers, long long lo, long long n) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv = 1.f / static_cast<float>(peers.nshards + 1);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += stride) {
+    const long long e = lo + i;
+    const float m = mine[e];
+    float sum = m;
+    for (int k = 0; k < peers.nshards; ++k) sum += __ldcg(peers.server[k] + e);
+    atomicAdd(mine + e, sum * inv - m);
+  }
+}
+
 }  // namespace sg
 
 using namespace sg;
+
+static int fill_table(ShardTable* t, const SgShardTable* a, const char* who) {
+  if (a == nullptr || a->nshards < 1 || a->nshards > SG_PS_MAX_WORLD || a->per <= 0) {
+    set_error("%s: bad shard table", who);
+    return 2;
+  }
+  for (int k = 0; k < SG_PS_MAX_WORLD; ++k) t->server[k] = k < a->nshards ? a->server[k] : nullptr;
+  for (int k = 0; k < a->nshards; ++k)
+    if (t->server[k] == nullptr) { set_error("%s: null server pointer for shard %d", who, k); return 2; }
+  t->nshards = a->nshards;
+  t->per = a->per;
+  return 0;
+}
+
+static unsigned sweep_grid(long long work) {
+  long long blocks = (work + 255) / 256;
+  const long long cap = static_cast<long long>(num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  return static_cast<unsigned>(blocks < 1 ? 1 : blocks);
+}
+
+extern "C" int sg_easgd_sync_sharded(float* w, const SgShardTable* table, long long n, float alpha, void* w16,
+                                     void* stream) {
+  if (n <= 0) return 0;
+  ShardTable t;
+  if (int rc = fill_table(&t, table, "sg_easgd_sync_sharded")) return rc;
+  easgd_sharded_kernel<<<sweep_grid(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(w, t, n, alpha, (__nv_bfloat16*)w16);
+  SG_CHECK_LAUNCH("easgd_sync_sharded");
+  return 0;
+}
+
+extern "C" int sg_randomsync_sharded(float* w, float* snap, const SgShardTable* table, long long n, float ratio,
+                                     unsigned long long seed, const unsigned long long* seed_dev, void* w16,
+                                     unsigned long long* nselected, void* stream) {
+  if (n <= 0) return 0;
+  ShardTable t;
+  if (int rc = fill_table(&t, table, "sg_randomsync_sharded")) return rc;
+  randomsync_sharded_kernel<<<sweep_grid((n + 3) / 4), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      w, snap, t, n, ratio, seed, seed_dev, (__nv_bfloat16*)w16, nselected);
+  SG_CHECK_LAUNCH("randomsync_sharded");
+  return 0;
+}
+
+extern "C" int sg_group_average(float* mine, const SgShardTable* peers, long long lo, long long n, void* stream) {
+  if (n <= 0 || peers == nullptr || peers->nshards == 0) return 0;
+  SgShardTable a = *peers;
+  if (a.per <= 0) a.per = 1;
+  ShardTable t;
+  if (int rc = fill_table(&t, &a, "sg_group_average")) return rc;
+  group_average_kernel<<<sweep_grid(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(mine, t, lo, n);
+  SG_CHECK_LAUNCH("group_average");
+  return 0;
+}
 
 extern "C" int sg_update_arena(float* w, const float* g, float* h, float* u, void* w16,
                                const int* chunk_param, const float* lr_mult, const float* wd_mult,

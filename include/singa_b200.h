@@ -221,6 +221,24 @@ int sg_easgd_sync(float* w, float* server, long long n, float alpha, void* w16, 
 int sg_randomsync(float* w, float* snap, float* server, long long n, float ratio,
                   unsigned long long seed, void* w16, unsigned long long* nselected, void* stream);
 
+/* Sharded forms: ONE launch exchanges the whole local arena (n elements) with every server shard — shard k holds
+ * elements [k*per, (k+1)*per) behind server[k], a (peer-mapped) arena base indexed with the same element index.
+ * seed_dev (optional device word) is mixed into the RandomSync seed so a captured CUDA graph draws a new subset per
+ * replay.  SG_PS_MAX_WORLD bounds the table. */
+typedef struct SgShardTable {
+  float* server[8];
+  int nshards;
+  long long per;
+} SgShardTable;
+int sg_easgd_sync_sharded(float* w, const SgShardTable* table, long long n, float alpha, void* w16, void* stream);
+int sg_randomsync_sharded(float* w, float* snap, const SgShardTable* table, long long n, float ratio,
+                          unsigned long long seed, const unsigned long long* seed_dev, void* w16,
+                          unsigned long long* nselected, void* stream);
+/* Server-group neighbour synchronisation (src/server/pm_server.cc:105-127,296-354, src/utils/param_shard.cc:52-58):
+ * mine[lo, lo+n) moves to the mean of itself and the same elements of the peers->nshards neighbour groups' copies
+ * (peer loads; applied as an atomic add of the difference, so concurrent worker exchanges are kept). */
+int sg_group_average(float* mine, const SgShardTable* peers, long long lo, long long n, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Parameter-server data plane over NVSwitch peer memory (gradient push = reduce-scatter + server Updater +
  * weight broadcast in ONE kernel; device-side version flags instead of kSync / WaitUpdate messages:

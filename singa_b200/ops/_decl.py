@@ -9,6 +9,10 @@ class ConvGeom(C.Structure):
                 ("k", i32), ("stride", i32), ("pad_lo", i32), ("chunk_bytes", i32)]
 
 
+class ShardTable(C.Structure):
+    _fields_ = [("server", vp * 8), ("nshards", i32), ("per", i64)]
+
+
 class Updater(C.Structure):
     _fields_ = [("kind", i32), ("lr", f32), ("momentum", f32), ("weight_decay", f32), ("delta", f32),
                 ("rho", f32), ("grad_scale", f32), ("lr_dev", vp)]
@@ -44,6 +48,9 @@ SIGNATURES = {
     "sg_update_arena": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, C.POINTER(Updater), vp],
     "sg_easgd_sync": [vp, vp, i64, f32, vp, vp],
     "sg_randomsync": [vp, vp, vp, i64, f32, u64, vp, vp, vp],
+    "sg_easgd_sync_sharded": [vp, C.POINTER(ShardTable), i64, f32, vp, vp],
+    "sg_randomsync_sharded": [vp, vp, C.POINTER(ShardTable), i64, f32, u64, vp, vp, vp, vp],
+    "sg_group_average": [vp, C.POINTER(ShardTable), i64, i64, vp],
     "sg_ps_push_update": [vp, vp],
     "sg_ps_push_update_noalloc": [vp, i32, vp],
     "sg_ps_flag_set": [vp, vp, i64, vp],

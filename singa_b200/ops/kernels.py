@@ -8,7 +8,7 @@ import ctypes
 import torch
 
 from . import native
-from ._decl import Updater
+from ._decl import ShardTable, Updater
 from .gemm import ACT_NONE, ACT_RELU, ACT_STANH, gemm  # noqa: F401  (re-exported)
 
 
@@ -204,3 +204,24 @@ def easgd_sync(w, server, alpha, w16=None):
 def randomsync(w, snap, server, ratio, seed, w16=None, nselected=None):
     _call("sg_randomsync", w.data_ptr(), snap.data_ptr(), server.data_ptr(), w.numel(), float(ratio),
           seed & (2**64 - 1), native.ptr(w16), native.ptr(nselected))
+
+
+def shard_table(ptrs, per: int) -> ShardTable:
+    t = ShardTable()
+    for k, p in enumerate(ptrs):
+        t.server[k] = p
+    t.nshards, t.per = len(ptrs), per
+    return t
+
+
+def easgd_sync_sharded(w, table: ShardTable, alpha, w16=None):
+    _call("sg_easgd_sync_sharded", w.data_ptr(), ctypes.byref(table), w.numel(), float(alpha), native.ptr(w16))
+
+
+def randomsync_sharded(w, snap, table: ShardTable, ratio, seed, seed_dev=None, w16=None, nselected=None):
+    _call("sg_randomsync_sharded", w.data_ptr(), snap.data_ptr(), ctypes.byref(table), w.numel(), float(ratio),
+          seed & (2**64 - 1), native.ptr(seed_dev), native.ptr(w16), native.ptr(nselected))
+
+
+def group_average(mine, table: ShardTable, lo: int, n: int):
+    _call("sg_group_average", mine.data_ptr(), ctypes.byref(table), lo, n)

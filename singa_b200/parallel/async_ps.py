@@ -39,21 +39,40 @@ class AsyncExchange:
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.arena = pm.arena
-        self.staleness = max(0, int(pm.cluster.proto.staleness)) if pm.cluster is not None else 0
-        self.shards: List[Tuple[int, int]] = [(lo * 1024, hi * 1024) for lo, hi in
-                                             shard_bounds(self.arena.nchunks, self.world)]
+        cproto = pm.cluster.proto if pm.cluster is not None else None
+        self.staleness = max(0, int(cproto.staleness)) if cproto is not None else 0
+        # Server groups (src/server/pm_server.cc:105-127, Topology.server_group): the ranks are cut into `ngroups`
+        # groups; each group keeps its own center copy, sharded over its `gsize` ranks, and the workers of a group
+        # exchange with their own group's shards only.  Shard l of group g lives on rank g * gsize + l.
+        self.ngroups = max(1, int(cproto.nserver_groups)) if cproto is not None else 1
+        assert self.world % self.ngroups == 0, "nserver_groups must divide the number of ranks"
+        self.gsize = self.world // self.ngroups
+        self.group, self.local = self.rank // self.gsize, self.rank % self.gsize
+        self.sync_interval = max(1, int(cproto.server_sync_interval)) if cproto is not None else 1
+        assert self.arena.total % self.gsize == 0
+        self.per = self.arena.total // self.gsize
+        self.shards: List[Tuple[int, int]] = [(k * self.per, (k + 1) * self.per) for k in range(self.gsize)]
         self.center_local = heap.tensor("center", torch.float32)
-        self.center_peer = [heap.tensor("center", torch.float32, r) for r in range(self.world)]
+        self.center_peer = [heap.tensor("center", torch.float32, self.group * self.gsize + k)
+                            for k in range(self.gsize)]
+        # ONE launch exchanges the whole arena with every shard of the group (pointer table in the kernel parameters)
+        self.table = K.shard_table([heap.ptr("center", self.group * self.gsize + k) for k in range(self.gsize)],
+                                   self.per)
+        # the same shard in the other server groups: what the neighbour synchronisation averages with
+        self.neighbours = K.shard_table([heap.ptr("center", g * self.gsize + self.local)
+                                         for g in range(self.ngroups) if g != self.group], self.per) \
+            if self.ngroups > 1 else None
         self.step_dev = step_state()["step"]
         self._wait = (ctypes.c_void_p * 32)()
         for r in range(self.world):
             self._wait[r] = heap.ptr("progress", r)
         self.nsync = 0
+        self.ngroup_sync = 0
         self.seed_base = 0x5EED
 
     def seed_center(self) -> None:
-        """Every owner copies its shard of the (identically initialised) weights into the center."""
-        lo, hi = self.shards[self.rank]
+        """Every owner copies its shard of the (identically initialised) weights into its group's center."""
+        lo, hi = self.shards[self.local]
         self.center_local[lo:hi].copy_(self.arena.data[lo:hi])
         torch.cuda.synchronize()
         if self.world > 1:
@@ -86,21 +105,44 @@ class AsyncExchange:
 
     def sync_all(self, step: int) -> None:
         ar = self.arena
-        for o, (lo, hi) in enumerate(self.shards):
-            if hi <= lo:
-                continue
-            w = ar.data[lo:hi]
-            w16 = ar.data16[lo:hi] if ar.data16 is not None else None
-            server = self.center_peer[o][lo:hi]
-            if self.pm.param_type == "RandomSync":
-                K.randomsync(w, ar.snapshot[lo:hi], server, self.pm.sample_ratio,
-                             self.seed_base + step * 131 + self.rank, w16)
-            else:
-                K.easgd_sync(w, server, self.pm.moving_rate, w16)
+        w16 = ar.data16 if (ar.data16 is not None and ar.data16.dtype == torch.bfloat16) else None
+        if self.pm.param_type == "RandomSync":
+            # the subset changes per step through the DEVICE step scalar, so the launch can live in a captured graph
+            K.randomsync_sharded(ar.data, ar.snapshot, self.table, self.pm.sample_ratio,
+                                 self.seed_base + self.rank, self.step_dev, w16)
+        else:
+            K.easgd_sync_sharded(ar.data, self.table, self.pm.moving_rate, w16)
         for p in ar.params:
             if p.pack16 is not None:
                 p.pack16()
+        # server-group neighbour synchronisation (ParamShard::sync_now: every sync_interval updates of the shard);
+        # decided from the step number alone so that a captured graph of "a step that synchronises" stays valid
+        if self.group_sync_due(step):
+            lo, hi = self.shards[self.local]
+            K.group_average(self.center_local, self.neighbours, lo, hi - lo)
+        self.account(step)
+
+    def group_sync_due(self, step: int) -> bool:
+        if self.neighbours is None:
+            return False
+        k = (step + 1) // self.pm.sync_frequency          # ordinal of this exchange
+        return k % self.sync_interval == 0
+
+    def account(self, step: int) -> None:
+        """Host-side counters of one synchronising step (also called for steps replayed from a CUDA graph)."""
         self.nsync += 1
+        if self.group_sync_due(step):
+            self.ngroup_sync += 1
+
+    def graph_variant(self, step: int):
+        """Steps with the same variant launch the same kernels: plain / worker exchange / + neighbour averaging."""
+        if not self.pm.sync_now(step):
+            return 0
+        return 2 if self.group_sync_due(step) else 1
+
+    def after_replay(self, step: int) -> None:
+        if self.pm.sync_now(step):
+            self.account(step)
 
     def wait_layer(self, layer, step: int) -> None:
         pass

@@ -248,6 +248,11 @@ MESSAGES = {
         ("opt", "int32", "staleness", 30, 0),           # max steps a worker group may run ahead of a shard
         ("opt", "string", "push_pull", 31, "fused"),    # "fused" (peer-memory kernels) | "nccl" (baseline)
         ("opt", "string", "checkpoint_subfolder", 32, "checkpoint"),
+        # server groups on one box (Topology.nserver_groups / ServerGroup.sync_interval of the reference's Stack B):
+        # the ranks are cut into this many groups, each holding its own sharded copy of the parameters; a shard owner
+        # averages with the same shard of the other groups every `server_sync_interval` worker exchanges
+        ("opt", "int32", "nserver_groups", 33, 1),
+        ("opt", "int32", "server_sync_interval", 34, 1),
     ]),
     # ---- topology.proto ----------------------------------------------------------------------
     "Topology": ({}, [

@@ -82,9 +82,12 @@ class Executor:
         self._copy_stream = torch.cuda.Stream() if ctx().device.type == "cuda" else None
         env = os.environ.get("SINGA_B200_CUDA_GRAPH")
         if use_graph is None:
-            use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local", "fused", "nccl")
-        if pm.backend_name in ("async", "zmq"):
-            use_graph = False        # sync steps differ from plain steps: run eagerly
+            use_graph = ctx().is_native and (env != "0") and pm.backend_name in ("local", "fused", "nccl", "async")
+        if pm.backend_name == "zmq":
+            use_graph = False        # host messages inside the step: run eagerly
+        # asynchronous groups: a step that exchanges with the servers launches more kernels than a plain one, so one
+        # graph is captured per variant (plain / worker exchange / + server-group averaging)
+        self._variant_graphs = {}
         self.use_graph = use_graph
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_warmup = 3
@@ -390,11 +393,28 @@ class Executor:
         replayed from a CUDA graph once captured."""
         cuda = ctx().device.type == "cuda"
         if self.use_graph and not self._has_bridges:
-            if self._graph is None and self.ticks > self._graph_warmup:
-                self._capture(step)
-            if self._graph is not None:
-                self._graph.replay()
-                return
+            be = self.pm.backend
+            if be is not None and hasattr(be, "graph_variant"):
+                v = be.graph_variant(step)
+                fresh = False
+                if v not in self._variant_graphs and self.ticks > self._graph_warmup:
+                    self._graph = None
+                    self._capture(step)                      # walks the step once in Python (host counters included)
+                    if self._graph is None:
+                        return self._run_compute(step)       # capture failed: use_graph is off now
+                    self._variant_graphs[v] = self._graph
+                    fresh = True
+                if v in self._variant_graphs:
+                    self._variant_graphs[v].replay()
+                    if not fresh:
+                        be.after_replay(step)
+                    return
+            else:
+                if self._graph is None and self.ticks > self._graph_warmup:
+                    self._capture(step)
+                if self._graph is not None:
+                    self._graph.replay()
+                    return
         if cuda:
             e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             e0.record()

@@ -286,3 +286,43 @@ def test_easgd_and_randomsync():
     torch.testing.assert_close(w, wr)
     torch.testing.assert_close(snap, snr)
     torch.testing.assert_close(s, sr)
+
+
+def test_sharded_exchange_and_group_average():
+    """One launch over all server shards (pointer table) equals the per-shard launches; the neighbour-group averaging
+    moves a shard to the mean of the group copies.  'Peers' are local buffers here (one GPU)."""
+    n, nsh = 8 * 1024, 4
+    per = n // nsh
+    w = torch.randn(n, device=DEV)
+    servers = [torch.randn(n, device=DEV) for _ in range(nsh)]       # full-size arenas; shard k uses [k*per, (k+1)*per)
+    wr, sr = w.clone(), [s.clone() for s in servers]
+    tbl = K().shard_table([s.data_ptr() for s in servers], per)
+    K().easgd_sync_sharded(w, tbl, 0.3)
+    for k in range(nsh):
+        R.easgd_ref(wr[k * per:(k + 1) * per], sr[k][k * per:(k + 1) * per], 0.3)
+    torch.testing.assert_close(w, wr)
+    for k in range(nsh):
+        torch.testing.assert_close(servers[k], sr[k])
+    # RandomSync: same subset as the single-shard kernel with the same (device-mixed) seed
+    w, snap = torch.randn(n, device=DEV), torch.randn(n, device=DEV)
+    servers = [torch.randn(n, device=DEV) for _ in range(nsh)]
+    w1, snap1, s1 = w.clone(), snap.clone(), [s.clone() for s in servers]
+    step = torch.tensor([41], dtype=torch.int64, device=DEV)
+    nsel = torch.zeros(1, dtype=torch.int64, device=DEV)
+    tbl = K().shard_table([s.data_ptr() for s in servers], per)
+    K().randomsync_sharded(w, snap, tbl, 0.25, 777, step, None, nsel)
+    mixed = 777 ^ ((42 * 0x9E3779B97F4A7C15) & (2**64 - 1))
+    joined = torch.cat([s1[k][k * per:(k + 1) * per] for k in range(nsh)])
+    cnt = R.randomsync_ref(w1, snap1, joined, 0.25, mixed)
+    assert int(nsel.item()) == cnt
+    torch.testing.assert_close(w, w1)
+    torch.testing.assert_close(snap, snap1)
+    torch.testing.assert_close(torch.cat([servers[k][k * per:(k + 1) * per] for k in range(nsh)]), joined)
+    # neighbour-group averaging of one shard
+    mine = torch.randn(n, device=DEV)
+    others = [torch.randn(n, device=DEV) for _ in range(3)]
+    ref = mine.clone()
+    lo, cnt = 2 * per, per
+    ref[lo:lo + cnt] = (mine[lo:lo + cnt] + sum(o[lo:lo + cnt] for o in others)) / 4
+    K().group_average(mine, K().shard_table([o.data_ptr() for o in others], per), lo, cnt)
+    torch.testing.assert_close(mine, ref, rtol=1e-5, atol=1e-6)

@@ -16,6 +16,15 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="mnist_mlp")
+    ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--groups", type=int, default=1, help="server groups (each keeps its own sharded center)")
+    ap.add_argument("--sync-interval", type=int, default=2, help="worker exchanges between neighbour-group averagings")
+    ap.add_argument("--staleness", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=60)
+    args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -25,10 +34,11 @@ def main():
     from singa_b200.models import configs
     from singa_b200.proto import schema as S
     from singa_b200.worker import Worker
-    device.set_context(f"cuda:{local}", "native")
+    device.set_context(f"cuda:{local}", "native", args.dtype)
     ok = True
     for param_type in ("Elastic", "RandomSync"):
-        model = configs.mnist_mlp(batch=128, hidden=(256, 128))
+        model = configs.mnist_mlp(batch=128, hidden=(256, 128)) if args.config == "mnist_mlp" \
+            else configs.CONFIGS[args.config](batch=32)
         model.display_frequency = 0
         model.prefetch = False
         u = model.updater
@@ -37,14 +47,15 @@ def main():
         cp = S.ClusterProto()
         cp.nworkers = cp.nservers = world
         cp.workspace = "/tmp/singa_b200_async"
-        cp.staleness = 3
+        cp.staleness = args.staleness
+        cp.nserver_groups, cp.server_sync_interval = args.groups, args.sync_interval
         Cluster.reset()
         cluster = Cluster.get(cp, "", rank)
         w = Worker(cluster, backend="async")
         w.build(model)
         w.pm.sample_ratio = 0.5
         ex, be = w.executor, w.pm.backend
-        steps, worst_lead = 60, 0
+        steps, worst_lead = args.steps, 0
         first = last = None
         for step in range(steps):
             ex.ticks += 1
@@ -65,7 +76,6 @@ def main():
                     last = val
         torch.cuda.synchronize()
         dist.barrier()
-        lo, hi = be.shards[rank]
         dev_from_center = 0.0
         for o, (a, b) in enumerate(be.shards):
             if b > a:
@@ -79,11 +89,14 @@ def main():
             lead = max(float(x[0]) for x in allt)
             devc = max(float(x[1]) for x in allt)
             f0, l0 = float(allt[0][2]), float(allt[0][3])
-            good = lead <= cp.staleness + 1 and l0 < f0 and devc < 0.5 and be.nsync > 0
+            good = lead <= cp.staleness + 1 and l0 < f0 and devc < 0.5 and be.nsync > 0 and \
+                (args.groups == 1 or be.ngroup_sync > 0) and (ex._variant_graphs or not ex.use_graph)
             ok = ok and good
-            print(f"{'PASS' if good else 'FAIL'} async {param_type}: world={world} staleness={cp.staleness} "
-                  f"max observed lead={lead:.0f} steps, loss {f0:.4f} -> {l0:.4f}, "
-                  f"max relative distance to the center {devc:.3f}, syncs={be.nsync}")
+            print(f"{'PASS' if good else 'FAIL'} async {param_type} [{args.config} {args.dtype}]: world={world} "
+                  f"server groups={args.groups} staleness={cp.staleness} max observed lead={lead:.0f} steps, "
+                  f"loss {f0:.4f} -> {l0:.4f}, max relative distance to the group's center {devc:.3f}, "
+                  f"worker exchanges={be.nsync}, neighbour-group averagings={be.ngroup_sync}, "
+                  f"graph variants captured={sorted(ex._variant_graphs)}")
         w.pm.finish()
         dist.barrier()
     flag = torch.tensor([1 if ok else 0], device="cuda")
