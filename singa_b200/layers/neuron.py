@@ -644,6 +644,12 @@ class SoftmaxLossLayer(LossLayer):
         if self.native:
             g = self.srclayers[0].grad_for(self) if training else None
             l2 = logits if logits.dim() == 2 else logits.view(self.batchsize, self.dim)
+            if labels.dtype != torch.int32:
+                # labels that travelled through Slice / Bridge layers of a partitioned net arrive as activations
+                if getattr(self, "_labels_i32", None) is None:
+                    self._labels_i32 = torch.zeros(self.batchsize, dtype=torch.int32, device=labels.device)
+                self._labels_i32.copy_(labels.reshape(-1))
+                labels = self._labels_i32
             _K().softmax_loss(l2, l2.stride(0), labels, self.batchsize, self.dim, self.topk, self.scale,
                               self.data, g, g.stride(0) if g is not None else 0, self.metric)
         else:
