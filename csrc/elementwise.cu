@@ -360,6 +360,44 @@ __global__ void rgb_parse_kernel(const S* __restrict__ src, const float* __restr
   }
 }
 
+// MNIST distortion (intent of the reference's disabled block, src/worker/layer.cc:406-438: random scaling by
+// +-gamma %, then a random rotation by up to beta degrees or a horizontal shear of beta/90, plus the elastic
+// displacement field of MnistProto.kernel / sigma / alpha): every output pixel is bilinearly sampled from the source
+// image at  A_n * (x, y, 1) + displacement_n(x, y)  and normalised (x / norm_a - norm_b).  A_n (2x3, per image) and
+// the smoothed displacement field are produced by the caller; pixels sampled outside the image read 0.
+template <typename S, typename D>
+__global__ void mnist_distort_kernel(const S* __restrict__ src, D* __restrict__ dst, int n_img, int in_size, int out_size,
+                                     const float* __restrict__ affine, const float* __restrict__ disp, float norm_a,
+                                     float norm_b) {
+  const long long total = static_cast<long long>(n_img) * out_size * out_size;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv = 1.f / norm_a;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int x = static_cast<int>(i % out_size);
+    const long long t = i / out_size;
+    const int y = static_cast<int>(t % out_size);
+    const int n = static_cast<int>(t / out_size);
+    const float* a = affine + static_cast<long long>(n) * 6;
+    float sx = a[0] * x + a[1] * y + a[2];
+    float sy = a[3] * x + a[4] * y + a[5];
+    if (disp != nullptr) {
+      const long long plane = static_cast<long long>(out_size) * out_size;
+      sx += disp[(static_cast<long long>(n) * 2) * plane + static_cast<long long>(y) * out_size + x];
+      sy += disp[(static_cast<long long>(n) * 2 + 1) * plane + static_cast<long long>(y) * out_size + x];
+    }
+    const float fx = floorf(sx), fy = floorf(sy);
+    const int x0 = static_cast<int>(fx), y0 = static_cast<int>(fy);
+    const float wx = sx - fx, wy = sy - fy;
+    const S* img = src + static_cast<long long>(n) * in_size * in_size;
+    auto px = [&](int yy, int xx) -> float {
+      return (yy >= 0 && yy < in_size && xx >= 0 && xx < in_size) ? static_cast<float>(img[yy * in_size + xx]) : 0.f;
+    };
+    const float v = (1.f - wy) * ((1.f - wx) * px(y0, x0) + wx * px(y0, x0 + 1)) +
+                    wy * ((1.f - wx) * px(y0 + 1, x0) + wx * px(y0 + 1, x0 + 1));
+    dst[i] = from_float<D>(v * inv - norm_b);
+  }
+}
+
 // 2-D copy that changes the row stride (used to pad a [rows][cols] matrix to a TMA-legal ld); T = 2- or 4-byte words.
 template <typename T>
 __global__ void copy2d_kernel(const T* __restrict__ src, long long lds, T* __restrict__ dst, long long ldd,
@@ -548,6 +586,25 @@ extern "C" int sg_mnist_parse_src(const void* src, int src_f32, void* dst, long 
     else mnist_parse_kernel<uint8_t, T><<<ew_grid(n, 256), 256, 0, s>>>((const uint8_t*)src, (T*)dst, n, norm_a, norm_b);
   })
   SG_CHECK_LAUNCH("mnist_parse");
+  return 0;
+}
+
+extern "C" int sg_mnist_distort(const void* src, int src_f32, void* dst, int n_img, int in_size, int out_size,
+                                const float* affine, const float* disp, float norm_a, float norm_b, int dst_bf16,
+                                void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (n_img <= 0) return 0;
+  SG_REQUIRE(norm_a != 0.f && affine != nullptr && in_size > 0 && out_size > 0, "sg_mnist_distort: bad arguments");
+  const long long total = static_cast<long long>(n_img) * out_size * out_size;
+  DTYPE_SWITCH(dst_bf16, T, {
+    if (src_f32)
+      mnist_distort_kernel<float, T><<<ew_grid(total, 256), 256, 0, s>>>((const float*)src, (T*)dst, n_img, in_size, out_size,
+                                                                        affine, disp, norm_a, norm_b);
+    else
+      mnist_distort_kernel<uint8_t, T><<<ew_grid(total, 256), 256, 0, s>>>((const uint8_t*)src, (T*)dst, n_img, in_size,
+                                                                          out_size, affine, disp, norm_a, norm_b);
+  })
+  SG_CHECK_LAUNCH("mnist_distort");
   return 0;
 }
 

@@ -121,6 +121,11 @@ int sg_mnist_parse(const void* src_u8, void* dst, long long n, float norm_a, flo
 int sg_rgb_parse(const void* src_u8, const float* mean, void* dst, int batch, int C, int H, int W,
                  int crop, const int* off_h, const int* off_w, const int* mirror, float scale,
                  int dst_bf16, void* stream);
+/* MNIST distortion (the reference's disabled block, layer.cc:406-438): dst[n][y][x] = bilinear(src[n]; A_n (x,y,1) +
+ * disp[n][:, y, x]) / norm_a - norm_b with A_n = affine[n][0..5] (2x3) and disp (optional) an [n][2][out][out]
+ * displacement field in source pixels. */
+int sg_mnist_distort(const void* src, int src_f32, void* dst, int n_img, int in_size, int out_size,
+                     const float* affine, const float* disp, float norm_a, float norm_b, int dst_bf16, void* stream);
 /* the same with src_f32 != 0: the staged records are fp32 (float-valued records such as mean-subtracted images,
  * which the reference copies unchanged, layer.cc:595-598) */
 int sg_mnist_parse_src(const void* src, int src_f32, void* dst, long long n, float norm_a, float norm_b,

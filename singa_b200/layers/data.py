@@ -357,9 +357,10 @@ class ParserLayer(Layer):
 
 
 class MnistImageLayer(ParserLayer):
-    """uint8 pixel -> x / norm_a - norm_b, output {N, s, s} (src/worker/layer.cc:382-473).  The elastic
-    distortion fields of MnistProto are accepted but, as in the reference (commented out, layer.cc:406-438),
-    not applied."""
+    """uint8 pixel -> x / norm_a - norm_b, output {N, s, s} (src/worker/layer.cc:382-473).  The distortion fields of
+    MnistProto (gamma: random scaling in %, beta: random rotation in degrees or shear, kernel / sigma / alpha: elastic
+    displacement field) are applied to TRAINING batches — the reference parses them and then skips the block
+    (commented out, layer.cc:406-438); the intended augmentation is implemented here (``sg_mnist_distort``)."""
     type_id = "kMnistImage"
 
     def setup(self):
@@ -369,12 +370,35 @@ class MnistImageLayer(ParserLayer):
         sh = d.sample_shape
         assert len(sh) >= 2 and sh[-1] == sh[-2], f"{self.name}: MNIST records must be square, got {sh}"
         s = mp.resize if mp.resize else sh[-1]
+        self.in_size = sh[-1]
+        self.gamma, self.beta = float(mp.gamma), float(mp.beta)
+        self.ekernel, self.esigma, self.ealpha = int(mp.kernel), float(mp.sigma), float(mp.alpha)
+        self.distort = bool(self.gamma or self.beta or (self.ekernel and self.esigma and self.ealpha))
+        if s != sh[-1] and not self.distort:
+            raise NotImplementedError(f"{self.name}: MnistProto.resize without a distortion is not supported")
+        if self.distort:
+            self._gen = torch.Generator(device=ctx().device)
+            self._gen.manual_seed(97531)
         self._alloc([d.batchsize, s, s], need_grad=False)
 
     def host_tensor(self):
         return self._data_layer().pixels
 
     def parse(self, staged, training):
+        if self.distort and training:
+            from ..ops import reference as R
+            n, out = self.shape_[0], self.shape_[1]
+            labels = self._data_layer().labels
+            A, disp = R.mnist_distortion_params(n, self.in_size, out, self.gamma, self.beta, self.ekernel, self.esigma,
+                                                self.ealpha, labels, self._gen, ctx().device)
+            self._last_distortion = (A, disp)
+            if self.native:
+                from ..ops import kernels as K
+                K.mnist_distort(staged, self.data, n, self.in_size, out, A, disp, self.norm_a, self.norm_b)
+            else:
+                src = staged.view(n, self.in_size, self.in_size)
+                self.data.copy_(R.mnist_distort(src, A, disp, out, self.norm_a, self.norm_b))
+            return
         if self.native:
             from ..ops import kernels as K
             K.mnist_parse(staged, self.data, self.norm_a, self.norm_b)

@@ -32,6 +32,7 @@ SIGNATURES = {
     "sg_asum": [vp, i64, vp, i32, vp],
     "sg_fill_random": [vp, i64, i32, f32, f32, f32, u64, vp],
     "sg_mnist_parse": [vp, vp, i64, f32, f32, i32, vp],
+    "sg_mnist_distort": [vp, i32, vp, i32, i32, i32, vp, vp, f32, f32, i32, vp],
     "sg_mnist_parse_src": [vp, i32, vp, i64, f32, f32, i32, vp],
     "sg_rgb_parse_src": [vp, i32, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, f32, i32, vp],
     "sg_rgb_parse": [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, f32, i32, vp],

@@ -89,6 +89,11 @@ def mnist_parse(src, dst, norm_a, norm_b):
           float(norm_b), _bf(dst))
 
 
+def mnist_distort(src, dst, n_img, in_size, out_size, affine, disp, norm_a, norm_b):
+    _call("sg_mnist_distort", src.data_ptr(), _src_f32(src), dst.data_ptr(), n_img, in_size, out_size,
+          affine.data_ptr(), native.ptr(disp), float(norm_a), float(norm_b), _bf(dst))
+
+
 def rgb_parse(src, mean, dst, batch, C, H, W, crop, off_h, off_w, mirror, scale):
     _call("sg_rgb_parse_src", src.data_ptr(), _src_f32(src), native.ptr(mean), dst.data_ptr(), batch, C, H, W, crop,
           native.ptr(off_h), native.ptr(off_w), native.ptr(mirror), float(scale), _bf(dst))

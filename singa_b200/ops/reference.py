@@ -161,6 +161,74 @@ def lrn_bwd(x, norm, dy, lsize, alpha, beta):
     return dy * norm.pow(-beta) - (2.0 * beta * alpha / lsize) * x * _chwindow_sum(t, lsize)
 
 
+# ------------------------------------------------------------------------------------------- MNIST distortion
+def mnist_distortion_params(n, in_size, out_size, gamma, beta, kernel, sigma, alpha, labels, gen, device):
+    """Per-image inverse affine maps [n, 6] (output pixel -> source pixel) and the elastic displacement field
+    [n, 2, out, out] (or None), following the reference's disabled block (src/worker/layer.cc:406-438): resize by
+    (1 + r * gamma / 100) per axis, then — with equal probability — a rotation by r * beta degrees about the centre of
+    the resized image or a horizontal shear of r * beta / 90 (halved for the digits 1 and 7); the elastic field is
+    alpha x a Gaussian blur (kernel, sigma) of uniform noise in [-1, 1]."""
+    def rnd(*shape):
+        return torch.rand(*shape, generator=gen, device=device) * 2 - 1
+    sx = 1 + (rnd(n) * gamma / 100.0 if gamma else torch.zeros(n, device=device))
+    sy = 1 + (rnd(n) * gamma / 100.0 if gamma else torch.zeros(n, device=device))
+    M = torch.eye(3, device=device).repeat(n, 1, 1)
+    if beta:
+        r = rnd(n)
+        rot = torch.rand(n, generator=gen, device=device) < 0.5
+        th = torch.deg2rad(r * beta)
+        c, s_ = torch.cos(th), torch.sin(th)
+        cx, cy = in_size * sx / 2, in_size * sy / 2
+        R = torch.eye(3, device=device).repeat(n, 1, 1)
+        R[:, 0, 0], R[:, 0, 1], R[:, 0, 2] = c, s_, (1 - c) * cx - s_ * cy
+        R[:, 1, 0], R[:, 1, 1], R[:, 1, 2] = -s_, c, s_ * cx + (1 - c) * cy
+        sh = r * beta / 90.0
+        if labels is not None:
+            lab = labels.to(device)
+            sh = torch.where((lab == 1) | (lab == 7), sh / 2, sh)
+        Sh = torch.eye(3, device=device).repeat(n, 1, 1)
+        Sh[:, 0, 1] = sh
+        M = torch.where(rot[:, None, None], R, Sh)
+    S_ = torch.eye(3, device=device).repeat(n, 1, 1)
+    S_[:, 0, 0], S_[:, 1, 1] = sx, sy
+    A = torch.linalg.inv(M @ S_)[:, :2, :].reshape(n, 6).contiguous().float()
+    disp = None
+    if kernel and sigma and alpha:
+        k = int(kernel) | 1
+        ax = torch.arange(k, device=device, dtype=torch.float32) - k // 2
+        g1 = torch.exp(-ax * ax / (2 * sigma * sigma))
+        g1 = g1 / g1.sum()
+        noise = rnd(n * 2, 1, out_size, out_size)
+        blur = F.conv2d(F.conv2d(noise, g1.view(1, 1, 1, k), padding=(0, k // 2)), g1.view(1, 1, k, 1),
+                        padding=(k // 2, 0))
+        disp = (blur * alpha).view(n, 2, out_size, out_size).contiguous()
+    return A, disp
+
+
+def mnist_distort(src, A, disp, out_size, norm_a, norm_b):
+    """Bilinear sampling of src [n, S, S] at A (x, y, 1) + disp, zero outside, then x / norm_a - norm_b."""
+    n, S_, _ = src.shape
+    dev = src.device
+    ys, xs = torch.meshgrid(torch.arange(out_size, device=dev, dtype=torch.float32),
+                            torch.arange(out_size, device=dev, dtype=torch.float32), indexing="ij")
+    a = A.view(n, 6, 1, 1)
+    sx = a[:, 0] * xs + a[:, 1] * ys + a[:, 2]
+    sy = a[:, 3] * xs + a[:, 4] * ys + a[:, 5]
+    if disp is not None:
+        sx, sy = sx + disp[:, 0], sy + disp[:, 1]
+    x0, y0 = torch.floor(sx), torch.floor(sy)
+    wx, wy = sx - x0, sy - y0
+    img = src.float()
+
+    def px(yy, xx):
+        ok = (yy >= 0) & (yy < S_) & (xx >= 0) & (xx < S_)
+        idx = (yy.clamp(0, S_ - 1) * S_ + xx.clamp(0, S_ - 1)).long().view(n, -1)
+        return (img.view(n, -1).gather(1, idx).view(n, out_size, out_size)) * ok
+
+    v = (1 - wy) * ((1 - wx) * px(y0, x0) + wx * px(y0, x0 + 1)) + wy * ((1 - wx) * px(y0 + 1, x0) + wx * px(y0 + 1, x0 + 1))
+    return v / norm_a - norm_b
+
+
 # ------------------------------------------------------------------------------------------- conv / inner product
 def conv_fwd(x, weight, bias, k, s, pad):
     """weight {F, C*k*k} with column (c*k + ky)*k + kx  (SURVEY A.1)."""

@@ -115,8 +115,19 @@ class Executor:
         if self.rotate and hasattr(pm.backend, "main_bumps_seq"):
             pm.backend.main_bumps_seq = True
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
-        from .parallel.bridge import BridgeTransport
-        self.bridge = BridgeTransport(cluster, local_threadid) if self._has_bridges else None
+        from .parallel.bridge import BridgeTransport, PeerBridgeTransport
+        self.bridge = None
+        if self._has_bridges:
+            import torch.distributed as dist
+            one_group = cluster is not None and cluster.nprocs_per_group > 1 and \
+                cluster.nworkers == cluster.nprocs_per_group
+            if ctx().is_native and dist.is_available() and dist.is_initialized() and one_group:
+                # a group spread over several GPU ranks: bridges are peer-memory copies + device flags (capturable)
+                base = cluster.global_procsid - cluster.group_procsid
+                self.bridge = PeerBridgeTransport(train_net, dist.get_rank(), dist.get_world_size(), ctx().device,
+                                                  rank_of=lambda l: base + cluster.group_procsid_of(l.locationid))
+            else:
+                self.bridge = BridgeTransport(cluster, local_threadid)
 
     # -- locality ------------------------------------------------------------------------------------
     def _is_local(self, layer) -> bool:
@@ -392,7 +403,7 @@ class Executor:
         """forward + backward (+ per-layer parameter update / push) of one step on the already-parsed batch;
         replayed from a CUDA graph once captured."""
         cuda = ctx().device.type == "cuda"
-        if self.use_graph and not self._has_bridges:
+        if self.use_graph and (not self._has_bridges or getattr(self.bridge, "capturable", False)):
             be = self.pm.backend
             if be is not None and hasattr(be, "graph_variant"):
                 v = be.graph_variant(step)
@@ -672,6 +683,12 @@ class Worker:
 
     def build(self, model) -> None:
         self.model = model
+        if model.alg == S.enum_value("ModelProto.GradCalcAlg", "kContrastiveDivergence"):
+            # declared in the reference (src/proto/model.proto:40-44, include/worker/base_layer.h:34,96-108) with no
+            # layer or worker code behind it; training such a model with back-propagation would be silently wrong
+            raise NotImplementedError(
+                "ModelProto.alg = kContrastiveDivergence: neither the reference nor this framework has RBM layers or a "
+                "CD training loop; use kBackPropagation")
         registry_param(model.updater.param_type)
         self.train_net = self.setup_neuralnet(model, S.kTrain)
         assert self.train_net is not None, "the model has no training data layer"

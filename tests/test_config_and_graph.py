@@ -173,3 +173,15 @@ def test_share_weights_and_phase_nets():
         assert a.data.data_ptr() == b.data.data_ptr()
     vals = w.executor.test(w.test_net, 2, disperf=False)
     assert len(vals[0]) == 2
+
+
+def test_contrastive_divergence_is_rejected_loudly():
+    """ModelProto.alg = kContrastiveDivergence is declared by the reference without any implementation; training such a
+    model by back-propagation would be silently wrong, so building it fails."""
+    import pytest
+    from singa_b200.models import configs
+    from singa_b200.worker import Worker
+    m = configs.mnist_mlp(batch=8, hidden=(16,))
+    m.alg = S.enum_value("ModelProto.GradCalcAlg", "kContrastiveDivergence")
+    with pytest.raises(NotImplementedError, match="kContrastiveDivergence"):
+        Worker().build(m)

@@ -326,3 +326,18 @@ def test_sharded_exchange_and_group_average():
     ref[lo:lo + cnt] = (mine[lo:lo + cnt] + sum(o[lo:lo + cnt] for o in others)) / 4
     K().group_average(mine, K().shard_table([o.data_ptr() for o in others], per), lo, cnt)
     torch.testing.assert_close(mine, ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_mnist_distort_kernel_matches_reference(dtype):
+    n, S_, out = 16, 28, 24
+    src = torch.randint(0, 256, (n, S_, S_), device=DEV, dtype=torch.uint8)
+    gen = torch.Generator(device=DEV)
+    gen.manual_seed(5)
+    labels = torch.randint(0, 10, (n,), device=DEV, dtype=torch.int32)
+    A, disp = R.mnist_distortion_params(n, S_, out, 15.0, 20.0, 7, 2.5, 4.0, labels, gen, torch.device(DEV))
+    dst = torch.empty(n, out, out, device=DEV, dtype=dtype)
+    K().mnist_distort(src, dst, n, S_, out, A, disp, 127.5, 1.0)
+    ref = R.mnist_distort(src, A, disp, out, 127.5, 1.0)
+    tol = dict(rtol=1e-2, atol=1e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(dst.float(), ref, **tol)

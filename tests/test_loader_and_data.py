@@ -66,3 +66,38 @@ def test_training_from_a_real_shard_on_cpu(tmp_path):
         first = sh.next()
     assert first[0] == b"00000000"
     device.reset_context()
+
+
+def test_mnist_distortion_is_applied_in_training_only():
+    """MnistProto gamma / beta / elastic fields change training batches (the reference parses and ignores them) and
+    leave test batches alone; identity parameters reproduce the plain normalisation."""
+    import torch
+    from singa_b200 import device
+    from singa_b200.neuralnet import NeuralNet
+    from singa_b200.ops import reference as R
+    from singa_b200.proto import schema as S
+    device.set_context("cpu", "torch")
+    p = S.NetProto()
+    l = p.layer.add(); l.name, l.type = "data", "kShardData"
+    l.data_param.batchsize = 6; l.data_param.source = "synthetic"; l.data_param.synthetic_shape.extend([12, 12])
+    l = p.layer.add(); l.name, l.type = "mnist", "kMnistImage"; l.srclayers.append("data")
+    l.mnist_param.norm_a, l.mnist_param.norm_b = 127.5, 1.0
+    l.mnist_param.gamma, l.mnist_param.beta = 15.0, 15.0
+    l.mnist_param.kernel, l.mnist_param.sigma, l.mnist_param.alpha = 5, 2.0, 3.0
+    net = NeuralNet(p)
+    d, m = net.name2layer("data"), net.name2layer("mnist")
+    d.compute_feature(True)
+    plain = d.pixels.float().view(6, 12, 12) / 127.5 - 1.0
+    m.compute_feature(False)
+    assert torch.allclose(m.data, plain)                     # test phase: no distortion
+    m.stage_ready = -1
+    m.compute_feature(True)
+    assert not torch.allclose(m.data, plain)                 # training phase: distorted
+    assert float(m.data.min()) >= -1.0 - 1e-5 and float(m.data.max()) <= 1.0 + 1e-5
+    A, disp = m._last_distortion
+    assert A.shape == (6, 6) and disp.shape == (6, 2, 12, 12) and float(disp.abs().max()) < 3.0
+    # identity map reproduces the normalisation
+    eye = torch.tensor([[1., 0., 0., 0., 1., 0.]]).repeat(6, 1)
+    out = R.mnist_distort(d.pixels.view(6, 12, 12), eye, None, 12, 127.5, 1.0)
+    assert torch.allclose(out, plain, atol=1e-6)
+    device.reset_context()
