@@ -50,6 +50,11 @@ for ln, lr in zip(nat.train_net.layers, ref.train_net.layers):
         continue
     rel = float((a - b).norm() / (b.norm() + 1e-20))
     print(f"{ln.name:14s} {ln.type_id:16s} out rel diff {rel:.3e}   |ref| {float(b.norm()):.3e}")
+for ln, lr in zip(reversed(nat.train_net.layers), reversed(ref.train_net.layers)):
+    if ln.grad is None or lr.grad is None or ln.grad.shape != lr.grad.shape:
+        continue
+    a, b = ln.grad.float(), lr.grad.float()
+    print(f"{ln.name:14s} {ln.type_id:16s} grad rel diff {float((a - b).norm() / (b.norm() + 1e-20)):.3e}   |ref| {float(b.norm()):.3e}")
 for a, b in zip(nat.train_net.params, ref.train_net.params):
     ga, gb = a.grad.float().flatten(), b.grad.float().flatten()
     print(f"grad {a.name:10s} {str(tuple(a.shape)):16s} rel diff {float((ga - gb).norm() / (gb.norm() + 1e-20)):.3e}")
