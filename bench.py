@@ -36,7 +36,11 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch", "torch-layers"],
+                    help="ours = this framework's native path; reference = the unmodified reference (unavailable offline); "
+                         "torch = library baseline: torch.nn + autograd + cuBLAS/cuDNN + bucketed NCCL all-reduce under one "
+                         "CUDA graph (baseline/torch_baseline.py); torch-layers = this framework's layer classes on their "
+                         "plain-PyTorch backend")
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16", "fp32-strict"],
                     help="compute precision. fp32 (default; the reference computes in fp32): fp32 storage, tf32 tensor-core "
                          "products, fp32 accumulation - ours = tcgen05 kind::tf32, torch = cuBLAS/cuDNN with TF32 allowed. "
@@ -45,7 +49,13 @@ def parse_args():
     ap.add_argument("--config", default="mnist_mlp")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the config's own)")
     ap.add_argument("--push-pull", default=os.environ.get("SINGA_B200_PUSH_PULL", "fused"),
-                    choices=["fused", "nccl"])
+                    choices=["fused", "nccl", "async"],
+                    help="parameter exchange between the ranks: fused = one kernel per bucket over peer memory (product), "
+                         "nccl = bucketed NCCL reduce-scatter / all-gather (library baseline), async = asynchronous worker "
+                         "groups (local updates + EASGD exchange with peer-memory server shards, bounded staleness)")
+    ap.add_argument("--staleness", type=int, default=2, help="--push-pull async: steps a group may run ahead")
+    ap.add_argument("--sync-frequency", type=int, default=0, help="--push-pull async: steps between exchanges (0 = config's)")
+    ap.add_argument("--server-groups", type=int, default=1, help="--push-pull async: server groups (neighbour averaging)")
     ap.add_argument("--no-graph", action="store_true")
     return ap.parse_args()
 
@@ -164,6 +174,44 @@ def reference_arm(args):
     return 0
 
 
+def torch_arm(args, rank, local_rank, world):
+    """Library baseline (see baseline/torch_baseline.py): same metric, config, timing rules and JSON line."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import torch_baseline as TB
+    r = TB.run(args, rank, local_rank, world, ClockSampler)
+    global_batch = r["per_gpu_batch"] * world
+    if rank == 0:
+        out = {
+            "metric": "images/sec (device-timed, max over ranks)",
+            "value": round(global_batch * args.steps / (r["ms_total"] / 1e3), 1), "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 5), "ms_per_step": round(r["ms_total"] / args.steps, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "fp32 (tf32 tensor-core products, fp32 accumulate)", "bf16": "bf16 (autocast)",
+                      "fp32-strict": "fp32 (no tensor cores)"}[args.dtype],
+            "data": "synthetic", "impl": "torch",
+            "config": {"model": args.config, "global_batch": global_batch, "per_gpu_batch": r["per_gpu_batch"],
+                       "seq_len": None,
+                       "parallelism": f"dp{world}: torch.nn + autograd, {r['buckets']} gradient buckets all-reduced by NCCL on "
+                                      "a side stream during backward, foreach SGD",
+                       "cuda_graph": r["graph"], "l2": "inputs + activations + parameters exceed L2 or are re-read per step; "
+                                                       "no explicit flush (same as the product arm for this config)"},
+            "clocks": r["clocks"],
+            "e2e": {"value": round(global_batch * args.steps / (r["e2e_ms"] / 1e3), 1), "unit": "images/s",
+                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "ms_per_step": round(r["e2e_ms"] / args.steps, 4), "final_loss": round(r["last_loss"], 4)},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(out))
+    sys.stdout.flush()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
+    return 0
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -184,6 +232,9 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    if args.impl == "torch":
+        return torch_arm(args, rank, local_rank, world)
+
     from singa_b200 import device
     from singa_b200.cluster import Cluster
     from singa_b200.models import configs
@@ -191,11 +242,11 @@ def main():
     from singa_b200.proto import schema as S
     from singa_b200.worker import Worker
 
-    backend_kind = "torch" if args.impl == "torch" else "native"
+    backend_kind = "torch" if args.impl == "torch-layers" else "native"
     if args.impl == "ours" and args.dtype == "fp32-strict":
         raise SystemExit("--dtype fp32-strict is a library-arm setting (tensor cores off); ours runs fp32 (tf32) or bf16")
     device.set_context(f"cuda:{local_rank}", backend_kind, "bf16" if args.dtype == "bf16" else "fp32")
-    if args.impl == "torch":
+    if args.impl == "torch-layers":
         from singa_b200.ops import reference as R
         tf32 = args.dtype == "fp32"
         torch.backends.cuda.matmul.allow_tf32 = tf32
@@ -218,8 +269,16 @@ def main():
         cp = S.ClusterProto()
         cp.nworkers, cp.nservers = world, world        # one server shard co-located with every worker group
         cp.workspace = os.environ.get("SINGA_B200_WORKSPACE", "/tmp/singa_b200_bench")
-        cp.synchronous = True
-        cp.push_pull = args.push_pull
+        cp.synchronous = args.push_pull != "async"
+        cp.push_pull = args.push_pull if args.push_pull != "async" else "fused"
+        if args.push_pull == "async":
+            cp.staleness = args.staleness
+            cp.nserver_groups = args.server_groups
+            model.updater.param_type = "Elastic"
+            model.updater.warmup_steps = 0
+            model.updater.sync_frequency = args.sync_frequency or max(1, model.updater.sync_frequency)
+            if model.updater.moving_rate <= 0:
+                model.updater.moving_rate = 0.5
         Cluster.reset()
         cluster = Cluster.get(cp, "", rank)
         exchange = args.push_pull
@@ -364,8 +423,11 @@ def main():
                 "global_batch": global_batch,
                 "per_gpu_batch": per_gpu_batch,
                 "seq_len": None,
-                "parallelism": f"dp{world} (1 worker group + 1 server shard per GPU, sync push/pull: "
-                               f"{exchange or 'local'})",
+                "parallelism": (f"dp{world} (1 worker group + 1 server shard per GPU, sync push/pull: "
+                                f"{exchange or 'local'})") if exchange != "async" else
+                               (f"dp{world} asynchronous worker groups, EASGD exchange every "
+                                f"{model.updater.sync_frequency} steps with {world} peer-memory server shards in "
+                                f"{args.server_groups} group(s), staleness {args.staleness}"),
                 "precision": {"fp32": "fp32 activations/gradients/weights, tf32 tensor-core products, fp32 accumulate",
                               "bf16": "bf16 operands, fp32 accumulate, fp32 master weights + optimizer state",
                               "fp32-strict": "fp32 FMA, TF32 off"}[args.dtype],
