@@ -269,6 +269,18 @@ class FusedExchange:
                 p.pack_from_mirror = True
                 p.pack16()
 
+    def use_rotated_schedule(self) -> None:
+        """Called by the executor when it runs backward(t) + push(t) || forward(t+1) in one graph.  The consumer-side
+        sequence numbers are then advanced on the compute stream, and the weights of a layer are awaited by a
+        one-warp kernel in front of its forward GEMM instead of inside it: a persistent GEMM that spins for its weights
+        holds a whole SM (200 KB of shared memory, 54 K registers in the tf32 build), and when its grid covers every
+        SM the push kernel it waits for may find no SM to run on — measured as a deadlock (trap after the bounded
+        spin) on the 16k-wide MLP.  A one-warp waiter leaves the SMs to the push."""
+        self.main_bumps_seq = True
+        for l in self.layers:
+            if getattr(l, "pull_wait", None) is not None:
+                l.pull_wait = None
+
     def pre_forward(self, step: int) -> None:
         assert self.main_bumps_seq, "pre_forward is part of the rotated schedule (the executor sets main_bumps_seq)"
         self.wait_seq.add_(1)

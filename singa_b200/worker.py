@@ -112,8 +112,8 @@ class Executor:
         self._primed_step = -1            # step whose forward pass has already run (rotated schedule)
         self._rot_parity = 0              # which of the parsers' two output buffers holds the current batch
         self._rot_graphs = [None, None]
-        if self.rotate and hasattr(pm.backend, "main_bumps_seq"):
-            pm.backend.main_bumps_seq = True
+        if self.rotate and hasattr(pm.backend, "use_rotated_schedule"):
+            pm.backend.use_rotated_schedule()
         self._has_bridges = any(l.is_bridgesrclayer or l.is_bridgedstlayer for l in train_net.layers)
         from .parallel.bridge import BridgeTransport, PeerBridgeTransport
         self.bridge = None

@@ -26,13 +26,14 @@ PY
 for c in $CONFIGS; do
   steps=100; warm=10
   case $c in alexnet|wide_mlp) steps=20; warm=5;; esac
-  for d in fp32 bf16; do
+  for d in ${DTYPES:-fp32 bf16}; do
     if [ "$N" = "1" ]; then
       run ${c}_n1_ours_$d --config $c --dtype $d --steps $steps --warmup $warm
       run ${c}_n1_torch_$d --config $c --dtype $d --impl torch --steps $steps --warmup $warm
     else
       run ${c}_n${N}_fused_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull fused
       run ${c}_n${N}_nccl_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull nccl
+      run ${c}_n${N}_torch_$d --config $c --dtype $d --impl torch --steps $steps --warmup $warm
       if [ "$c" = "cifar10" ]; then
         for st in 0 2 8; do
           run ${c}_n${N}_async_s${st}_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull async --staleness $st --sync-frequency 4
@@ -40,7 +41,4 @@ for c in $CONFIGS; do
       fi
     fi
   done
-  if [ "$N" != "1" ] && [ "$c" = "mnist_mlp" ]; then
-    run ${c}_n${N}_torch_nccl_fp32 --config $c --dtype fp32 --impl torch --steps $steps --warmup $warm --push-pull nccl
-  fi
 done
