@@ -18,6 +18,7 @@
 // smem tiles use the 128-byte swizzle; K-major tiles are [rows][64 k] with 128-byte rows, MN-major tiles
 // are stacks of [64 k][64 mn] boxes (8 KB each) — the canonical tcgen05 layouts for SWIZZLE_128B.
 #include <cuda.h>
+#include <stdlib.h>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -91,6 +92,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   if (threadIdx.x == 0) SG_TRACE(1);
+  // everything above touched only this CTA's shared memory / TMEM: with a programmatic launch it overlapped the tail
+  // of the previous kernel.  From here on global memory written by that kernel is read.
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -453,6 +458,12 @@ static int make_tmap(CUtensorMap* out, int eb, const void* ptr, long long inner,
   return 0;
 }
 
+// Programmatic dependent launch of the single-CTA GEMM (opt-in: SINGA_B200_PDL=1): back-to-back GEMMs of a layer chain
+// overlap their launch + set-up with the previous kernel's last tiles.  Measured on the MNIST MLP step (B200, CUDA
+// graph): 0.444 ms with it against 0.436 ms without in fp32, 0.341 against 0.342 in bf16 — the early-started CTAs sit
+// on the SMs that the concurrent weight-gradient GEMMs of the side streams want — so it is off by default.
+static int g_pdl = [] { const char* e = getenv("SINGA_B200_PDL"); return (e != nullptr && e[0] == '1') ? 1 : 0; }();
+
 template <int EB, int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
                        cudaStream_t stream) {
@@ -472,6 +483,16 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   const int n_tiles = (p.N + BN - 1) / BN;
   const int tiles = m_tiles * n_tiles * p.split_k;
   const int grid = tiles < num_sms() ? tiles : num_sms();
+  if (g_pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (check_cuda(cudaLaunchKernelEx(&cfg, kern, ta, tb, p), "gemm_tcgen05 (programmatic launch)")) return 1;
+    return 0;
+  }
   kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
   SG_CHECK_LAUNCH("gemm_tcgen05");
   return 0;
