@@ -411,6 +411,62 @@ __global__ void copy2d_kernel(const T* __restrict__ src, long long lds, T* __res
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Space-to-depth for strided convolutions over thin inputs (RGB, stride 4: AlexNet conv1).  A k x k, stride-s
+// convolution over C channels equals a ceil(k/s) x ceil(k/s), stride-1 convolution over s*s*C channels of
+//   xs[n][Y][X][(dy*s + dx)*C + c] = x[n][Y*s + dy - pad][X*s + dx - pad][c]      (0 outside the image),
+// whose pixels are wide enough for the implicit-GEMM tile loads (ops/conv.py, S2dConvPlan).  T is a bit
+// container (bf16 as 16-bit, fp32 as 32-bit words); one block per (image, row of xs).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+space_to_depth_kernel(const T* __restrict__ x, T* __restrict__ xs, int H, int W, int C, int Hs, int Ws, int Cs,
+                      int s, int pad) {
+  const int n = blockIdx.x / Hs, Y = blockIdx.x - n * Hs;
+  const int sc = s * C, real = s * sc;
+  const T* xn = x + static_cast<long long>(n) * H * W * C;
+  T* row = xs + static_cast<long long>(blockIdx.x) * Ws * Cs;
+  for (int j = threadIdx.x; j < Ws * Cs; j += blockDim.x) {
+    const int X = j / Cs, ch = j - X * Cs;
+    T v = 0;
+    if (ch < real) {
+      const int dy = ch / sc, r = ch - dy * sc;       // r = dx*C + c: s*C consecutive input elements
+      const int yy = Y * s + dy - pad, x0 = X * s - pad;
+      const int xx = x0 + r / C;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = xn[(static_cast<long long>(yy) * W + x0) * C + r];
+    }
+    row[j] = v;
+  }
+}
+
+// dst[r][j] = idx[j] >= 0 ? src[r][idx[j]] : 0   (filter re-layouts)
+template <typename S>
+__global__ void gather_cols_kernel(const S* __restrict__ src, long long lds, float* __restrict__ dst, long long ldd,
+                                   int rows, int ncols, const int* __restrict__ idx) {
+  const long long total = static_cast<long long>(rows) * ncols;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int r = static_cast<int>(i / ncols), j = static_cast<int>(i - static_cast<long long>(r) * ncols);
+    const int k = idx[j];
+    dst[r * ldd + j] = k >= 0 ? to_float(src[r * lds + k]) : 0.f;
+  }
+}
+
+// dst[r][idx[j]] (+)= src[r][j] for idx[j] >= 0   (idx injective on its non-negative entries)
+__global__ void scatter_cols_kernel(const float* __restrict__ src, long long lds, float* __restrict__ dst,
+                                    long long ldd, int rows, int ncols, const int* __restrict__ idx, int accumulate) {
+  const long long total = static_cast<long long>(rows) * ncols;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
+    const int r = static_cast<int>(i / ncols), j = static_cast<int>(i - static_cast<long long>(r) * ncols);
+    const int k = idx[j];
+    if (k < 0) continue;
+    float* d = dst + r * ldd + k;
+    *d = accumulate ? *d + src[r * lds + j] : src[r * lds + j];
+  }
+}
+
 }  // namespace sg
 
 using namespace sg;
@@ -672,5 +728,43 @@ extern "C" int sg_conv_pack(const void* w, int w_bf16, long long ldw, int F, int
   else SG_PACK(float, float);
 #undef SG_PACK
   SG_CHECK_LAUNCH("conv_pack");
+  return 0;
+}
+
+extern "C" int sg_space_to_depth(const void* x, void* xs, int N, int H, int W, int C, int Hs, int Ws, int Cs, int s_,
+                                 int pad, int is_bf16, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (N <= 0) return 0;
+  SG_REQUIRE(s_ > 0 && pad >= 0 && Cs >= s_ * s_ * C && Hs > 0 && Ws > 0, "sg_space_to_depth: bad geometry");
+  const int grid = N * Hs;
+  if (is_bf16)
+    space_to_depth_kernel<unsigned short><<<grid, 256, 0, s>>>((const unsigned short*)x, (unsigned short*)xs, H, W, C, Hs, Ws, Cs, s_, pad);
+  else
+    space_to_depth_kernel<unsigned int><<<grid, 256, 0, s>>>((const unsigned int*)x, (unsigned int*)xs, H, W, C, Hs, Ws, Cs, s_, pad);
+  SG_CHECK_LAUNCH("space_to_depth");
+  return 0;
+}
+
+extern "C" int sg_gather_cols(const void* src, int src_bf16, long long lds, float* dst, long long ldd, int rows,
+                              int ncols, const int* idx, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || ncols <= 0) return 0;
+  SG_REQUIRE(src != nullptr && dst != nullptr && idx != nullptr && ldd >= ncols, "sg_gather_cols: bad arguments");
+  const int grid = ew_grid(static_cast<long long>(rows) * ncols, 256);
+  if (src_bf16)
+    gather_cols_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)src, lds, dst, ldd, rows, ncols, idx);
+  else
+    gather_cols_kernel<float><<<grid, 256, 0, s>>>((const float*)src, lds, dst, ldd, rows, ncols, idx);
+  SG_CHECK_LAUNCH("gather_cols");
+  return 0;
+}
+
+extern "C" int sg_scatter_cols(const float* src, long long lds, float* dst, long long ldd, int rows, int ncols,
+                               const int* idx, int accumulate, void* stream) {
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (rows <= 0 || ncols <= 0) return 0;
+  SG_REQUIRE(src != nullptr && dst != nullptr && idx != nullptr && lds >= ncols, "sg_scatter_cols: bad arguments");
+  scatter_cols_kernel<<<ew_grid(static_cast<long long>(rows) * ncols, 256), 256, 0, s>>>(src, lds, dst, ldd, rows, ncols, idx, accumulate);
+  SG_CHECK_LAUNCH("scatter_cols");
   return 0;
 }

@@ -127,80 +127,121 @@ __global__ void pool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y
   }
 }
 
-// 8 channels per thread (bf16, 128-bit accesses): C % 8 == 0.
+// Vector forms: one block per (image, row), threads over (column, 16-byte channel vector); C % Vec<T>::N == 0.
+// Only 32-bit index arithmetic, and the window is a compile-time bound so that every load of a pixel is issued
+// before the first use (the loops above wait for each window element in turn: ~6x slower on AlexNet's pools).
+//   forward : K = window size (2, 3) -> K*K predicated loads of x per output vector
+//   backward: MW = ceil(k / stride) = most windows per dimension that contain one input pixel (1, 2, 3)
+template <typename T, int K, bool MAX>
 __global__ void __launch_bounds__(256)
-pool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H, int W, int C,
-                     int OH, int OW, int k, int s, int pad, int is_max) {
-  const int cv = C / 8;
-  const long long total = static_cast<long long>(N) * OH * OW * cv;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
-    const int c = static_cast<int>(i % cv) * 8;
-    long long t = i / cv;
-    const int ox = static_cast<int>(t % OW); t /= OW;
-    const int oy = static_cast<int>(t % OH);
-    const int n = static_cast<int>(t / OH);
-    const int y0 = oy * s - pad, x0 = ox * s - pad;
-    const int y1 = min(y0 + k, H), x1 = min(x0 + k, W);
-    float acc[8];
+pool_fwd_row_kernel(const T* __restrict__ x, T* __restrict__ y, int H, int W, int C, int OH, int OW, int s, int pad) {
+  constexpr int V = Vec<T>::N;
+  const int cv = C / V;
+  const int n = blockIdx.x / OH, oy = blockIdx.x - n * OH;
+  const int y0 = oy * s - pad;
+  const T* xn = x + static_cast<long long>(n) * H * W * C;
+  T* yrow = y + static_cast<long long>(blockIdx.x) * OW * C;
+  for (int j = threadIdx.x; j < OW * cv; j += blockDim.x) {
+    const int ox = j / cv, c = (j - ox * cv) * V;
+    const int x0 = ox * s - pad;
+    float v[K * K][V];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = is_max ? -FLT_MAX : 0.f;
-    for (int yy = max(y0, 0); yy < y1; ++yy)
-      for (int xx = max(x0, 0); xx < x1; ++xx) {
-        float v[8];
-        Vec<__nv_bfloat16>::load(x + ((static_cast<long long>(n) * H + yy) * W + xx) * C + c, v);
+    for (int a = 0; a < K; ++a)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = is_max ? fmaxf(acc[j], v[j]) : acc[j] + v[j];
+      for (int b = 0; b < K; ++b) {
+        const int yy = y0 + a, xx = x0 + b;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+          Vec<T>::load(xn + (static_cast<long long>(yy) * W + xx) * C + c, v[a * K + b]);
+        } else {
+#pragma unroll
+          for (int q = 0; q < V; ++q) v[a * K + b][q] = MAX ? -FLT_MAX : 0.f;
+        }
       }
-    if (!is_max) {
-      const float inv = 1.f / (k * k);
+    float acc[V];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    for (int q = 0; q < V; ++q) acc[q] = v[0][q];
+#pragma unroll
+    for (int w = 1; w < K * K; ++w)
+#pragma unroll
+      for (int q = 0; q < V; ++q) acc[q] = MAX ? fmaxf(acc[q], v[w][q]) : acc[q] + v[w][q];
+    if (!MAX) {
+#pragma unroll
+      for (int q = 0; q < V; ++q) acc[q] *= 1.f / (K * K);
     }
-    Vec<__nv_bfloat16>::store(y + ((static_cast<long long>(n) * OH + oy) * OW + ox) * C + c, acc);
+    Vec<T>::store(yrow + static_cast<long long>(ox) * C + c, acc);
   }
 }
 
+template <typename T, int MW, bool MAX>
 __global__ void __launch_bounds__(256)
-pool_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
-                     const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H, int W,
-                     int C, int OH, int OW, int k, int s, int pad, int is_max) {
-  const int cv = C / 8;
-  const long long total = static_cast<long long>(N) * H * W * cv;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += stride) {
-    const int c = static_cast<int>(i % cv) * 8;
-    long long t = i / cv;
-    const int xx = static_cast<int>(t % W); t /= W;
-    const int yy = static_cast<int>(t % H);
-    const int n = static_cast<int>(t / H);
-    const long long xi = ((static_cast<long long>(n) * H + yy) * W + xx) * C + c;
-    float xv[8], g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    Vec<__nv_bfloat16>::load(x + xi, xv);
-    const int oy_lo = max(0, (yy + pad - k + s) / s), oy_hi = min(OH - 1, (yy + pad) / s);
+pool_bwd_row_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                    int H, int W, int C, int OH, int OW, int k, int s, int pad) {
+  constexpr int V = Vec<T>::N;
+  const int cv = C / V;
+  const int n = blockIdx.x / H, yy = blockIdx.x - n * H;
+  const int oy_lo = max(0, (yy + pad - k + s) / s), oy_hi = min(OH - 1, (yy + pad) / s);
+  const long long obase = static_cast<long long>(n) * OH * OW * C;
+  const T* xrow = x + static_cast<long long>(blockIdx.x) * W * C;
+  T* dxrow = dx + static_cast<long long>(blockIdx.x) * W * C;
+  const float inv = 1.f / (k * k);
+  for (int j = threadIdx.x; j < W * cv; j += blockDim.x) {
+    const int xx = j / cv, c = (j - xx * cv) * V;
     const int ox_lo = max(0, (xx + pad - k + s) / s), ox_hi = min(OW - 1, (xx + pad) / s);
-    for (int oy = oy_lo; oy <= oy_hi; ++oy)
-      for (int ox = ox_lo; ox <= ox_hi; ++ox) {
-        const long long o = ((static_cast<long long>(n) * OH + oy) * OW + ox) * C + c;
-        float gv[8];
-        Vec<__nv_bfloat16>::load(dy + o, gv);
-        if (is_max) {
-          float yv[8];
-          Vec<__nv_bfloat16>::load(y + o, yv);
+    float xv[V], gv[MW * MW][V], yv[MAX ? MW * MW : 1][V];
+    if (MAX) Vec<T>::load(xrow + static_cast<long long>(xx) * C + c, xv);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] += (yv[j] == xv[j]) ? gv[j] : 0.f;
+    for (int a = 0; a < MW; ++a)
+#pragma unroll
+      for (int b = 0; b < MW; ++b) {
+        const int oy = oy_lo + a, ox = ox_lo + b;
+        if (oy <= oy_hi && ox <= ox_hi) {
+          const long long o = obase + (static_cast<long long>(oy) * OW + ox) * C + c;
+          Vec<T>::load(dy + o, gv[a * MW + b]);
+          if (MAX) Vec<T>::load(y + o, yv[a * MW + b]);
         } else {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] += gv[j];
+          for (int q = 0; q < V; ++q) {
+            gv[a * MW + b][q] = 0.f;
+            if (MAX) yv[a * MW + b][q] = FLT_MAX;     // never equal to a finite input
+          }
         }
       }
-    if (!is_max) {
-      const float inv = 1.f / (k * k);
+    float g[V];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] *= inv;
+    for (int q = 0; q < V; ++q) g[q] = 0.f;
+#pragma unroll
+    for (int w = 0; w < MW * MW; ++w)
+#pragma unroll
+      for (int q = 0; q < V; ++q) g[q] += MAX ? (yv[w][q] == xv[q] ? gv[w][q] : 0.f) : gv[w][q];
+    if (!MAX) {
+#pragma unroll
+      for (int q = 0; q < V; ++q) g[q] *= inv;
     }
-    Vec<__nv_bfloat16>::store(dx + xi, g);
+    Vec<T>::store(dxrow + static_cast<long long>(xx) * C + c, g);
   }
+}
+
+template <typename T>
+static bool launch_pool_fwd_rows(const T* x, T* y, int N, int H, int W, int C, int OH, int OW, int k, int st, int pad,
+                                 int is_max, cudaStream_t s) {
+  const int grid = N * OH;
+#define SG_POOL_F(K_, M_) pool_fwd_row_kernel<T, K_, M_><<<grid, 256, 0, s>>>(x, y, H, W, C, OH, OW, st, pad)
+  if (k == 2) { if (is_max) SG_POOL_F(2, true); else SG_POOL_F(2, false); return true; }
+  if (k == 3) { if (is_max) SG_POOL_F(3, true); else SG_POOL_F(3, false); return true; }
+#undef SG_POOL_F
+  return false;
+}
+
+template <typename T>
+static bool launch_pool_bwd_rows(const T* x, const T* y, const T* dy, T* dx, int N, int H, int W, int C, int OH, int OW,
+                                 int k, int st, int pad, int is_max, cudaStream_t s) {
+  const int grid = N * H, mw = (k + st - 1) / st;
+#define SG_POOL_B(W_, M_) pool_bwd_row_kernel<T, W_, M_><<<grid, 256, 0, s>>>(x, y, dy, dx, H, W, C, OH, OW, k, st, pad)
+  if (mw == 1) { if (is_max) SG_POOL_B(1, true); else SG_POOL_B(1, false); return true; }
+  if (mw == 2) { if (is_max) SG_POOL_B(2, true); else SG_POOL_B(2, false); return true; }
+  if (mw == 3) { if (is_max) SG_POOL_B(3, true); else SG_POOL_B(3, false); return true; }
+#undef SG_POOL_B
+  return false;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -250,6 +291,81 @@ __global__ void lrn_bwd_kernel(const T* __restrict__ x, const float* __restrict_
   }
 }
 
+// Tiled forms (C % Vec<T>::N == 0, C <= LRN_TILE): a block stages whole pixels in shared memory with 16-byte loads,
+// then every thread sums its channel window from shared memory — each element is read from global memory once and
+// raised to a power once (the loops above re-read x / dy / norm and call __powf for every window element).
+constexpr int LRN_TILE = 2048;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+lrn_fwd_tile_kernel(const T* __restrict__ x, T* __restrict__ y, float* __restrict__ norm, long long pixels, int C,
+                    int ppt, int half, float salpha, float beta, float knorm) {
+  constexpr int V = Vec<T>::N;
+  __shared__ __align__(16) float sx[LRN_TILE];
+  for (long long tile = blockIdx.x; tile * ppt < pixels; tile += gridDim.x) {
+    const long long p0 = tile * ppt, base = p0 * C;
+    const int np = static_cast<int>(min(static_cast<long long>(ppt), pixels - p0)), ne = np * C;
+    for (int e = threadIdx.x * V; e < ne; e += blockDim.x * V) {
+      float xv[V];
+      Vec<T>::load(x + base + e, xv);
+#pragma unroll
+      for (int q = 0; q < V; q += 4)
+        *reinterpret_cast<float4*>(&sx[e + q]) = make_float4(xv[q], xv[q + 1], xv[q + 2], xv[q + 3]);
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < ne; e += blockDim.x) {
+      const int c = e % C;
+      float sum = 0.f;
+      for (int cc = max(-half, -c); cc <= min(half, C - 1 - c); ++cc) sum += sx[e + cc] * sx[e + cc];
+      const float nm = knorm + salpha * sum;
+      norm[base + e] = nm;
+      y[base + e] = from_float<T>(sx[e] * __powf(nm, -beta));
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+lrn_bwd_tile_kernel(const T* __restrict__ x, const float* __restrict__ norm, const T* __restrict__ dy,
+                    T* __restrict__ dx, long long pixels, int C, int ppt, int half, float coef, float beta) {
+  constexpr int V = Vec<T>::N;
+  __shared__ __align__(16) float st[LRN_TILE], sa[LRN_TILE], sx[LRN_TILE];
+  for (long long tile = blockIdx.x; tile * ppt < pixels; tile += gridDim.x) {
+    const long long p0 = tile * ppt, base = p0 * C;
+    const int np = static_cast<int>(min(static_cast<long long>(ppt), pixels - p0)), ne = np * C;
+    for (int e = threadIdx.x * V; e < ne; e += blockDim.x * V) {
+      float xv[V], gv[V], nv[V], t[V], a[V];
+      Vec<T>::load(x + base + e, xv);
+      Vec<T>::load(dy + base + e, gv);
+#pragma unroll
+      for (int q = 0; q < V; q += 4) {
+        const float4 n4 = *reinterpret_cast<const float4*>(norm + base + e + q);
+        nv[q] = n4.x; nv[q + 1] = n4.y; nv[q + 2] = n4.z; nv[q + 3] = n4.w;
+      }
+#pragma unroll
+      for (int q = 0; q < V; ++q) {
+        a[q] = gv[q] * __powf(nv[q], -beta);          // dy * norm^-beta
+        t[q] = a[q] * xv[q] / nv[q];                  // dy * x * norm^(-beta-1)
+      }
+#pragma unroll
+      for (int q = 0; q < V; q += 4) {
+        *reinterpret_cast<float4*>(&st[e + q]) = make_float4(t[q], t[q + 1], t[q + 2], t[q + 3]);
+        *reinterpret_cast<float4*>(&sa[e + q]) = make_float4(a[q], a[q + 1], a[q + 2], a[q + 3]);
+        *reinterpret_cast<float4*>(&sx[e + q]) = make_float4(xv[q], xv[q + 1], xv[q + 2], xv[q + 3]);
+      }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < ne; e += blockDim.x) {
+      const int c = e % C;
+      float sum = 0.f;
+      for (int cc = max(-half, -c); cc <= min(half, C - 1 - c); ++cc) sum += st[e + cc];
+      dx[base + e] = from_float<T>(sa[e] - coef * sx[e] * sum);
+    }
+    __syncthreads();
+  }
+}
+
 static inline int grid_for(long long n, int threads) {
   long long b = (n + threads - 1) / threads;
   const long long cap = static_cast<long long>(num_sms()) * 16;
@@ -286,9 +402,14 @@ extern "C" int sg_pool_fwd(const void* x, void* y, int N, int H, int W, int C, i
   const long long total = static_cast<long long>(N) * OH * OW * C;
   if (total <= 0) return 0;
   SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_fwd: bad window");
-  if (is_bf16 && C % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0)
-    pool_fwd_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
-  else if (is_bf16)
+  const bool aligned = (((uintptr_t)x | (uintptr_t)y) & 15) == 0;
+  bool done = false;
+  if (aligned && is_bf16 && C % 8 == 0)
+    done = launch_pool_fwd_rows((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max, s);
+  else if (aligned && !is_bf16 && C % 4 == 0)
+    done = launch_pool_fwd_rows((const float*)x, (float*)y, N, H, W, C, OH, OW, k, stride, pad, is_max, s);
+  if (done) {
+  } else if (is_bf16)
     pool_fwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
   else
     pool_fwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (float*)y, N, H, W, C, OH, OW, k, stride, pad, is_max);
@@ -303,10 +424,14 @@ extern "C" int sg_pool_bwd(const void* x, const void* y, const void* dy, void* d
   const long long total = static_cast<long long>(N) * H * W * C;
   if (total <= 0) return 0;
   SG_REQUIRE(k > 0 && stride > 0 && pad >= 0 && pad < k, "sg_pool_bwd: bad window");
-  if (is_bf16 && C % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0 && ((uintptr_t)dy & 15) == 0 &&
-      ((uintptr_t)dx & 15) == 0)
-    pool_bwd_vec8_kernel<<<grid_for(total / 8, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
-  else if (is_bf16)
+  const bool aligned = (((uintptr_t)x | (uintptr_t)y | (uintptr_t)dy | (uintptr_t)dx) & 15) == 0;
+  bool done = false;
+  if (aligned && is_bf16 && C % 8 == 0)
+    done = launch_pool_bwd_rows((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max, s);
+  else if (aligned && !is_bf16 && C % 4 == 0)
+    done = launch_pool_bwd_rows((const float*)x, (const float*)y, (const float*)dy, (float*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max, s);
+  if (done) {
+  } else if (is_bf16)
     pool_bwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
   else
     pool_bwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (const float*)y, (const float*)dy, (float*)dx, N, H, W, C, OH, OW, k, stride, pad, is_max);
@@ -320,7 +445,15 @@ extern "C" int sg_lrn_fwd(const void* x, void* y, float* norm, long long pixels,
   const long long total = pixels * C;
   if (total <= 0) return 0;
   SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_fwd: local size must be odd and positive");
-  if (is_bf16)
+  const int vn = is_bf16 ? 8 : 4;
+  if (C % vn == 0 && C <= LRN_TILE && ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)norm)) & 15) == 0) {
+    const int ppt = LRN_TILE / C;
+    const int grid = grid_for((pixels + ppt - 1) / ppt * 256, 256);
+    if (is_bf16)
+      lrn_fwd_tile_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, norm, pixels, C, ppt, lsize / 2, alpha / lsize, beta, knorm);
+    else
+      lrn_fwd_tile_kernel<float><<<grid, 256, 0, s>>>((const float*)x, (float*)y, norm, pixels, C, ppt, lsize / 2, alpha / lsize, beta, knorm);
+  } else if (is_bf16)
     lrn_fwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, norm, pixels, C, lsize, alpha, beta, knorm);
   else
     lrn_fwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, (float*)y, norm, pixels, C, lsize, alpha, beta, knorm);
@@ -334,7 +467,16 @@ extern "C" int sg_lrn_bwd(const void* x, const float* norm, const void* dy, void
   const long long total = pixels * C;
   if (total <= 0) return 0;
   SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_bwd: local size must be odd and positive");
-  if (is_bf16)
+  const int vn = is_bf16 ? 8 : 4;
+  if (C % vn == 0 && C <= LRN_TILE && ((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)norm)) & 15) == 0) {
+    const int ppt = LRN_TILE / C;
+    const int grid = grid_for((pixels + ppt - 1) / ppt * 256, 256);
+    const float coef = 2.f * beta * alpha / lsize;
+    if (is_bf16)
+      lrn_bwd_tile_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, norm, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, pixels, C, ppt, lsize / 2, coef, beta);
+    else
+      lrn_bwd_tile_kernel<float><<<grid, 256, 0, s>>>((const float*)x, norm, (const float*)dy, (float*)dx, pixels, C, ppt, lsize / 2, coef, beta);
+  } else if (is_bf16)
     lrn_bwd_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>((const __nv_bfloat16*)x, norm, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, pixels, C, lsize, alpha, beta);
   else
     lrn_bwd_kernel<float><<<grid_for(total, 256), 256, 0, s>>>((const float*)x, norm, (const float*)dy, (float*)dx, pixels, C, lsize, alpha, beta);

@@ -107,6 +107,18 @@ int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long
  * dimension). */
 int sg_copy2d(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, int is_bf16, void* stream);
 int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, void* stream);
+/* Space-to-depth for strided convolutions over thin (grey / RGB) inputs:
+ *   xs[n][Y][X][(dy*s + dx)*C + c] = x[n][Y*s + dy - pad][X*s + dx - pad][c], zero outside the image and for the
+ *   padding channels [s*s*C, Cs).  x: [N][H][W][C], xs: [N][Hs][Ws][Cs], both of one element type. */
+int sg_space_to_depth(const void* x, void* xs, int N, int H, int W, int C, int Hs, int Ws, int Cs, int s, int pad,
+                      int is_bf16, void* stream);
+/* Column re-layouts of a [rows][*] matrix through an index list (idx[j] < 0: no source / dropped):
+ *   gather : dst[r][j] = src[r][idx[j]] (or 0), fp32 or bf16 source, fp32 destination
+ *   scatter: dst[r][idx[j]] (+)= src[r][j]; idx must not repeat a non-negative entry */
+int sg_gather_cols(const void* src, int src_bf16, long long lds, float* dst, long long ldd, int rows, int ncols,
+                   const int* idx, void* stream);
+int sg_scatter_cols(const float* src, long long lds, float* dst, long long ldd, int rows, int ncols, const int* idx,
+                    int accumulate, void* stream);
 /* Per image [rows][cols] -> [cols][rows] (NCHW <-> NHWC). */
 int sg_transpose_planes(const void* src, int src_bf16, void* dst, int dst_bf16, int batch, int rows,
                         int cols, void* stream);

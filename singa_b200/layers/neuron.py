@@ -316,12 +316,12 @@ class ConvolutionLayer(NeuronLayer):
             self._setup_native()
 
     def _setup_native(self):
-        from ..ops.conv import ConvPlan
+        from ..ops.conv import make_plan
         src = self.srclayers[0]
         need_dgrad = not (src.is_datalayer or src.is_parserlayer)
         self.P = self.batchsize * self.col_width
-        self.plan = ConvPlan(self.batchsize, self.channels, self.height, self.width, self.num_filters, self.kernel,
-                             self.stride, self.pad, ctx().act_dtype, ctx().device, need_dgrad=need_dgrad)
+        self.plan = make_plan(self.batchsize, self.channels, self.height, self.width, self.num_filters, self.kernel,
+                              self.stride, self.pad, ctx().act_dtype, ctx().device, need_dgrad=need_dgrad)
         self.weight.data16 = self.plan.wf      # the forward GEMM's filter operand ([F][(ky,kx,c)], zero padded)
 
         def pack(w=self.weight, plan=self.plan):

@@ -10,6 +10,10 @@ GEMM.  What remains explicit (``sg_im2col`` / ``sg_col2im``), and why:
     matrix is an MN-major operand, which for tf32 exists only with 128-byte rows — a 3-channel pixel would be 90 %
     zero fill;
   * the DATA gradient of strided convolutions (no such layer feeds a trainable layer in the five benchmark nets).
+
+Strided convolutions over thin inputs (AlexNet conv1: RGB, 11x11, stride 4) run as ``S2dConvPlan``: a space-to-depth
+copy of the input turns them into a stride-1 convolution over s*s*C channels (3x3 over 48 channels for conv1), which
+has pixels wide enough for full tile loads and an implicit weight gradient; ``make_plan`` chooses.
 """
 from __future__ import annotations
 
@@ -134,3 +138,68 @@ class ConvPlan:
         K.gemm(dy2d, self.w_dense[:, :kc], self.P, kc, self.F, b_mn=True, **out)
         K.col2im_nhwc(self.dcol, self.dcol.stride(0), dx2d, self.N, self.H, self.W, self.C, self.OH, self.OW, self.k,
                       self.stride, self.pad, grad_act, aux2d)
+
+
+class S2dConvPlan:
+    """k x k, stride s > 1 over C thin channels == ceil(k/s)^2, stride 1 over s*s*C channels of the space-to-depth
+    image (taps beyond k are zero filters).  Same interface as ``ConvPlan`` for an input layer (no data gradient).
+
+    x[n][Y*s+dy-pad][X*s+dx-pad][c] -> xs[n][Y][X][(dy*s+dx)*C + c];  filter tap (ty*s+dy, tx*s+dx) of channel c ->
+    inner tap (ty, tx) of channel (dy*s+dx)*C + c.  The inner plan keeps the reference's [F][c*k*k + tap] layout
+    for its own (inner) geometry, so the re-layouts are two index lists over the columns of the weight matrix."""
+
+    def __init__(self, N, C, H, W, F, k, stride, pad, dtype: torch.dtype, device):
+        assert stride > 1
+        self.N, self.C, self.H, self.W, self.F, self.k, self.stride, self.pad = N, C, H, W, F, k, stride, pad
+        self.dtype, self.device = dtype, device
+        eb = 2 if dtype == torch.bfloat16 else 4
+        q = 16 // eb
+        s = stride
+        self.ks = (k + s - 1) // s
+        self.OH = (H + 2 * pad - k) // s + 1
+        self.OW = (W + 2 * pad - k) // s + 1
+        self.P = N * self.OH * self.OW
+        self.Hs, self.Ws = self.OH + self.ks - 1, self.OW + self.ks - 1
+        self.Cs = _rup(s * s * C, q)
+        self.inner = ConvPlan(N, self.Cs, self.Hs, self.Ws, F, self.ks, 1, 0, dtype, device, need_dgrad=False)
+        self.wf = self.inner.wf
+        self.xs = torch.zeros(N, self.Hs, self.Ws, self.Cs, dtype=dtype, device=device)
+        self.xs_cl = self.xs.permute(0, 3, 1, 2)          # [N, Cs, Hs, Ws] channels-last view for the inner plan
+        ncol_in = self.Cs * self.ks * self.ks
+        idx = torch.full((ncol_in,), -1, dtype=torch.int32)
+        for dy in range(s):
+            for dx in range(s):
+                for c in range(C):
+                    cs = (dy * s + dx) * C + c
+                    for ty in range(self.ks):
+                        for tx in range(self.ks):
+                            ky, kx = ty * s + dy, tx * s + dx
+                            if ky < k and kx < k:
+                                idx[(cs * self.ks + ty) * self.ks + tx] = (c * k + ky) * k + kx
+        self.idx = idx.to(device)
+        self.w_inner = torch.zeros(F, ncol_in, dtype=torch.float32, device=device)
+        self.dw_inner = torch.zeros(F, ncol_in, dtype=torch.float32, device=device)
+
+    def pack(self, w: torch.Tensor) -> None:
+        K.gather_cols(w, self.w_inner, self.idx)
+        self.inner.pack(self.w_inner)
+
+    def forward(self, x, y2d, bias=None, act=ACT_NONE, wait=None):
+        K.space_to_depth(x, self.xs, self.N, self.H, self.W, self.C, self.Hs, self.Ws, self.Cs, self.stride, self.pad)
+        self.inner.forward(self.xs_cl, y2d, bias=bias, act=act, wait=wait)
+
+    def wgrad(self, dy, dw, accumulate=False):
+        self.inner.wgrad(dy, self.dw_inner)
+        K.scatter_cols(self.dw_inner, dw, self.idx, accumulate)
+
+    def dgrad(self, dy, dx2d, grad_act=ACT_NONE, aux2d=None):
+        raise NotImplementedError("S2dConvPlan serves input layers only")
+
+
+def make_plan(N, C, H, W, F, k, stride, pad, dtype: torch.dtype, device, need_dgrad: bool = True):
+    """The plan for one convolution layer: space-to-depth for strided convolutions whose input pixels are narrower
+    than 64 bytes and that need no data gradient (input layers), the direct implicit GEMM otherwise."""
+    eb = 2 if dtype == torch.bfloat16 else 4
+    if stride > 1 and not need_dgrad and C * eb < 64 and stride * stride * C * eb >= 64:
+        return S2dConvPlan(N, C, H, W, F, k, stride, pad, dtype, device)
+    return ConvPlan(N, C, H, W, F, k, stride, pad, dtype, device, need_dgrad=need_dgrad)

@@ -66,6 +66,25 @@ def copy2d(src, lds, dst, ldd, rows, cols):
 copy2d_bf16 = copy2d
 
 
+def space_to_depth(x, xs, N, H, W, C, Hs, Ws, Cs, s, pad):
+    assert x.dtype == xs.dtype
+    _call("sg_space_to_depth", x.data_ptr(), xs.data_ptr(), N, H, W, C, Hs, Ws, Cs, s, pad, _bf(x))
+
+
+def gather_cols(src, dst, idx):
+    """dst[r][j] = src[r][idx[j]] (0 where idx[j] < 0); src fp32 / bf16, dst fp32."""
+    assert dst.dtype == torch.float32 and idx.dtype == torch.int32 and src.stride(-1) == 1 and dst.stride(-1) == 1
+    _call("sg_gather_cols", src.data_ptr(), _bf(src), src.stride(0), dst.data_ptr(), dst.stride(0), dst.shape[0],
+          idx.numel(), idx.data_ptr())
+
+
+def scatter_cols(src, dst, idx, accumulate=False):
+    """dst[r][idx[j]] (+)= src[r][j] for idx[j] >= 0; fp32 both."""
+    assert src.dtype == torch.float32 and dst.dtype == torch.float32 and idx.dtype == torch.int32
+    _call("sg_scatter_cols", src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), src.shape[0], idx.numel(),
+          idx.data_ptr(), 1 if accumulate else 0)
+
+
 def transpose_planes(src, dst, batch, rows, cols):
     _call("sg_transpose_planes", src.data_ptr(), _bf(src), dst.data_ptr(), _bf(dst), batch, rows, cols)
 

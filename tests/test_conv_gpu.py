@@ -105,3 +105,54 @@ def test_conv_larger_batch_many_tiles():
     finally:
         torch.backends.cudnn.allow_tf32 = prev
     torch.testing.assert_close(y, ref, **_tols(dtype, C * k * k))
+
+
+S2D_CASES = [
+    # N, C, H, W, F, k, stride, pad
+    (2, 3, 35, 35, 24, 11, 4, 0),      # AlexNet conv1 family: 3x3 over 48 channels after space-to-depth
+    (3, 3, 31, 29, 40, 7, 2, 3),       # padded, ragged, stride 2 (4x4 over 12 channels, padded to 16-byte pixels)
+    (2, 1, 33, 33, 16, 5, 4, 1),       # grey input, k not a multiple of the stride
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", S2D_CASES)
+def test_conv_space_to_depth_plan(case, dtype):
+    """Strided convolution of a thin input layer as a stride-1 convolution over the space-to-depth image."""
+    from singa_b200.ops.conv import S2dConvPlan, make_plan
+    N, C, H, W, F, k, s, p = case
+    torch.manual_seed(sum(case))
+    x32 = torch.randn(N, C, H, W, device=DEV) * 0.5
+    w32 = torch.randn(F, C * k * k, device=DEV) * 0.2
+    b32 = torch.randn(F, device=DEV)
+    x = _nhwc(x32.to(dtype))
+    plan = S2dConvPlan(N, C, H, W, F, k, s, p, dtype, DEV)
+    if C * (2 if dtype == torch.bfloat16 else 4) * s * s >= 64:
+        assert isinstance(make_plan(N, C, H, W, F, k, s, p, dtype, DEV, need_dgrad=False), S2dConvPlan)
+    plan.pack(w32)
+    OH, OW = plan.OH, plan.OW
+    xr, wr = x.float(), w32.to(dtype).float().view(F, C, k, k)
+    prev = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        y = _nhwc(torch.full((N, F, OH, OW), float("nan"), device=DEV, dtype=dtype))
+        y2d = y.permute(0, 2, 3, 1).reshape(plan.P, F)
+        plan.forward(x if C > 1 else x[:, 0], y2d, bias=b32, act=G.ACT_RELU)
+        torch.cuda.synchronize()
+        ref = torch.relu(F_.conv2d(xr, wr, b32, stride=s, padding=p))
+        assert ref.shape == y.shape
+        torch.testing.assert_close(y.float(), ref, **_tols(dtype, C * k * k))
+        dy32 = torch.randn(N, F, OH, OW, device=DEV) * 0.5
+        dy = _nhwc(dy32.to(dtype))
+        dw = torch.full((F, C * k * k), float("nan"), device=DEV)
+        plan.wgrad(dy, dw)
+        torch.cuda.synchronize()
+        dw_ref = torch.nn.grad.conv2d_weight(xr, wr.shape, dy.float(), stride=s, padding=p).reshape(F, -1)
+        tol = _tols(dtype, plan.P)
+        torch.testing.assert_close(dw, dw_ref, **tol)
+        dw2 = torch.ones_like(dw)
+        plan.wgrad(dy, dw2, accumulate=True)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(dw2, dw_ref + 1.0, **tol)
+    finally:
+        torch.backends.cudnn.allow_tf32 = prev

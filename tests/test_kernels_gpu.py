@@ -157,25 +157,32 @@ def test_softmax_loss(rows, dim, topk):
     torch.testing.assert_close(grad.float(), g, rtol=2e-2, atol=1e-5)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("is_max", [True, False])
 @pytest.mark.parametrize("shape,k,s,pad", [((4, 32, 32, 32), 3, 2, 0), ((2, 20, 24, 24), 2, 2, 0),
-                                           ((3, 8, 9, 9), 4, 2, 0), ((2, 16, 13, 13), 3, 2, 1)])
-def test_pool(shape, k, s, pad, is_max):
+                                           ((3, 8, 9, 9), 4, 2, 0), ((2, 16, 13, 13), 3, 2, 1),
+                                           ((2, 24, 11, 14), 3, 1, 1), ((2, 6, 10, 10), 3, 2, 0),
+                                           ((5, 96, 55, 55), 3, 2, 0)])
+def test_pool(shape, k, s, pad, is_max, dtype):
+    """Row kernels (16-byte channel vectors; windows of 2 / 3, one to three windows per pixel) and the scalar
+    fallbacks (k = 4, channel counts that are not a vector multiple) against the fp32 reference."""
     n, c, h, w = shape
     x32 = torch.randn(shape, device=DEV)
     if is_max:   # exercise the tie rule
         x32 = (x32 * 2).round() / 2
-    x = nhwc(x32.to(torch.bfloat16))
+    x = nhwc(x32.to(dtype))
     oh, ow = R.pool_out_size(h, k, s, pad), R.pool_out_size(w, k, s, pad)
-    y = nhwc(torch.empty(n, c, oh, ow, device=DEV, dtype=torch.bfloat16))
+    y = nhwc(torch.full((n, c, oh, ow), float("nan"), device=DEV, dtype=dtype))
     K().pool_fwd(x, y, n, h, w, c, oh, ow, k, s, pad, is_max)
     yr = R.pool_fwd(x.float(), k, s, pad, is_max)
-    torch.testing.assert_close(y.float(), yr, rtol=1e-2, atol=1e-2)
-    dy = nhwc(torch.randn(n, c, oh, ow, device=DEV).to(torch.bfloat16))
-    dx = nhwc(torch.empty(shape, device=DEV, dtype=torch.bfloat16))
+    tol = dict(rtol=1e-2, atol=1e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(y.float(), yr, **tol)
+    dy = nhwc(torch.randn(n, c, oh, ow, device=DEV).to(dtype))
+    dx = nhwc(torch.full(shape, float("nan"), device=DEV, dtype=dtype))
     K().pool_bwd(x, y, dy, dx, n, h, w, c, oh, ow, k, s, pad, is_max)
     dxr = R.pool_bwd(x.float(), y.float(), dy.float(), k, s, pad, is_max)
-    torch.testing.assert_close(dx.float(), dxr, rtol=2e-2, atol=2e-2)
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(dx.float(), dxr, **tol)
 
 
 def test_pool_reference_matches_torch_when_exact():
@@ -184,22 +191,27 @@ def test_pool_reference_matches_torch_when_exact():
     torch.testing.assert_close(R.pool_fwd(x, 2, 2, 0, False), torch.nn.functional.avg_pool2d(x, 2, 2))
 
 
-@pytest.mark.parametrize("lsize,C", [(5, 96), (3, 32)])
-def test_lrn(lsize, C):
-    n, h, w = 4, 13, 13
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("lsize,C,hw", [(5, 96, 13), (3, 32, 13), (5, 256, 7), (3, 6, 5), (5, 2400, 2)])
+def test_lrn(lsize, C, hw, dtype):
+    """Tiled kernels (whole pixels staged in shared memory) and the scalar fallbacks (C = 6: not a vector
+    multiple, C = 2400: wider than a tile)."""
+    n, h, w = 4, hw, hw
     alpha, beta, knorm = 1e-2, 0.75, 1.0
-    x = nhwc((torch.randn(n, C, h, w, device=DEV) * 3).to(torch.bfloat16))
-    y = nhwc(torch.empty_like(x))
-    norm = nhwc(torch.empty(n, C, h, w, device=DEV))
+    x = nhwc((torch.randn(n, C, h, w, device=DEV) * 3).to(dtype))
+    y = nhwc(torch.full_like(x, float("nan")))
+    norm = nhwc(torch.full((n, C, h, w), float("nan"), device=DEV))
     K().lrn_fwd(x, y, norm, n * h * w, C, lsize, alpha, beta, knorm)
     yr, nr = R.lrn_fwd(x.float(), lsize, alpha, beta, knorm)
     torch.testing.assert_close(norm, nr, rtol=1e-4, atol=1e-5)
-    torch.testing.assert_close(y.float(), yr, rtol=1e-2, atol=1e-2)
-    dy = nhwc(torch.randn(n, C, h, w, device=DEV).to(torch.bfloat16))
-    dx = nhwc(torch.empty_like(x))
+    tol = dict(rtol=1e-2, atol=1e-2) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(y.float(), yr, **tol)
+    dy = nhwc(torch.randn(n, C, h, w, device=DEV).to(dtype))
+    dx = nhwc(torch.full_like(x, float("nan")))
     K().lrn_bwd(x, norm, dy, dx, n * h * w, C, lsize, alpha, beta)
     dxr = R.lrn_bwd(x.float(), nr, dy.float(), lsize, alpha, beta)
-    torch.testing.assert_close(dx.float(), dxr, rtol=2e-2, atol=2e-2)
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(dx.float(), dxr, **tol)
 
 
 def test_lrn_reference_matches_autograd():
