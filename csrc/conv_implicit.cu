@@ -116,6 +116,7 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     if (lane == 0) {
       if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
       uint32_t stage = 0, phase = 0;
+      const int conv_oh = cp.OHW / cp.OW;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         const int slice = p.split_k == 1 ? 0 : item / num_tiles;
         const int tile = item - slice * num_tiles;
@@ -125,12 +126,45 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         const int n0 = (tile / m_tiles) * BN;
         // MODE_ROWS: the tile's first pixel, decomposed once per tile
         int img = 0, base_w = 0, base_h = 0;
+        // MODE_COLS: this one thread issues 4 + BN/MN_BOX loads per k-block and the kernel was found to be bound by
+        // that issue loop (ncu: the MMA warp starves on the full barrier while the producer never waits), so everything
+        // that does not change with the k-block is decided here: the (channel, tap) of each of the tile's boxes, and a
+        // pixel cursor (image, row, column) that is advanced by BK instead of being divided out again.
+        constexpr int NB = BN / MN_BOX;
+        int box_c[NB];
+        unsigned short box_kx[NB], box_ky[NB];
+        int pimg = 0, poy = 0, pox = 0;
+        int rq = 0, rch = 0, rkx = 0, rky = 0;      // MODE_ROWS: cursor over the (tap, channel chunk) boxes of K
         if (MODE == MODE_ROWS) {
+          rq = kb_lo * (128 / cp.R);
+          const int tap = rq / cp.nchunk;
+          rch = rq - tap * cp.nchunk;
+          rky = tap / cp.ksize;
+          rkx = tap - rky * cp.ksize;
           img = m0 / cp.OHW;
           const int rem = m0 - img * cp.OHW;
           const int oy = rem / cp.OW;
           base_h = oy * cp.stride - cp.pad_lo;
           base_w = (rem - oy * cp.OW) * cp.stride - cp.pad_lo;
+        } else {
+          int q = n0 / MN_BOX;
+          int tap = q / cp.nchunk;
+          int ch = q - tap * cp.nchunk;
+          int ky = tap / cp.ksize;
+          int kx = tap - ky * cp.ksize;
+#pragma unroll
+          for (int b = 0; b < NB; ++b, ++q) {
+            const bool live = q < cp.nsub;
+            box_c[b] = live ? ch * cp.chunk_elems : cp.c_oob;
+            box_kx[b] = static_cast<unsigned short>(live ? kx : 0);
+            box_ky[b] = static_cast<unsigned short>(live ? ky : 0);
+            if (++ch == cp.nchunk) { ch = 0; if (++kx == cp.ksize) { kx = 0; ++ky; } }
+          }
+          const int k0 = kb_lo * BK;
+          pimg = k0 / cp.OHW;
+          const int rem = k0 - pimg * cp.OHW;
+          poy = rem / cp.OW;
+          pox = rem - poy * cp.OW;
         }
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
@@ -142,16 +176,11 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             // A: 128/R boxes of [128 pixels][R bytes]; box q of the K dimension = (tap, channel chunk)
             const int per_kb = 128 / cp.R;
             const uint32_t box_bytes = BM * cp.R;
-            int q = kb * per_kb;
-            int tap = q / cp.nchunk;
-            int ch = q - tap * cp.nchunk;
-            int ky = tap / cp.ksize;
-            int kx = tap - ky * cp.ksize;
-            for (int i = 0; i < per_kb; ++i, ++q) {
-              const int c0 = q < cp.nsub ? ch * cp.chunk_elems : cp.c_oob;
-              tma_load_im2col_4d(sa + i * box_bytes, &tma_a, fb, c0, base_w, base_h, img, q < cp.nsub ? kx : 0,
-                                 q < cp.nsub ? ky : 0);
-              if (++ch == cp.nchunk) { ch = 0; if (++kx == cp.ksize) { kx = 0; ++ky; } }
+            for (int i = 0; i < per_kb; ++i, ++rq) {
+              const bool live = rq < cp.nsub;
+              tma_load_im2col_4d(sa + i * box_bytes, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w, base_h,
+                                 img, live ? rkx : 0, live ? rky : 0);
+              if (++rch == cp.nchunk) { rch = 0; if (++rkx == cp.ksize) { rkx = 0; ++rky; } }
             }
             tma_load_2d(sb, &tma_b, fb, kb * BK, n0);
           } else {
@@ -159,22 +188,15 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             const int k0 = kb * BK;
 #pragma unroll
             for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
-            const int pimg = k0 / cp.OHW;
-            const int rem = k0 - pimg * cp.OHW;
-            const int oy = rem / cp.OW;
-            const int bh = oy * cp.stride - cp.pad_lo;
-            const int bw = (rem - oy * cp.OW) * cp.stride - cp.pad_lo;
-            int q = n0 / MN_BOX;
-            int tap = q / cp.nchunk;
-            int ch = q - tap * cp.nchunk;
-            int ky = tap / cp.ksize;
-            int kx = tap - ky * cp.ksize;
-#pragma unroll 1
-            for (int b = 0; b < BN / MN_BOX; ++b, ++q) {
-              const bool live = q < cp.nsub;
-              tma_load_im2col_4d(sb + b * MN_BOX_BYTES, &tma_b, fb, live ? ch * cp.chunk_elems : cp.c_oob, bw, bh, pimg,
-                                 live ? kx : 0, live ? ky : 0);
-              if (++ch == cp.nchunk) { ch = 0; if (++kx == cp.ksize) { kx = 0; ++ky; } }
+            const int bh = poy * cp.stride - cp.pad_lo;
+            const int bw = pox * cp.stride - cp.pad_lo;
+#pragma unroll
+            for (int b = 0; b < NB; ++b)
+              tma_load_im2col_4d(sb + b * MN_BOX_BYTES, &tma_b, fb, box_c[b], bw, bh, pimg, box_kx[b], box_ky[b]);
+            pox += BK;
+            while (pox >= cp.OW) {
+              pox -= cp.OW;
+              if (++poy == conv_oh) { poy = 0; ++pimg; }
             }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }

@@ -75,9 +75,26 @@ __global__ void act_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y
 // ---------------------------------------------------------------------------------- dropout
 // mask(i) = (u(seed, i) < pkeep) / pkeep, regenerated in backward from (seed, i): no mask tensor.
 // Reference semantics: src/worker/layer.cc:142-160.
+__device__ __forceinline__ void load4(const float* p, float (&v)[4]) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void load4(const __nv_bfloat16* p, float (&v)[4]) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  v[0] = __uint_as_float(t.x << 16); v[1] = __uint_as_float(t.x & 0xFFFF0000u);
+  v[2] = __uint_as_float(t.y << 16); v[3] = __uint_as_float(t.y & 0xFFFF0000u);
+}
+__device__ __forceinline__ void store4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, const float (&v)[4]) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+
 template <typename T>
 __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, float pkeep,
-                               unsigned long long seed, const unsigned long long* __restrict__ seed_dev) {
+                               unsigned long long seed, const unsigned long long* __restrict__ seed_dev, bool vec) {
   // seed_dev (optional) holds a per-step value in device memory so a captured CUDA graph draws a fresh
   // mask on every replay.
   if (seed_dev != nullptr) seed ^= (*seed_dev + 1ull) * 0x9E3779B97F4A7C15ull;
@@ -87,6 +104,14 @@ __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long 
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
     float u[4];
     philox_uniform4(seed, static_cast<unsigned long long>(i), u);
+    if (vec && i * 4 + 4 <= n) {          // one 16-byte (fp32) / 8-byte (bf16) access per Philox block
+      float v[4];
+      load4(x + i * 4, v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = u[j] < pkeep ? v[j] * inv : 0.f;
+      store4(y + i * 4, v);
+      continue;
+    }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const long long e = i * 4 + j;
@@ -417,26 +442,48 @@ __global__ void copy2d_kernel(const T* __restrict__ src, long long lds, T* __res
 // convolution over C channels equals a ceil(k/s) x ceil(k/s), stride-1 convolution over s*s*C channels of
 //   xs[n][Y][X][(dy*s + dx)*C + c] = x[n][Y*s + dy - pad][X*s + dx - pad][c]      (0 outside the image),
 // whose pixels are wide enough for the implicit-GEMM tile loads (ops/conv.py, S2dConvPlan).  T is a bit
-// container (bf16 as 16-bit, fp32 as 32-bit words); one block per (image, row of xs).
+// container (bf16 as 16-bit, fp32 as 32-bit words); one block per (image, row of xs), four channels per thread.
 // ------------------------------------------------------------------------------------------------
+constexpr int S2D_MAX_CS = 1024;
 template <typename T>
 __global__ void __launch_bounds__(256)
 space_to_depth_kernel(const T* __restrict__ x, T* __restrict__ xs, int H, int W, int C, int Hs, int Ws, int Cs,
                       int s, int pad) {
-  const int n = blockIdx.x / Hs, Y = blockIdx.x - n * Hs;
+  // channel of xs -> (dy, dx, offset dx*C + c) of the source, looked up instead of divided out per element
+  __shared__ unsigned tab[S2D_MAX_CS];
   const int sc = s * C, real = s * sc;
+  for (int ch = threadIdx.x; ch < Cs; ch += blockDim.x) {
+    unsigned e = 0xFFFFFFFFu;
+    if (ch < real) {
+      const int dy = ch / sc, r = ch - dy * sc;
+      e = (static_cast<unsigned>(dy) << 24) | (static_cast<unsigned>(r / C) << 16) | static_cast<unsigned>(r);
+    }
+    tab[ch] = e;
+  }
+  __syncthreads();
+  const int n = blockIdx.x / Hs, Y = blockIdx.x - n * Hs;
   const T* xn = x + static_cast<long long>(n) * H * W * C;
   T* row = xs + static_cast<long long>(blockIdx.x) * Ws * Cs;
-  for (int j = threadIdx.x; j < Ws * Cs; j += blockDim.x) {
-    const int X = j / Cs, ch = j - X * Cs;
-    T v = 0;
-    if (ch < real) {
-      const int dy = ch / sc, r = ch - dy * sc;       // r = dx*C + c: s*C consecutive input elements
-      const int yy = Y * s + dy - pad, x0 = X * s - pad;
-      const int xx = x0 + r / C;
-      if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = xn[(static_cast<long long>(yy) * W + x0) * C + r];
+  const int groups = Cs / 4;
+  for (int j = threadIdx.x; j < Ws * groups; j += blockDim.x) {
+    const int X = j / groups, ch0 = (j - X * groups) * 4;
+    const int x0 = X * s - pad, y0 = Y * s - pad;
+    T v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const unsigned e = tab[ch0 + q];
+      const int yy = y0 + static_cast<int>(e >> 24), xx = x0 + static_cast<int>((e >> 16) & 0xFFu);
+      v[q] = 0;
+      if (e != 0xFFFFFFFFu && yy >= 0 && yy < H && xx >= 0 && xx < W)
+        v[q] = xn[(static_cast<long long>(yy) * W + x0) * C + static_cast<int>(e & 0xFFFFu)];
     }
-    row[j] = v;
+    T* d = row + X * Cs + ch0;
+    if (sizeof(T) == 4) {
+      *reinterpret_cast<uint4*>(d) = make_uint4(v[0], v[1], v[2], v[3]);
+    } else {
+      *reinterpret_cast<uint2*>(d) = make_uint2(static_cast<unsigned>(v[0]) | (static_cast<unsigned>(v[1]) << 16),
+                                                static_cast<unsigned>(v[2]) | (static_cast<unsigned>(v[3]) << 16));
+    }
   }
 }
 
@@ -505,7 +552,8 @@ extern "C" int sg_dropout(const void* x, void* y, long long n, float pkeep, unsi
   if (n <= 0) return 0;
   SG_REQUIRE(pkeep > 0.f && pkeep <= 1.f, "sg_dropout: pkeep must be in (0,1]");
   DTYPE_SWITCH(is_bf16, T, {
-    dropout_kernel<T><<<ew_grid((n + 3) / 4, 256), 256, 0, s>>>((const T*)x, (T*)y, n, pkeep, seed, seed_dev);
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+    dropout_kernel<T><<<ew_grid((n + 3) / 4, 256), 256, 0, s>>>((const T*)x, (T*)y, n, pkeep, seed, seed_dev, vec);
   })
   SG_CHECK_LAUNCH("dropout");
   return 0;
@@ -735,7 +783,9 @@ extern "C" int sg_space_to_depth(const void* x, void* xs, int N, int H, int W, i
                                  int pad, int is_bf16, void* stream) {
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (N <= 0) return 0;
-  SG_REQUIRE(s_ > 0 && pad >= 0 && Cs >= s_ * s_ * C && Hs > 0 && Ws > 0, "sg_space_to_depth: bad geometry");
+  SG_REQUIRE(s_ > 0 && s_ < 256 && pad >= 0 && Cs >= s_ * s_ * C && Hs > 0 && Ws > 0, "sg_space_to_depth: bad geometry");
+  SG_REQUIRE(Cs % 4 == 0 && Cs <= S2D_MAX_CS && s_ * C < 65536 && ((uintptr_t)xs & 15) == 0,
+             "sg_space_to_depth: Cs must be a multiple of 4, at most %d, and xs 16-byte aligned", S2D_MAX_CS);
   const int grid = N * Hs;
   if (is_bf16)
     space_to_depth_kernel<unsigned short><<<grid, 256, 0, s>>>((const unsigned short*)x, (unsigned short*)xs, H, W, C, Hs, Ws, Cs, s_, pad);

@@ -129,7 +129,8 @@ __global__ void pool_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y
 
 // Vector forms: one block per (image, row), threads over (column, 16-byte channel vector); C % Vec<T>::N == 0.
 // Only 32-bit index arithmetic, and the window is a compile-time bound so that every load of a pixel is issued
-// before the first use (the loops above wait for each window element in turn: ~6x slower on AlexNet's pools).
+// before the first use (the loops above wait for each window element in turn: 5-13x slower on AlexNet's fp32 pools;
+// several rows per block were tried for the short bf16 rows and lost to the extra index arithmetic).
 //   forward : K = window size (2, 3) -> K*K predicated loads of x per output vector
 //   backward: MW = ceil(k / stride) = most windows per dimension that contain one input pixel (1, 2, 3)
 template <typename T, int K, bool MAX>
@@ -296,6 +297,25 @@ __global__ void lrn_bwd_kernel(const T* __restrict__ x, const float* __restrict_
 // raised to a power once (the loops above re-read x / dy / norm and call __powf for every window element).
 constexpr int LRN_TILE = 2048;
 
+// w[0..11] = s[e-4 .. e+7] of one pixel's channel row (c = channel of s[e], a multiple of 4); channels outside
+// [0, C) read as zero.  Window half-widths up to 4 (local size <= 9) are served from these three vectors.
+__device__ __forceinline__ void lrn_window(const float* s, int e, int c, int C, float (&w)[12]) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 lo = c >= 4 ? *reinterpret_cast<const float4*>(&s[e - 4]) : z;
+  const float4 mi = *reinterpret_cast<const float4*>(&s[e]);
+  const float4 hi = c + 4 < C ? *reinterpret_cast<const float4*>(&s[e + 4]) : z;
+  w[0] = lo.x; w[1] = lo.y; w[2] = lo.z; w[3] = lo.w;
+  w[4] = mi.x; w[5] = mi.y; w[6] = mi.z; w[7] = mi.w;
+  w[8] = hi.x; w[9] = hi.y; w[10] = hi.z; w[11] = hi.w;
+}
+__device__ __forceinline__ void store4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, const float (&v)[4]) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 lrn_fwd_tile_kernel(const T* __restrict__ x, T* __restrict__ y, float* __restrict__ norm, long long pixels, int C,
@@ -313,13 +333,23 @@ lrn_fwd_tile_kernel(const T* __restrict__ x, T* __restrict__ y, float* __restric
         *reinterpret_cast<float4*>(&sx[e + q]) = make_float4(xv[q], xv[q + 1], xv[q + 2], xv[q + 3]);
     }
     __syncthreads();
-    for (int e = threadIdx.x; e < ne; e += blockDim.x) {
-      const int c = e % C;
-      float sum = 0.f;
-      for (int cc = max(-half, -c); cc <= min(half, C - 1 - c); ++cc) sum += sx[e + cc] * sx[e + cc];
-      const float nm = knorm + salpha * sum;
-      norm[base + e] = nm;
-      y[base + e] = from_float<T>(sx[e] * __powf(nm, -beta));
+    for (int e = threadIdx.x * 4; e < ne; e += blockDim.x * 4) {
+      float w[12];
+      lrn_window(sx, e, e % C, C, w);
+#pragma unroll
+      for (int q = 0; q < 12; ++q) w[q] *= w[q];
+      float nm[4], o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float sum = w[4 + q];
+#pragma unroll
+        for (int d = 1; d <= 4; ++d)
+          if (d <= half) sum += w[4 + q - d] + w[4 + q + d];
+        nm[q] = knorm + salpha * sum;
+        o[q] = sx[e + q] * __powf(nm[q], -beta);
+      }
+      *reinterpret_cast<float4*>(norm + base + e) = make_float4(nm[0], nm[1], nm[2], nm[3]);
+      store4(y + base + e, o);
     }
     __syncthreads();
   }
@@ -356,11 +386,21 @@ lrn_bwd_tile_kernel(const T* __restrict__ x, const float* __restrict__ norm, con
       }
     }
     __syncthreads();
-    for (int e = threadIdx.x; e < ne; e += blockDim.x) {
-      const int c = e % C;
-      float sum = 0.f;
-      for (int cc = max(-half, -c); cc <= min(half, C - 1 - c); ++cc) sum += st[e + cc];
-      dx[base + e] = from_float<T>(sa[e] - coef * sx[e] * sum);
+    for (int e = threadIdx.x * 4; e < ne; e += blockDim.x * 4) {
+      float w[12], o[4];
+      lrn_window(st, e, e % C, C, w);
+      const float4 a4 = *reinterpret_cast<const float4*>(&sa[e]);
+      const float4 x4 = *reinterpret_cast<const float4*>(&sx[e]);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w}, xv[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float sum = w[4 + q];
+#pragma unroll
+        for (int d = 1; d <= 4; ++d)
+          if (d <= half) sum += w[4 + q - d] + w[4 + q + d];
+        o[q] = av[q] - coef * xv[q] * sum;
+      }
+      store4(dx + base + e, o);
     }
     __syncthreads();
   }
@@ -446,7 +486,7 @@ extern "C" int sg_lrn_fwd(const void* x, void* y, float* norm, long long pixels,
   if (total <= 0) return 0;
   SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_fwd: local size must be odd and positive");
   const int vn = is_bf16 ? 8 : 4;
-  if (C % vn == 0 && C <= LRN_TILE && ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)norm)) & 15) == 0) {
+  if (C % vn == 0 && C <= LRN_TILE && lsize <= 9 && ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)norm)) & 15) == 0) {
     const int ppt = LRN_TILE / C;
     const int grid = grid_for((pixels + ppt - 1) / ppt * 256, 256);
     if (is_bf16)
@@ -468,7 +508,7 @@ extern "C" int sg_lrn_bwd(const void* x, const float* norm, const void* dy, void
   if (total <= 0) return 0;
   SG_REQUIRE(lsize > 0 && (lsize & 1), "sg_lrn_bwd: local size must be odd and positive");
   const int vn = is_bf16 ? 8 : 4;
-  if (C % vn == 0 && C <= LRN_TILE && ((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)norm)) & 15) == 0) {
+  if (C % vn == 0 && C <= LRN_TILE && lsize <= 9 && ((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)norm)) & 15) == 0) {
     const int ppt = LRN_TILE / C;
     const int grid = grid_for((pixels + ppt - 1) / ppt * 256, 256);
     const float coef = 2.f * beta * alpha / lsize;

@@ -103,30 +103,70 @@ def push_case():
 
 
 def membound_cases():
+    """Achieved bandwidth of the memory-bound kernels, counted on the COMPULSORY traffic (every input read once, every
+    output written once), against the measured copy bandwidth."""
     peak = PEAKS.get("hbm_gbs", 6650.0)
-    n = 256 << 20
-    x = torch.randn(n, device=DEV).to(torch.bfloat16)
-    y = torch.empty_like(x)
-    for name, fn, nbytes in [
-        ("act_fwd stanh bf16", lambda: K.act_fwd(x, y, 2), 4 * n),
-        ("act_bwd stanh bf16", lambda: K.act_bwd(x, y, y, 2), 6 * n),
-        ("dropout bf16", lambda: K.dropout(x, y, 0.5, 1), 4 * n),
-    ]:
-        ms = timed(fn, iters=5, flush=False)
-        print(f"{name:22s} {ms*1e3:8.1f} us  {nbytes/ms/1e6:7.0f} GB/s  {nbytes/ms/1e6/peak*100:5.1f}% of copy bandwidth")
+
+    def line(name, ms, nbytes):
+        print(f"{name:34s} {ms*1e3:8.1f} us  {nbytes/ms/1e6:7.0f} GB/s  {nbytes/ms/1e6/peak*100:5.1f}% of copy bandwidth")
+
+    cl = lambda t: t.contiguous(memory_format=torch.channels_last)   # noqa: E731
+    for dt, dn in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
+        eb = 4 if dt == torch.float32 else 2
+        n = 128 << 20
+        x = torch.randn(n, device=DEV).to(dt)
+        y = torch.empty_like(x)
+        line(f"act_fwd stanh {dn}", timed(lambda: K.act_fwd(x, y, 2), iters=5, flush=False), 2 * eb * n)
+        line(f"act_bwd stanh {dn}", timed(lambda: K.act_bwd(x, y, y, 2), iters=5, flush=False), 3 * eb * n)
+        line(f"dropout {dn}", timed(lambda: K.dropout(x, y, 0.5, 1), iters=5, flush=False), 2 * eb * n)
+        del x, y
+        # AlexNet pool1 (after conv1): 256 x 96 x 55 x 55 -> 27 x 27, max 3/2
+        N, C, H, W, k, s = 256, 96, 55, 55, 3, 2
+        OH = OW = 27
+        xi = cl(torch.randn(N, C, H, W, device=DEV).to(dt))
+        yo = cl(torch.empty(N, C, OH, OW, device=DEV, dtype=dt))
+        dy = cl(torch.randn(N, C, OH, OW, device=DEV).to(dt))
+        dx = cl(torch.empty_like(xi))
+        nin, nout = xi.numel() * eb, yo.numel() * eb
+        line(f"pool_fwd max 3/2 96x55x55 {dn}",
+             timed(lambda: K.pool_fwd(xi, yo, N, H, W, C, OH, OW, k, s, 0, True), iters=5), nin + nout)
+        line(f"pool_bwd max 3/2 96x55x55 {dn}",
+             timed(lambda: K.pool_bwd(xi, yo, dy, dx, N, H, W, C, OH, OW, k, s, 0, True), iters=5), 2 * nin + 2 * nout)
+        del xi, dx
+        # AlexNet norm1: 256 x 96 x 27 x 27, local size 5
+        norm = torch.empty(N, OH, OW, C, device=DEV)
+        y2 = cl(torch.empty_like(yo))
+        px = N * OH * OW
+        yo.normal_()
+        line(f"lrn_fwd 5 96x27x27 {dn}", timed(lambda: K.lrn_fwd(yo, y2, norm, px, C, 5, 1e-4, 0.75, 1.0), iters=5),
+             2 * nout + 4 * yo.numel())
+        line(f"lrn_bwd 5 96x27x27 {dn}", timed(lambda: K.lrn_bwd(yo, norm, dy, y2, px, C, 5, 1e-4, 0.75), iters=5),
+             3 * nout + 4 * yo.numel())
+        # bias gradient of AlexNet conv1 / conv2: column sums of [pixels][F]
+        for F, pix in ((96, 256 * 55 * 55), (256, 256 * 27 * 27)):
+            m = torch.randn(pix, F, device=DEV).to(dt)
+            out = torch.zeros(F, device=DEV)
+            line(f"colsum [{pix}][{F}] {dn}", timed(lambda: K.colsum(m, pix, F, F, out), iters=5), pix * F * eb)
+            del m
+        # AlexNet input: space-to-depth of 256 x 227 x 227 x 3 (stride 4, 3x3 taps -> 57 x 57 x 48)
+        xin = torch.randn(256, 227, 227, 3, device=DEV).to(dt)
+        xs = torch.empty(256, 57, 57, 48, device=DEV, dtype=dt)
+        line(f"space_to_depth 227x227x3 /4 {dn}",
+             timed(lambda: K.space_to_depth(xin, xs, 256, 227, 227, 3, 57, 57, 48, 4, 0), iters=5),
+             (xin.numel() + xs.numel()) * eb)
+        del xin, xs
     rows, cols = 65536, 4096
     m = torch.randn(rows, cols, device=DEV).to(torch.bfloat16)
     out = torch.zeros(cols, device=DEV)
-    ms = timed(lambda: K.colsum(m, rows, cols, cols, out), iters=5, flush=False)
-    print(f"{'colsum bf16':22s} {ms*1e3:8.1f} us  {2*rows*cols/ms/1e6:7.0f} GB/s")
+    line("colsum [65536][4096] bf16", timed(lambda: K.colsum(m, rows, cols, cols, out), iters=5, flush=False), 2 * rows * cols)
+    del m
     nch = 200000
     w = torch.randn(nch * 1024, device=DEV); g = torch.randn_like(w); h = torch.zeros_like(w)
     w16 = torch.zeros(nch * 1024, device=DEV, dtype=torch.bfloat16)
     cp = torch.zeros(nch, dtype=torch.int32, device=DEV); one = torch.ones(1, device=DEV)
     ms = timed(lambda: K.update_arena(w, g, h, None, w16, cp, one, one, 0, nch, kind=0, lr=0.01, momentum=0.9),
                iters=5, flush=False)
-    nb = nch * 1024 * (4 * 2 + 4 + 4 * 2 + 2)
-    print(f"{'update_arena sgd+mom':22s} {ms*1e3:8.1f} us  {nb/ms/1e6:7.0f} GB/s  {nb/ms/1e6/peak*100:5.1f}% of copy bandwidth")
+    line("update_arena sgd+mom (+bf16 mirror)", ms, nch * 1024 * (4 * 2 + 4 + 4 * 2 + 2))
 
 
 if __name__ == "__main__":
