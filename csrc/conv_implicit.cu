@@ -20,6 +20,7 @@
 //
 // Warp roles, barriers, TMEM double buffering and the fused epilogue are those of gemm_tcgen05.cu.
 #include <cuda.h>
+#include <stdlib.h>
 #include <mutex>
 
 #include "../include/singa_b200.h"
@@ -49,6 +50,18 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* tma
       "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n),
+        "h"(static_cast<unsigned short>(off_w)), "h"(static_cast<unsigned short>(off_h))
+      : "memory");
+}
+
+// The same load issued by either CTA of a pair (cta_group::2): the bytes land in the issuing CTA's shared memory, the
+// transaction count goes to the LEADER's barrier (peer bit of the barrier address cleared).
+__device__ __forceinline__ void tma_load_im2col_4d_pair(uint32_t dst, const void* tmap, uint32_t bar, int c, int w, int h,
+                                                        int n, int off_w, int off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar & kPeerBitMask), "r"(c), "r"(w), "r"(h), "r"(n),
         "h"(static_cast<unsigned short>(off_w)), "h"(static_cast<unsigned short>(off_h))
       : "memory");
 }
@@ -287,6 +300,170 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------------
+// MODE_ROWS on CTA pairs (cta_group::2): one 256-pixel x BN tile per pair.  Each CTA builds the patch tile of ITS 128
+// pixels and stages HALF of the filter tile, so a k-block costs 16 KB + BN*64 B per CTA instead of 16 KB + BN*128 B —
+// these kernels sit on the L2 -> shared-memory limit (ncu, AlexNet conv2 forward: 11.7 TB/s, tensor pipe 51 %), and
+// the filter tile is two thirds of the traffic at BN = 256.  128-byte channel chunks only (one im2col box per k-block,
+// the GEMM's K-major SW128 tile); barrier protocol as in gemm_tcgen05_pair_kernel.
+// ------------------------------------------------------------------------------------------------
+template <int EB, int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const GemmParams p, const ConvParams cp) {
+  using Cfg = PairCfg<BN>;
+  using E = Elem<EB>;
+  constexpr int BK = E::BK;
+  constexpr int UMMA_K = E::UMMA_K;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int B_HALF_BYTES = Cfg::B_HALF_BYTES;
+  constexpr int BNH = BN / 2;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA0 = smem_base;
+  const uint32_t sB0 = smem_base + STAGES * A_STAGE_BYTES;
+  const uint32_t bar0 = smem_base + STAGES * Cfg::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar0 + 8u * (2 * STAGES + 4);
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair_id = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const int m_tiles = (p.M + 2 * BM - 1) / (2 * BM);
+  const int n_tiles = (p.N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 2);     // leader's own arrive.expect_tx + the peer's remote arrive
+      mbar_init(empty_bar(s), 1);    // multicast commit from the leader's MMA warp
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 2 * EPI_WARPS);
+    }
+    fence_mbar_init();
+  }
+  cluster_sync_all();
+  if (warp == 1) {
+    tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (both CTAs)
+    if (lane == 0) {
+      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+      uint32_t stage = 0, phase = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+        const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 pixels
+        const int n0 = (tile / m_tiles) * BN + static_cast<int>(rank) * BNH;        // this CTA's half of the filters
+        const int img = m0 / cp.OHW;
+        const int rem = m0 - img * cp.OHW;
+        const int oy = rem / cp.OW;
+        const int base_h = oy * cp.stride - cp.pad_lo;
+        const int base_w = (rem - oy * cp.OW) * cp.stride - cp.pad_lo;
+        int rch = 0, rkx = 0, rky = 0;       // k-block kb = box kb = (tap, channel chunk), walked in order
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t fb = full_bar(stage);
+          if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
+          else mbar_arrive_remote(fb, 0);
+          const bool live = kb < cp.nsub;
+          tma_load_im2col_4d_pair(sA0 + stage * A_STAGE_BYTES, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w,
+                                  base_h, img, live ? rkx : 0, live ? rky : 0);
+          tma_load_2d_pair(sB0 + stage * B_HALF_BYTES, &tma_b, fb, kb * BK, n0);
+          if (++rch == cp.nchunk) { rch = 0; if (++rkx == cp.ksize) { rkx = 0; ++rky; } }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (leader) {
+      constexpr uint32_t idesc = make_idesc(EB == 2 ? 1u : 2u, 2 * BM, BN, 0, 0);
+      uint32_t stage = 0, phase = 0;
+      int it = 0;
+      for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+            const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t adesc = make_smem_desc_sw128(sa + 32u * k, 16, 1024);
+              const uint64_t bdesc = make_smem_desc_sw128(sb + 32u * k, 16, 1024);
+              umma_pair<EB>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit_pair(empty_bar(stage), 3);
+            if (kb == num_kb - 1) umma_commit_pair(tfull_bar(acc), 3);
+          }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..9, both CTAs)
+    const int quad = warp & 3;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bar0 - smem_u32(smem_raw)) + 256) + (warp - 2) * EPI_WARP_FLOATS;
+    const bool fast_ok = epilogue_fast_ok(p);
+    int it = 0;
+    for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+      const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;
+      const int n0 = (tile / m_tiles) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const long long row0 = m0 + quad * 32;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = ((warp - 2) >> 2) * 32; c < BN; c += 64) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c, r);
+        tmem_ld_wait();
+        if (c + 64 >= BN) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(tempty_bar(acc), 0);   // the leader's MMA warp waits on ITS barrier
+        }
+        epilogue_chunk(p, r, row0, lane, n0 + c, fast_ok, stg);
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Host side
 // ------------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -376,6 +553,28 @@ static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
+template <int EB, int BN>
+static int launch_conv_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, const ConvParams& cp,
+                            cudaStream_t stream) {
+  using Cfg = PairCfg<BN>;
+  auto kern = conv_tcgen05_pair_kernel<EB, BN>;
+  static thread_local int attr_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    if (check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES),
+                   "cudaFuncSetAttribute(conv pair smem)"))
+      return 1;
+    attr_dev = dev;
+  }
+  const long long tiles = static_cast<long long>((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
+  const int max_pairs = num_sms() / 2;
+  const int pairs = tiles < max_pairs ? static_cast<int>(tiles) : max_pairs;
+  kern<<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, cp);
+  SG_CHECK_LAUNCH("conv_tcgen05_pair");
+  return 0;
+}
+
 template <int EB, int MODE>
 static int dispatch_conv(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
                          const ConvParams& cp, cudaStream_t s) {
@@ -436,7 +635,14 @@ extern "C" int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, con
     return rc;
   int bn = ep->tile_bn ? ep->tile_bn : (ncols > 128 ? 256 : (ncols > 64 ? 128 : 64));
   SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_conv_rows: tile_bn must be 0, 64, 128 or 256");
-  if (int rc = make_tmap_2d(&tb, eb, filt, Kp, ncols, ldf, BK, bn, false)) return rc;
+  // CTA pairs: 128-byte chunks (one box per k-block), at least 128 filter columns per tile, and enough 256-pixel
+  // tiles for every pair of SMs; ep->tile_pair 1 / 2 and SINGA_B200_CONV_PAIR=0 / 1 force the choice
+  static const int env_pair = [] { const char* e = getenv("SINGA_B200_CONV_PAIR"); return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0); }();
+  bool pair = R == 128 && bn >= 128 && (P + 2 * BM - 1) / (2 * BM) * ((ncols + bn - 1) / bn) >= num_sms() / 2;
+  if (env_pair >= 0) pair = pair && env_pair == 1;
+  if (ep->tile_pair == 1) pair = false;
+  if (ep->tile_pair == 2) pair = R == 128 && bn >= 128;
+  if (int rc = make_tmap_2d(&tb, eb, filt, Kp, ncols, ldf, BK, pair ? bn / 2 : bn, false)) return rc;
   GemmParams p;
   fill_epilogue(p, ep);
   p.M = static_cast<int>(P); p.N = ncols; p.K = static_cast<int>(Kp);
@@ -450,6 +656,10 @@ extern "C" int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, con
   cp.a_sbo = 8u * R;                       // eight rows of a box
   cp.a_lbo = R == 16 ? BM * 16u : 16u;     // no swizzle: the second 16-byte half of an MMA's K lives in the next box
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (pair) {
+    if (eb == 2) return bn == 256 ? launch_conv_pair<2, 256>(ta, tb, p, cp, s) : launch_conv_pair<2, 128>(ta, tb, p, cp, s);
+    return bn == 256 ? launch_conv_pair<4, 256>(ta, tb, p, cp, s) : launch_conv_pair<4, 128>(ta, tb, p, cp, s);
+  }
   if (eb == 2) return dispatch_conv<2, MODE_ROWS>(bn, ta, tb, p, cp, s);
   return dispatch_conv<4, MODE_ROWS>(bn, ta, tb, p, cp, s);
 }

@@ -42,6 +42,15 @@ template <int BN> struct GemmCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 16 * 1024 /*epilogue staging, EPI_SMEM_BYTES*/;
 };
 
+// CTA pairs (cta_group::2): 256 x BN tiles, each CTA stages its own 128 rows of A and half of B.
+template <int BN> struct PairCfg {
+  static constexpr int B_HALF_BYTES = (BN / 2) * 128;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_HALF_BYTES;       // per CTA
+  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + 16 * 1024 /*epilogue staging*/;
+};
+
 // Kept at 96 bytes: with the two 128-byte tensor maps the kernel's parameter block stays under 368 bytes.  Growing it
 // to ~410 bytes cost ~1.3 us on EVERY launch (measured: +0.026 ms on the 18-GEMM MNIST step), so flags are bytes
 // and leading dimensions are 32-bit.

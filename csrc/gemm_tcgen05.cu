@@ -234,14 +234,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 //              warps 2..9 = epilogue of the CTA's own 128 accumulator rows (its own TMEM), arriving on the
 //              leader's tmem-empty barrier
 // ------------------------------------------------------------------------------------------------
-template <int BN> struct PairCfg {
-  static constexpr int B_HALF_BYTES = (BN / 2) * 128;
-  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_HALF_BYTES;       // per CTA
-  static constexpr int STAGES = (SMEM_BUDGET / STAGE_BYTES) > 8 ? 8 : (SMEM_BUDGET / STAGE_BYTES);
-  static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256 + 16 * 1024 /*epilogue staging*/;
-};
-
 template <int EB, int BN, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,

@@ -106,11 +106,11 @@ class ConvPlan:
         return self.dy_pad[which]
 
     # -- the three GEMMs -----------------------------------------------------------------------------------
-    def forward(self, x, y2d, bias=None, act=ACT_NONE, wait=None):
+    def forward(self, x, y2d, bias=None, act=ACT_NONE, wait=None, tile=None):
         """y2d [P][F] (a view of the channels-last output) = act(conv(x) + bias)."""
         self._x_raw = x
         self._x_saved = self._x_operand(x)
-        K.conv_rows(self._x_saved, self.g_fwd, self.wf, self.F, y2d, bias=bias, act=act, wait=wait)
+        K.conv_rows(self._x_saved, self.g_fwd, self.wf, self.F, y2d, bias=bias, act=act, wait=wait, tile=tile)
 
     def wgrad(self, dy, dw, accumulate=False):
         """dw [F][C*k*k] (fp32, reference layout) (+)= dY^T patches(x saved by forward)."""
@@ -125,11 +125,11 @@ class ConvPlan:
         K.gemm(dy2d, self.col[:, :kc], self.F, kc, self.P, a_mn=True, b_mn=True, out32=dw, accumulate=accumulate,
                perm=(self.C, self.kk) if self.kk > 1 and self.C > 1 else None)
 
-    def dgrad(self, dy, dx2d, grad_act=ACT_NONE, aux2d=None):
+    def dgrad(self, dy, dx2d, grad_act=ACT_NONE, aux2d=None, tile=None):
         """dx2d [N*H*W][C] = conv^T(dY) (times act'(aux) when the source activation's backward is fused here)."""
         dyo = self._dy_operand(dy, 1)
         if self.dgrad_implicit:
-            K.conv_rows(dyo, self.g_dgrad, self.wd, self.C, dx2d, grad_act=grad_act, aux=aux2d)
+            K.conv_rows(dyo, self.g_dgrad, self.wd, self.C, dx2d, grad_act=grad_act, aux=aux2d, tile=tile)
             return
         kc = self.kk * self.C
         dy2d = _mat(dyo, self.P, self.F, self.ldf)

@@ -185,9 +185,13 @@ def _epilogue(out, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None, wait=No
     return ep
 
 
-def conv_rows(src, geom, filt, ncols, out2d, *, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None, wait=None):
-    """out2d[pixel][n] = epilogue(sum_k patch(src; pixel, k) * filt[n][k]) — forward and stride-1 data gradient."""
+def conv_rows(src, geom, filt, ncols, out2d, *, bias=None, act=ACT_NONE, grad_act=ACT_NONE, aux=None, wait=None,
+              tile=None):
+    """out2d[pixel][n] = epilogue(sum_k patch(src; pixel, k) * filt[n][k]) — forward and stride-1 data gradient.
+    ``tile`` = (bn, pair) forces the tile width (0 = library's choice) and single-CTA (1) / CTA-pair (2) tiles."""
     ep = _epilogue(out2d, bias, act, grad_act, aux, wait)
+    if tile is not None:
+        ep.tile_bn, ep.tile_pair = tile
     assert filt.dtype == src.dtype and filt.stride(-1) == 1
     rc = _lib().sg_conv_rows(0 if _bf(src) else 1, src.data_ptr(), ctypes.byref(geom), filt.data_ptr(), filt.stride(0),
                              ncols, ctypes.byref(ep), native.stream_ptr())

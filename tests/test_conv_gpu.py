@@ -156,3 +156,43 @@ def test_conv_space_to_depth_plan(case, dtype):
         torch.testing.assert_close(dw2, dw_ref + 1.0, **tol)
     finally:
         torch.backends.cudnn.allow_tf32 = prev
+
+
+PAIR_CASES = [
+    # N, C, H, W, F, k, stride, pad — 128-byte channel chunks in both precisions
+    (5, 64, 13, 13, 256, 3, 1, 1),     # 845 pixels: 4 pair tiles, the last one with an all-padding second CTA
+    (3, 128, 12, 10, 136, 3, 1, 1),    # F = 136: ragged filter tile, half of it beyond the matrix for the second CTA
+    (2, 64, 17, 17, 128, 5, 1, 2),     # 5x5
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_conv_cta_pair_tiles(case, dtype):
+    """Forward and data gradient on CTA-pair (cta_group::2) tiles, forced, against the fp32 convolution."""
+    N, C, H, W, F, k, s, p = case
+    torch.manual_seed(sum(case))
+    x = _nhwc((torch.randn(N, C, H, W, device=DEV) * 0.5).to(dtype))
+    w32 = torch.randn(F, C * k * k, device=DEV) * 0.1
+    b32 = torch.randn(F, device=DEV)
+    plan = ConvPlan(N, C, H, W, F, k, s, p, dtype, DEV, need_dgrad=True)
+    plan.pack(w32)
+    OH, OW = plan.OH, plan.OW
+    xr, wr = x.float(), w32.to(dtype).float().view(F, C, k, k)
+    prev = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        ref = torch.relu(F_.conv2d(xr, wr, b32, stride=s, padding=p))
+        dy = _nhwc((torch.randn(N, F, OH, OW, device=DEV) * 0.5).to(dtype))
+        dx_ref = torch.nn.grad.conv2d_input(xr.shape, wr, dy.float(), stride=s, padding=p)
+        for bn in (128, 256):
+            y = _nhwc(torch.full((N, F, OH, OW), float("nan"), device=DEV, dtype=dtype))
+            plan.forward(x, y.permute(0, 2, 3, 1).reshape(plan.P, F), bias=b32, act=G.ACT_RELU, tile=(bn, 2))
+            torch.cuda.synchronize()
+            torch.testing.assert_close(y.float(), ref, **_tols(dtype, C * k * k))
+            dx = _nhwc(torch.full((N, C, H, W), float("nan"), device=DEV, dtype=dtype))
+            plan.dgrad(dy, dx.permute(0, 2, 3, 1).reshape(N * H * W, C), tile=(bn, 2))
+            torch.cuda.synchronize()
+            torch.testing.assert_close(dx.float(), dx_ref, **_tols(dtype, F * k * k))
+    finally:
+        torch.backends.cudnn.allow_tf32 = prev
