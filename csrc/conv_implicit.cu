@@ -126,8 +126,10 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+    // the whole warp walks the loop (uniform registers for every coordinate), one elected lane issues
+    {
+      if (lane == 0 && p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+      __syncwarp();
       uint32_t stage = 0, phase = 0;
       const int conv_oh = cp.OHW / cp.OW;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
@@ -182,7 +184,8 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t fb = full_bar(stage);
-          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
+          const bool issuer = elect_one();
+          if (issuer) mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
           const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
           if (MODE == MODE_ROWS) {
@@ -191,27 +194,31 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
             const uint32_t box_bytes = BM * cp.R;
             for (int i = 0; i < per_kb; ++i, ++rq) {
               const bool live = rq < cp.nsub;
-              tma_load_im2col_4d(sa + i * box_bytes, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w, base_h,
-                                 img, live ? rkx : 0, live ? rky : 0);
+              if (issuer)
+                tma_load_im2col_4d(sa + i * box_bytes, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w, base_h,
+                                   img, live ? rkx : 0, live ? rky : 0);
               if (++rch == cp.nchunk) { rch = 0; if (++rkx == cp.ksize) { rkx = 0; ++rky; } }
             }
-            tma_load_2d(sb, &tma_b, fb, kb * BK, n0);
+            if (issuer) tma_load_2d(sb, &tma_b, fb, kb * BK, n0);
           } else {
             // A = dY, MN-major 2-D boxes; B: one im2col box [BK pixels][128 bytes] per (tap, channel chunk)
             const int k0 = kb * BK;
-#pragma unroll
-            for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
             const int bh = poy * cp.stride - cp.pad_lo;
             const int bw = pox * cp.stride - cp.pad_lo;
+            if (issuer) {
 #pragma unroll
-            for (int b = 0; b < NB; ++b)
-              tma_load_im2col_4d(sb + b * MN_BOX_BYTES, &tma_b, fb, box_c[b], bw, bh, pimg, box_kx[b], box_ky[b]);
+              for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
+#pragma unroll
+              for (int b = 0; b < NB; ++b)
+                tma_load_im2col_4d(sb + b * MN_BOX_BYTES, &tma_b, fb, box_c[b], bw, bh, pimg, box_kx[b], box_ky[b]);
+            }
             pox += BK;
             while (pox >= cp.OW) {
               pox -= cp.OW;
               if (++poy == conv_oh) { poy = 0; ++pimg; }
             }
           }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -222,6 +229,15 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     constexpr uint32_t MN_KSTEP = UMMA_K * 128;
     constexpr uint32_t MN_LAYOUT = EB == 4 ? kLayoutSw128Base32 : kLayoutSw128;
     constexpr uint32_t MN_SBO = EB == 4 ? 512 : 1024;
+    // MODE_ROWS: descriptor of the A boxes without the address, and the 16-byte offset of each MMA's 32 bytes of K
+    // (inside one box when R >= 32, two 16-byte boxes LBO apart when R == 16) — once, not per k-block
+    const uint64_t a_tmpl = make_smem_desc(0, cp.a_lbo, cp.a_sbo, cp.a_layout);
+    uint32_t a_off16[BK / UMMA_K];
+#pragma unroll
+    for (int k = 0; k < BK / UMMA_K; ++k) {
+      const uint32_t byte = 32u * k;
+      a_off16[k] = (cp.R >= 32 ? (byte / cp.R) * (BM * cp.R) + (byte % cp.R) : (2u * k) * (BM * 16u)) >> 4;
+    }
     uint32_t stage = 0, phase = 0;
     int it = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
@@ -235,17 +251,14 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
-          const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
+        const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+        const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             uint64_t adesc, bdesc;
             if (MODE == MODE_ROWS) {
-              // 32 bytes of K per MMA: inside one box when R >= 32, two 16-byte boxes (LBO apart) when R == 16
-              const uint32_t byte = 32u * k;
-              const uint32_t a_off = cp.R >= 32 ? (byte / cp.R) * (BM * cp.R) + (byte % cp.R) : (2u * k) * (BM * 16u);
-              adesc = make_smem_desc(sa + a_off, cp.a_lbo, cp.a_sbo, cp.a_layout);
+              adesc = a_tmpl + ((sa >> 4) + a_off16[k]);       // the address field (14 bits) cannot carry: smem < 256 KB
               bdesc = make_smem_desc_sw128(sb + 32u * k, 16, 1024);
             } else {
               adesc = make_smem_desc(sa + k * MN_KSTEP, MN_BOX_BYTES, MN_SBO, MN_LAYOUT);
@@ -300,13 +313,16 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// MODE_ROWS on CTA pairs (cta_group::2): one 256-pixel x BN tile per pair.  Each CTA builds the patch tile of ITS 128
-// pixels and stages HALF of the filter tile, so a k-block costs 16 KB + BN*64 B per CTA instead of 16 KB + BN*128 B —
-// these kernels sit on the L2 -> shared-memory limit (ncu, AlexNet conv2 forward: 11.7 TB/s, tensor pipe 51 %), and
-// the filter tile is two thirds of the traffic at BN = 256.  128-byte channel chunks only (one im2col box per k-block,
-// the GEMM's K-major SW128 tile); barrier protocol as in gemm_tcgen05_pair_kernel.
+// Both modes on CTA pairs (cta_group::2): one 256 x BN tile per pair.  Each CTA stages the A tile of ITS 128 rows and
+// HALF of the B tile, so a k-block costs 16 KB + BN*64 B per CTA instead of 16 KB + BN*128 B — these kernels sit on
+// the L2 -> shared-memory limit (ncu, AlexNet conv2 forward: 11.7 TB/s, tensor pipe 51 %) and the B tile is two
+// thirds of the traffic at BN = 256.
+//   MODE_ROWS: rows = pixels; this CTA's 128 pixels of patches + half of the filter rows.
+//   MODE_COLS: rows = filters (dY^T); this CTA's 128 filters + half of the patch columns; split-K over the pixels.
+// Barrier protocol as in gemm_tcgen05_pair_kernel (both CTAs' loads count on the leader's full barrier, the leader's
+// MMA warp commits to both CTAs' empty / accumulator-full barriers).
 // ------------------------------------------------------------------------------------------------
-template <int EB, int BN>
+template <int EB, int BN, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          const GemmParams p, const ConvParams cp) {
@@ -314,6 +330,8 @@ conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   using E = Elem<EB>;
   constexpr int BK = E::BK;
   constexpr int UMMA_K = E::UMMA_K;
+  constexpr int MN_BOX = E::MN_BOX;
+  constexpr int MN_BOX_BYTES = E::MN_BOX_BYTES;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int B_HALF_BYTES = Cfg::B_HALF_BYTES;
   constexpr int BNH = BN / 2;
@@ -341,6 +359,7 @@ conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   const int n_tiles = (p.N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int num_kb = (p.K + BK - 1) / BK;
+  const int num_items = num_tiles * p.split_k;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -367,28 +386,96 @@ conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
-    if (lane == 0) {
-      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+    // the whole warp walks the loop (uniform registers for every coordinate), one elected lane issues
+    {
+      if (lane == 0 && p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+      __syncwarp();
       uint32_t stage = 0, phase = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
-        const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 pixels
-        const int n0 = (tile / m_tiles) * BN + static_cast<int>(rank) * BNH;        // this CTA's half of the filters
-        const int img = m0 / cp.OHW;
-        const int rem = m0 - img * cp.OHW;
-        const int oy = rem / cp.OW;
-        const int base_h = oy * cp.stride - cp.pad_lo;
-        const int base_w = (rem - oy * cp.OW) * cp.stride - cp.pad_lo;
-        int rch = 0, rkx = 0, rky = 0;       // k-block kb = box kb = (tap, channel chunk), walked in order
-        for (int kb = 0; kb < num_kb; ++kb) {
+      const int conv_oh = cp.OHW / cp.OW;
+      for (int item = pair_id; item < num_items; item += num_pairs) {
+        const int slice = p.split_k == 1 ? 0 : item / num_tiles;
+        const int tile = item - slice * num_tiles;
+        const int kb_lo = slice * p.kb_per_split;
+        const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
+        const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 rows
+        const int n0 = (tile / m_tiles) * BN + static_cast<int>(rank) * BNH;        // this CTA's half of B
+        // MODE_ROWS: first pixel of the CTA's rows and a cursor over the (tap, channel chunk) boxes of K
+        int img = 0, base_w = 0, base_h = 0, rq = 0, rch = 0, rkx = 0, rky = 0;
+        // MODE_COLS: (channel, tap) of each of the CTA's boxes and a pixel cursor advanced by BK per k-block
+        constexpr int NB = BNH / MN_BOX > 0 ? BNH / MN_BOX : 1;
+        int box_c[NB];
+        unsigned short box_kx[NB], box_ky[NB];
+        int pimg = 0, poy = 0, pox = 0;
+        if (MODE == MODE_ROWS) {
+          rq = kb_lo * (128 / cp.R);
+          const int tap = rq / cp.nchunk;
+          rch = rq - tap * cp.nchunk;
+          rky = tap / cp.ksize;
+          rkx = tap - rky * cp.ksize;
+          img = m0 / cp.OHW;
+          const int rem = m0 - img * cp.OHW;
+          const int oy = rem / cp.OW;
+          base_h = oy * cp.stride - cp.pad_lo;
+          base_w = (rem - oy * cp.OW) * cp.stride - cp.pad_lo;
+        } else {
+          int q = n0 / MN_BOX;
+          int tap = q / cp.nchunk;
+          int ch = q - tap * cp.nchunk;
+          int ky = tap / cp.ksize;
+          int kx = tap - ky * cp.ksize;
+#pragma unroll
+          for (int b = 0; b < NB; ++b, ++q) {
+            const bool live = q < cp.nsub;
+            box_c[b] = live ? ch * cp.chunk_elems : cp.c_oob;
+            box_kx[b] = static_cast<unsigned short>(live ? kx : 0);
+            box_ky[b] = static_cast<unsigned short>(live ? ky : 0);
+            if (++ch == cp.nchunk) { ch = 0; if (++kx == cp.ksize) { kx = 0; ++ky; } }
+          }
+          const int k0 = kb_lo * BK;
+          pimg = k0 / cp.OHW;
+          const int rem = k0 - pimg * cp.OHW;
+          poy = rem / cp.OW;
+          pox = rem - poy * cp.OW;
+        }
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t fb = full_bar(stage);
-          if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
-          else mbar_arrive_remote(fb, 0);
-          const bool live = kb < cp.nsub;
-          tma_load_im2col_4d_pair(sA0 + stage * A_STAGE_BYTES, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w,
-                                  base_h, img, live ? rkx : 0, live ? rky : 0);
-          tma_load_2d_pair(sB0 + stage * B_HALF_BYTES, &tma_b, fb, kb * BK, n0);
-          if (++rch == cp.nchunk) { rch = 0; if (++rkx == cp.ksize) { rkx = 0; ++rky; } }
+          const bool issuer = elect_one();
+          if (issuer) {
+            if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
+            else mbar_arrive_remote(fb, 0);
+          }
+          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+          const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          if (MODE == MODE_ROWS) {
+            const int per_kb = 128 / cp.R;
+            const uint32_t box_bytes = BM * cp.R;
+            for (int i = 0; i < per_kb; ++i, ++rq) {
+              const bool live = rq < cp.nsub;
+              if (issuer)
+                tma_load_im2col_4d_pair(sa + i * box_bytes, &tma_a, fb, live ? rch * cp.chunk_elems : cp.c_oob, base_w,
+                                        base_h, img, live ? rkx : 0, live ? rky : 0);
+              if (++rch == cp.nchunk) { rch = 0; if (++rkx == cp.ksize) { rkx = 0; ++rky; } }
+            }
+            if (issuer) tma_load_2d_pair(sb, &tma_b, fb, kb * BK, n0);
+          } else {
+            const int k0 = kb * BK;
+            const int bh = poy * cp.stride - cp.pad_lo;
+            const int bw = pox * cp.stride - cp.pad_lo;
+            if (issuer) {
+#pragma unroll
+              for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d_pair(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
+#pragma unroll
+              for (int b = 0; b < NB; ++b)
+                tma_load_im2col_4d_pair(sb + b * MN_BOX_BYTES, &tma_b, fb, box_c[b], bw, bh, pimg, box_kx[b], box_ky[b]);
+            }
+            pox += BK;
+            while (pox >= cp.OW) {
+              pox -= cp.OW;
+              if (++poy == conv_oh) { poy = 0; ++pimg; }
+            }
+          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -396,29 +483,47 @@ conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
     if (leader) {
-      constexpr uint32_t idesc = make_idesc(EB == 2 ? 1u : 2u, 2 * BM, BN, 0, 0);
+      constexpr uint32_t idesc = make_idesc(EB == 2 ? 1u : 2u, 2 * BM, BN, MODE == MODE_COLS ? 1 : 0, MODE == MODE_COLS ? 1 : 0);
+      constexpr uint32_t MN_KSTEP = UMMA_K * 128;
+      constexpr uint32_t MN_LAYOUT = EB == 4 ? kLayoutSw128Base32 : kLayoutSw128;
+      constexpr uint32_t MN_SBO = EB == 4 ? 512 : 1024;
+      const uint64_t a_tmpl = make_smem_desc(0, cp.a_lbo, cp.a_sbo, cp.a_layout);
+      uint32_t a_off16[BK / UMMA_K];
+#pragma unroll
+      for (int k = 0; k < BK / UMMA_K; ++k) {
+        const uint32_t byte = 32u * k;
+        a_off16[k] = (cp.R >= 32 ? (byte / cp.R) * (BM * cp.R) + (byte % cp.R) : (2u * k) * (BM * 16u)) >> 4;
+      }
       uint32_t stage = 0, phase = 0;
       int it = 0;
-      for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+      for (int item = pair_id; item < num_items; item += num_pairs, ++it) {
+        const int kb_lo = p.split_k == 1 ? 0 : (item / num_tiles) * p.kb_per_split;
+        const int kb_hi = min(num_kb, kb_lo + p.kb_per_split);
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
-            const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+          const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
-              const uint64_t adesc = make_smem_desc_sw128(sa + 32u * k, 16, 1024);
-              const uint64_t bdesc = make_smem_desc_sw128(sb + 32u * k, 16, 1024);
-              umma_pair<EB>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              uint64_t adesc, bdesc;
+              if (MODE == MODE_ROWS) {
+                adesc = a_tmpl + ((sa >> 4) + a_off16[k]);
+                bdesc = make_smem_desc_sw128(sb + 32u * k, 16, 1024);
+              } else {
+                adesc = make_smem_desc(sa + k * MN_KSTEP, MN_BOX_BYTES, MN_SBO, MN_LAYOUT);
+                bdesc = make_smem_desc(sb + k * MN_KSTEP, MN_BOX_BYTES, MN_SBO, MN_LAYOUT);
+              }
+              umma_pair<EB>(tmem_d, adesc, bdesc, idesc, (kb > kb_lo || k != 0) ? 1u : 0u);
             }
             umma_commit_pair(empty_bar(stage), 3);
-            if (kb == num_kb - 1) umma_commit_pair(tfull_bar(acc), 3);
+            if (kb == kb_hi - 1) umma_commit_pair(tfull_bar(acc), 3);
           }
           __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -431,7 +536,8 @@ conv_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     float* stg = reinterpret_cast<float*>(smem_raw + (bar0 - smem_u32(smem_raw)) + 256) + (warp - 2) * EPI_WARP_FLOATS;
     const bool fast_ok = epilogue_fast_ok(p);
     int it = 0;
-    for (int tile = pair_id; tile < num_tiles; tile += num_pairs, ++it) {
+    for (int item = pair_id; item < num_items; item += num_pairs, ++it) {
+      const int tile = p.split_k == 1 ? item : item % num_tiles;
       const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;
       const int n0 = (tile / m_tiles) * BN;
       const int acc = it & 1;
@@ -553,11 +659,11 @@ static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
-template <int EB, int BN>
+template <int EB, int BN, int MODE>
 static int launch_conv_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, const ConvParams& cp,
                             cudaStream_t stream) {
   using Cfg = PairCfg<BN>;
-  auto kern = conv_tcgen05_pair_kernel<EB, BN>;
+  auto kern = conv_tcgen05_pair_kernel<EB, BN, MODE>;
   static thread_local int attr_dev = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -567,7 +673,7 @@ static int launch_conv_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
       return 1;
     attr_dev = dev;
   }
-  const long long tiles = static_cast<long long>((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
+  const long long tiles = static_cast<long long>((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN) * p.split_k;
   const int max_pairs = num_sms() / 2;
   const int pairs = tiles < max_pairs ? static_cast<int>(tiles) : max_pairs;
   kern<<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, cp);
@@ -635,13 +741,12 @@ extern "C" int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, con
     return rc;
   int bn = ep->tile_bn ? ep->tile_bn : (ncols > 128 ? 256 : (ncols > 64 ? 128 : 64));
   SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_conv_rows: tile_bn must be 0, 64, 128 or 256");
-  // CTA pairs: 128-byte chunks (one box per k-block), at least 128 filter columns per tile, and enough 256-pixel
-  // tiles for every pair of SMs; ep->tile_pair 1 / 2 and SINGA_B200_CONV_PAIR=0 / 1 force the choice
+  // CTA pairs: at least 128 filter columns per tile and enough 256-pixel tiles for every pair of SMs; ep->tile_pair 1 / 2 and SINGA_B200_CONV_PAIR=0 / 1 force the choice
   static const int env_pair = [] { const char* e = getenv("SINGA_B200_CONV_PAIR"); return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0); }();
-  bool pair = R == 128 && bn >= 128 && (P + 2 * BM - 1) / (2 * BM) * ((ncols + bn - 1) / bn) >= num_sms() / 2;
+  bool pair = R >= 32 && bn >= 128 && (P + 2 * BM - 1) / (2 * BM) * ((ncols + bn - 1) / bn) >= num_sms() / 2;
   if (env_pair >= 0) pair = pair && env_pair == 1;
   if (ep->tile_pair == 1) pair = false;
-  if (ep->tile_pair == 2) pair = R == 128 && bn >= 128;
+  if (ep->tile_pair == 2) pair = bn >= 128;
   if (int rc = make_tmap_2d(&tb, eb, filt, Kp, ncols, ldf, BK, pair ? bn / 2 : bn, false)) return rc;
   GemmParams p;
   fill_epilogue(p, ep);
@@ -657,8 +762,9 @@ extern "C" int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, con
   cp.a_lbo = R == 16 ? BM * 16u : 16u;     // no swizzle: the second 16-byte half of an MMA's K lives in the next box
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (pair) {
-    if (eb == 2) return bn == 256 ? launch_conv_pair<2, 256>(ta, tb, p, cp, s) : launch_conv_pair<2, 128>(ta, tb, p, cp, s);
-    return bn == 256 ? launch_conv_pair<4, 256>(ta, tb, p, cp, s) : launch_conv_pair<4, 128>(ta, tb, p, cp, s);
+    if (eb == 2)
+      return bn == 256 ? launch_conv_pair<2, 256, MODE_ROWS>(ta, tb, p, cp, s) : launch_conv_pair<2, 128, MODE_ROWS>(ta, tb, p, cp, s);
+    return bn == 256 ? launch_conv_pair<4, 256, MODE_ROWS>(ta, tb, p, cp, s) : launch_conv_pair<4, 128, MODE_ROWS>(ta, tb, p, cp, s);
   }
   if (eb == 2) return dispatch_conv<2, MODE_ROWS>(bn, ta, tb, p, cp, s);
   return dispatch_conv<4, MODE_ROWS>(bn, ta, tb, p, cp, s);
@@ -690,8 +796,11 @@ extern "C" int sg_conv_wgrad(int dtype, const void* src, const SgConvGeom* g, co
   SG_REQUIRE(g->C < 32768, "sg_conv_wgrad: too many channels");
   p.perm_c = nchunk * MN_BOX; p.perm_kk = static_cast<short>(g->k * g->k); p.perm_valid = static_cast<short>(g->C);
   const int num_kb = static_cast<int>((P + BK - 1) / BK);
-  const long long tiles = static_cast<long long>((F + BM - 1) / BM) * ((Np + bn - 1) / bn);
-  int split = static_cast<int>(num_sms() / (tiles > 0 ? tiles : 1));
+  // CTA pairs when there are at least two row tiles of filters (each CTA then stages half of the patch tile)
+  static const int env_pair = [] { const char* e = getenv("SINGA_B200_CONV_PAIR"); return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0); }();
+  const bool pair = F > BM && bn >= 128 && env_pair != 0;
+  const long long tiles = static_cast<long long>((F + (pair ? 2 : 1) * BM - 1) / ((pair ? 2 : 1) * BM)) * ((Np + bn - 1) / bn);
+  int split = static_cast<int>((pair ? num_sms() / 2 : num_sms()) / (tiles > 0 ? tiles : 1));
   if (split > num_kb / 8) split = num_kb / 8;
   if (split > 64) split = 64;
   if (split < 1) split = 1;
@@ -711,6 +820,11 @@ extern "C" int sg_conv_wgrad(int dtype, const void* src, const SgConvGeom* g, co
   cp.OW = g->OW; cp.OHW = g->OH * g->OW; cp.stride = g->stride; cp.pad_lo = g->pad_lo; cp.ksize = g->k;
   cp.nchunk = nchunk; cp.chunk_elems = MN_BOX; cp.nsub = nsub; cp.c_oob = nchunk * MN_BOX + MN_BOX;
   cp.R = 128; cp.a_layout = 0; cp.a_sbo = 0; cp.a_lbo = 0;
+  if (pair) {
+    if (eb == 2)
+      return bn == 256 ? launch_conv_pair<2, 256, MODE_COLS>(ta, tb, p, cp, s) : launch_conv_pair<2, 128, MODE_COLS>(ta, tb, p, cp, s);
+    return bn == 256 ? launch_conv_pair<4, 256, MODE_COLS>(ta, tb, p, cp, s) : launch_conv_pair<4, 128, MODE_COLS>(ta, tb, p, cp, s);
+  }
   if (eb == 2) return dispatch_conv<2, MODE_COLS>(bn, ta, tb, p, cp, s);
   return dispatch_conv<4, MODE_COLS>(bn, ta, tb, p, cp, s);
 }

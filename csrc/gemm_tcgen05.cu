@@ -99,8 +99,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+    // The whole warp walks the loop and one elected lane issues (see elect_one): coordinates stay in uniform registers.
+    {
+      if (lane == 0 && p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+      __syncwarp();
       uint32_t stage = 0, phase = 0;
       for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
         const int slice = p.split_k == 1 ? 0 : item / num_tiles;   // no division on the common path
@@ -112,27 +114,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t fb = full_bar(stage);
-          mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
           const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
           const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
           const int k0 = kb * BK;
-          if (!A_MN) {
-            tma_load_2d(sa, &tma_a, fb, k0, m0);
-          } else {
+          if (elect_one()) {
+            mbar_arrive_expect_tx(fb, Cfg::STAGE_BYTES);
+            if (!A_MN) {
+              tma_load_2d(sa, &tma_a, fb, k0, m0);
+            } else {
 #pragma unroll
-            for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
-          }
-          if (!B_MN) {
-            tma_load_2d(sb, &tma_b, fb, k0, n0);
-          } else {
+              for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
+            }
+            if (!B_MN) {
+              tma_load_2d(sb, &tma_b, fb, k0, n0);
+            } else {
 #pragma unroll
-            for (int b = 0; b < BN / MN_BOX; ++b) tma_load_2d(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
+              for (int b = 0; b < BN / MN_BOX; ++b) tma_load_2d(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
+            }
+            if (kb == kb_lo) SG_TRACE(2);
           }
-          if (kb == kb_lo) SG_TRACE(2);
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
-      SG_TRACE(3);
+      if (lane == 0) SG_TRACE(3);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -160,9 +165,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
         if (lane == 0 && kb == kb_lo) SG_TRACE(4);
-        if (lane == 0) {
-          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
-          const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
+        const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+        const uint32_t sb = sB0 + stage * B_STAGE_BYTES;
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO, A_LAYOUT);
@@ -297,8 +302,9 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
-    if (lane == 0) {
-      if (p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+    {
+      if (lane == 0 && p.nwait > 0) wait_param_versions(p.wait_flags, p.nwait, p.wait_seq);
+      __syncwarp();
       uint32_t stage = 0, phase = 0;
       for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
         const int m0 = (tile % m_tiles) * (2 * BM) + static_cast<int>(rank) * BM;   // this CTA's 128 rows
@@ -306,23 +312,26 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t fb = full_bar(stage);
-          if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
-          else mbar_arrive_remote(fb, 0);
           const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
           const uint32_t sb = sB0 + stage * B_HALF_BYTES;
           const int k0 = kb * BK;
-          if (!A_MN) {
-            tma_load_2d_pair(sa, &tma_a, fb, k0, m0);
-          } else {
+          if (elect_one()) {
+            if (leader) mbar_arrive_expect_tx(fb, 2 * Cfg::STAGE_BYTES);
+            else mbar_arrive_remote(fb, 0);
+            if (!A_MN) {
+              tma_load_2d_pair(sa, &tma_a, fb, k0, m0);
+            } else {
 #pragma unroll
-            for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d_pair(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
-          }
-          if (!B_MN) {
-            tma_load_2d_pair(sb, &tma_b, fb, k0, n0);
-          } else {
+              for (int b = 0; b < BM / MN_BOX; ++b) tma_load_2d_pair(sa + b * MN_BOX_BYTES, &tma_a, fb, m0 + b * MN_BOX, k0);
+            }
+            if (!B_MN) {
+              tma_load_2d_pair(sb, &tma_b, fb, k0, n0);
+            } else {
 #pragma unroll
-            for (int b = 0; b < BNH / MN_BOX; ++b) tma_load_2d_pair(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
+              for (int b = 0; b < BNH / MN_BOX; ++b) tma_load_2d_pair(sb + b * MN_BOX_BYTES, &tma_b, fb, n0 + b * MN_BOX, k0);
+            }
           }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -350,9 +359,9 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a,
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
-            const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          const uint32_t sa = sA0 + stage * A_STAGE_BYTES;
+          const uint32_t sb = sB0 + stage * B_HALF_BYTES;
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t adesc = make_smem_desc(sa + k * A_KSTEP, A_LBO, A_SBO, A_LAYOUT);

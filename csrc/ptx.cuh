@@ -50,6 +50,22 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// One lane of a converged warp (elect.sync).  A producer loop that the WHOLE warp executes, with only the elected lane
+// issuing the TMA instructions, keeps the coordinates in uniform registers; a loop run by `if (lane == 0)` alone makes
+// the compiler wrap every UTMALDG in an ELECT / R2UR.BROADCAST / BRA.U.ANY "waterfall" (~15 instructions per load),
+// which made one-thread producers with 8-12 loads per k-block the bottleneck of the MN-major kernels.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.b32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ----------------------------------------------------------------------------------------------
 // Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
 // (launch latency, barrier / TMEM set-up) while the previous kernel of the stream still runs; pdl_wait() blocks until

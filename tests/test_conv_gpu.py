@@ -163,6 +163,8 @@ PAIR_CASES = [
     (5, 64, 13, 13, 256, 3, 1, 1),     # 845 pixels: 4 pair tiles, the last one with an all-padding second CTA
     (3, 128, 12, 10, 136, 3, 1, 1),    # F = 136: ragged filter tile, half of it beyond the matrix for the second CTA
     (2, 64, 17, 17, 128, 5, 1, 2),     # 5x5
+    (3, 96, 13, 13, 160, 5, 1, 2),     # bf16: 64-byte chunks (two boxes per k-block)
+    (4, 48, 14, 14, 384, 3, 1, 1),     # fp32: 64-byte chunks, bf16: 32-byte chunks; 384 filters = 1.5 pair tiles
 ]
 
 
@@ -194,5 +196,15 @@ def test_conv_cta_pair_tiles(case, dtype):
             plan.dgrad(dy, dx.permute(0, 2, 3, 1).reshape(N * H * W, C), tile=(bn, 2))
             torch.cuda.synchronize()
             torch.testing.assert_close(dx.float(), dx_ref, **_tols(dtype, F * k * k))
+        # weight gradient: CTA pairs are the library's own choice for more than 128 filters (split-K over the pixels)
+        dw = torch.full((F, C * k * k), float("nan"), device=DEV)
+        plan.wgrad(dy, dw)
+        torch.cuda.synchronize()
+        dw_ref = torch.nn.grad.conv2d_weight(xr, wr.shape, dy.float(), stride=s, padding=p).reshape(F, -1)
+        torch.testing.assert_close(dw, dw_ref, **_tols(dtype, plan.P))
+        dw2 = torch.ones_like(dw)
+        plan.wgrad(dy, dw2, accumulate=True)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(dw2, dw_ref + 1.0, **_tols(dtype, plan.P))
     finally:
         torch.backends.cudnn.allow_tf32 = prev

@@ -9,7 +9,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 import torch.nn.functional as F_  # noqa: E402
 
-from singa_b200.ops.conv import ConvPlan, _mat  # noqa: E402
+from singa_b200.ops.conv import _mat, make_plan  # noqa: E402
 
 dev = "cuda"
 torch.backends.cudnn.allow_tf32 = True
@@ -45,7 +45,7 @@ for dtype, name in ((torch.float32, "fp32 storage, tf32 products"), (torch.bfloa
     for lname, N, C, H, W, F, k, s, p, need_dx in LAYERS:
         x = (torch.randn(N, C, H, W, device=dev) * 0.5).to(dtype).contiguous(memory_format=torch.channels_last)
         w32 = torch.randn(F, C * k * k, device=dev) * 0.05
-        plan = ConvPlan(N, C, H, W, F, k, s, p, dtype, dev, need_dgrad=need_dx)
+        plan = make_plan(N, C, H, W, F, k, s, p, dtype, dev, need_dgrad=need_dx)   # what the layer uses
         plan.pack(w32)
         y = torch.empty(N, F, plan.OH, plan.OW, device=dev, dtype=dtype).contiguous(memory_format=torch.channels_last)
         dy = torch.randn_like(y)
