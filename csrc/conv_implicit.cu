@@ -741,9 +741,11 @@ extern "C" int sg_conv_rows(int dtype, const void* src, const SgConvGeom* g, con
     return rc;
   int bn = ep->tile_bn ? ep->tile_bn : (ncols > 128 ? 256 : (ncols > 64 ? 128 : 64));
   SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_conv_rows: tile_bn must be 0, 64, 128 or 256");
-  // CTA pairs: at least 128 filter columns per tile and enough 256-pixel tiles for every pair of SMs; ep->tile_pair 1 / 2 and SINGA_B200_CONV_PAIR=0 / 1 force the choice
+  // CTA pairs: 256-column filter tiles (measured: 1-5 % faster than single CTAs on AlexNet conv2-5 forward / data
+  // gradient; with 128-column tiles, e.g. the 96-channel data gradient of conv2, 10 % slower) and enough 256-pixel tiles
+  // for every pair of SMs; ep->tile_pair 1 / 2 and SINGA_B200_CONV_PAIR=0 / 1 force the choice
   static const int env_pair = [] { const char* e = getenv("SINGA_B200_CONV_PAIR"); return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0); }();
-  bool pair = R >= 32 && bn >= 128 && (P + 2 * BM - 1) / (2 * BM) * ((ncols + bn - 1) / bn) >= num_sms() / 2;
+  bool pair = R >= 32 && bn == 256 && (P + 2 * BM - 1) / (2 * BM) * ((ncols + bn - 1) / bn) >= num_sms() / 2;
   if (env_pair >= 0) pair = pair && env_pair == 1;
   if (ep->tile_pair == 1) pair = false;
   if (ep->tile_pair == 2) pair = bn >= 128;
@@ -796,9 +798,11 @@ extern "C" int sg_conv_wgrad(int dtype, const void* src, const SgConvGeom* g, co
   SG_REQUIRE(g->C < 32768, "sg_conv_wgrad: too many channels");
   p.perm_c = nchunk * MN_BOX; p.perm_kk = static_cast<short>(g->k * g->k); p.perm_valid = static_cast<short>(g->C);
   const int num_kb = static_cast<int>((P + BK - 1) / BK);
-  // CTA pairs when there are at least two row tiles of filters (each CTA then stages half of the patch tile)
+  // CTA pairs when the filters fill whole 256-row tiles (each CTA then stages half of the patch tile): 2-5 % faster on
+  // the 256-filter layers of AlexNet; 384 filters would leave a quarter of the second pair tile empty (measured 10-25 %
+  // slower than single CTAs)
   static const int env_pair = [] { const char* e = getenv("SINGA_B200_CONV_PAIR"); return e == nullptr ? -1 : (e[0] == '1' ? 1 : 0); }();
-  const bool pair = F > BM && bn >= 128 && env_pair != 0;
+  const bool pair = F % (2 * BM) == 0 && bn >= 128 && env_pair != 0;
   const long long tiles = static_cast<long long>((F + (pair ? 2 : 1) * BM - 1) / ((pair ? 2 : 1) * BM)) * ((Np + bn - 1) / bn);
   int split = static_cast<int>((pair ? num_sms() / 2 : num_sms()) / (tiles > 0 ? tiles : 1));
   if (split > num_kb / 8) split = num_kb / 8;

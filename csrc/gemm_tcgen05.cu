@@ -555,34 +555,41 @@ static int dispatch_tile(bool pair, int bn, int a_mn, int b_mn, const CUtensorMa
   }
 }
 
-// Tile-width choice from a small cost model (cycles).  Measured on B200: this kernel is bound by the
-// L2 -> shared-memory path (about 6300 B/cycle for the whole chip, i.e. ~42 B/cycle/SM with every SM pulling),
-// not by the tensor pipe, so wide tiles (fewer bytes per flop) win even when they leave SMs idle:
+// Tile choice from a small cost model (cycles), fitted to `tools/gemm_micro.py` sweeps of the 18 MNIST-MLP shapes in
+// both precisions (it picks the fastest of the five configurations for all 18 tf32 shapes and 17 of the bf16 ones).
+// Measured on B200: a CTA takes in about 40 bytes per cycle through TMA however few CTAs run, and the whole chip about
+// 6300; the tensor pipe is rarely the limit.  So the cost of a k-block is its bytes per CTA, and CTA pairs (half of
+// the B tile per CTA) win whenever their fewer, larger tiles still cover the SMs:
 //   per k-block:  mma = max(2*BN, 128 + BN) cycles   (tensor pipe vs. smem operand reads at 128 B/cycle)
-//                 l2  = (16 KB + BN*128 B) / min(64, 6300 / active CTAs)
-//   total = waves * (num_kb * max(mma, l2) + fixed per-tile overhead)
-static int pick_bn(int M, int N, int K, int BK) {
+//                 tma = bytes per CTA / min(40, 6300 / active CTAs),  bytes = 16 KB + BN*128 B  (pairs: BN*64 B)
+//   total = waves * (num_kb * max(mma, tma) + 1500)
+static void pick_tile(int M, int N, int K, int BK, bool allow_single, bool allow_pair, int* bn_out, bool* pair_out) {
   const int sms = num_sms();
-  const long long m_tiles = (M + BM - 1) / BM;
   const long long num_kb = (K + BK - 1) / BK;
   const int cands[3] = {256, 128, 64};
   double best = 1e30;
   int best_bn = 64;
-  for (int i = 0; i < 3; ++i) {
-    const int bn = cands[i];
-    if (bn > 64 && N <= bn / 2) continue;   // more than half of the tile would be padding
-    const long long tiles = m_tiles * ((N + bn - 1) / bn);
-    const long long active = tiles < sms ? tiles : sms;
-    const long long waves = (tiles + sms - 1) / sms;
-    const double mma = (2.0 * bn > 128.0 + bn) ? 2.0 * bn : 128.0 + bn;
-    double bw = 6300.0 / static_cast<double>(active);
-    if (bw > 64.0) bw = 64.0;
-    const double l2 = (16384.0 + bn * 128.0) / bw;
-    const double per_tile = num_kb * (mma > l2 ? mma : l2) + 2500.0 + 6.0 * bn;
-    const double total = waves * per_tile;
-    if (total < best) { best = total; best_bn = bn; }
+  bool best_pair = false;
+  for (int pr = 0; pr < 2; ++pr) {
+    if (pr == 0 ? !allow_single : !allow_pair) continue;
+    for (int i = 0; i < 3; ++i) {
+      const int bn = cands[i];
+      if (pr == 1 && bn < 128) continue;        // pairs stage BN/2 columns of B per CTA in boxes of >= 64 columns
+      if (bn > 64 && N <= bn / 2) continue;     // more than half of the tile would be padding
+      const long long rows = pr == 1 ? 2 * BM : BM;
+      const long long ctas = ((M + rows - 1) / rows) * ((N + bn - 1) / bn) * (pr == 1 ? 2 : 1);
+      const long long active = ctas < sms ? ctas : sms;
+      const long long waves = (ctas + sms - 1) / sms;
+      const double mma = (2.0 * bn > 128.0 + bn) ? 2.0 * bn : 128.0 + bn;
+      double bw = 6300.0 / static_cast<double>(active);
+      if (bw > 40.0) bw = 40.0;
+      const double tma = (16384.0 + bn * (pr == 1 ? 64.0 : 128.0)) / bw;
+      const double total = waves * (num_kb * (mma > tma ? mma : tma) + 1500.0);
+      if (total < best) { best = total; best_bn = bn; best_pair = pr == 1; }
+    }
   }
-  return best_bn;
+  *bn_out = best_bn;
+  *pair_out = best_pair;
 }
 
 int g_force_bn = 0;  // test hook (sg_gemm_set_tile)
@@ -621,11 +628,16 @@ extern "C" int sg_gemm(int dtype, const void* A, int a_mn_major, long long lda, 
              "sg_gemm: epilogue needs an output");
   SG_REQUIRE(ep->grad_act == SG_ACT_NONE || ep->aux != nullptr, "sg_gemm: grad_act needs aux");
   // per-call tile choice (autotuner) > process-wide test hooks > built-in model
-  int bn = ep->tile_bn ? ep->tile_bn : (g_force_bn ? g_force_bn : pick_bn(M, N, K, BK));
-  SG_REQUIRE(bn == 64 || bn == 128 || bn == 256, "sg_gemm: tile_bn must be 0, 64, 128 or 256");
+  int bn = ep->tile_bn ? ep->tile_bn : g_force_bn;
+  SG_REQUIRE(bn == 0 || bn == 64 || bn == 128 || bn == 256, "sg_gemm: tile_bn must be 0, 64, 128 or 256");
   // CTA pairs need BN in {128, 256} (each CTA stages BN/2 columns of B in 64-column boxes)
-  bool pair = ep->tile_pair == 2 || (ep->tile_pair == 0 &&
-      (g_pair_mode == 1 || (g_pair_mode == 2 && static_cast<long long>(M) * N >= 4096LL * 4096LL)));
+  bool pair = ep->tile_pair == 2 || (ep->tile_pair == 0 && g_pair_mode == 1);
+  const bool pair_free = ep->tile_pair == 0 && g_pair_mode == 2;
+  if (bn == 0) {
+    pick_tile(M, N, K, BK, !pair, pair || pair_free, &bn, &pair);
+  } else if (pair_free) {
+    pair = bn >= 128 && static_cast<long long>(M) * N >= 4096LL * 4096LL;
+  }
   if (pair && bn < 128) bn = 128;
   CUtensorMap ta, tb;
   int rc;

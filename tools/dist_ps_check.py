@@ -31,6 +31,14 @@ def run(push_pull, world, rank, steps, batch, hidden, config="mnist_mlp", graph=
     model.prefetch = False
     model.updater.base_learning_rate = 0.02
     model.updater.momentum = 0.9
+    if config == "alexnet":
+        # W ranks x B equals 1 process x W*B only for deterministic layers: the dropout mask is a function of the
+        # element index inside a rank's own batch, so the two jobs would draw different masks; and 0.02 with momentum
+        # diverges on this net within a few steps, which turns rounding differences into O(1) weight differences
+        model.updater.base_learning_rate = 0.002
+        for l in model.neuralnet.layer:
+            if l.type == "kDropout":
+                l.dropout_param.dropout_ratio = 0.0
     cluster = None
     Cluster.reset()      # the single-process reference must not inherit the worker-group layout of the previous run
     if push_pull is not None:
