@@ -107,6 +107,17 @@ int sg_convert(const void* src, int src_bf16, void* dst, int dst_bf16, long long
  * dimension). */
 int sg_copy2d(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, int is_bf16, void* stream);
 int sg_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, int rows, int cols, void* stream);
+/* Inner product with 1..16 outputs (classifier layers) on CUDA cores; operands and layouts as for sg_gemm:
+ * x [M][K], w [K][N] (the reference's {vdim, hdim} weight), y [M][N]; every operand fp32 or bf16 by its flag.
+ *   fwd  : y = act(x . w + bias)            dgrad: dx = (dy . w^T) * act'(aux)   (aux = output of the layer below)
+ *   wgrad: dw (+)= x^T . dy (fp32) and, when db is given, db (+)= column sums of dy */
+int sg_ip_small_fwd(const void* x, long long ldx, int x_bf16, const void* w, long long ldw, int w_bf16, const void* bias,
+                    int bias_bf16, void* y, long long ldy, int y_bf16, int M, int K, int N, int act, void* stream);
+int sg_ip_small_dgrad(const void* dy, long long lddy, int dy_bf16, const void* w, long long ldw, int w_bf16,
+                      const void* aux, long long ldaux, int aux_bf16, int grad_act, void* dx, long long lddx, int dx_bf16,
+                      int M, int K, int N, void* stream);
+int sg_ip_small_wgrad(const void* x, long long ldx, int x_bf16, const void* dy, long long lddy, int dy_bf16, float* dw,
+                      long long lddw, float* db, int M, int K, int N, int accumulate, void* stream);
 /* Space-to-depth for strided convolutions over thin (grey / RGB) inputs:
  *   xs[n][Y][X][(dy*s + dx)*C + c] = x[n][Y*s + dy - pad][X*s + dx - pad][c], zero outside the image and for the
  *   padding channels [s*s*C, Cs).  x: [N][H][W][C], xs: [N][Hs][Ws][Cs], both of one element type. */

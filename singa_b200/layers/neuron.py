@@ -15,6 +15,8 @@ Fusions decided by ``NeuralNet.fuse_activations`` (natural fusion boundaries of 
 """
 from __future__ import annotations
 
+import os
+
 import zlib
 
 from typing import List, Optional
@@ -186,14 +188,24 @@ class InnerProductLayer(NeuronLayer):
         w = self.weight if self.weight.is_owner else self.weight.owner
         return w.data16
 
+    def _small(self) -> bool:
+        """Classifier-sized layers (<= 16 outputs) run on the CUDA-core kernels of csrc/ip_small.cu: a 128-row
+        tensor-core tile would be mostly padding and three GEMM launches cost more than the arithmetic.  Not when the
+        forward GEMM itself has to wait for the parameter server's version flags (non-rotated fused pull)."""
+        return self.hdim <= 16 and self.pull_wait is None and os.environ.get("SINGA_B200_IP_SMALL", "1") != "0"
+
     def compute_feature(self, training):
         x = self._x2d()
         if self.native:
             K = _K()
             w16 = self._w16()
-            K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, **_out(self.data),
-                   bias=self._bias_operand() if self.bias_term else None, act=self.fused_act,
-                   wait=self.pull_wait if training else None)
+            if self._small():
+                K.ip_small_fwd(x, w16, self.data, self.batchsize, self.vdim, self.hdim,
+                               bias=self._bias_operand() if self.bias_term else None, act=self.fused_act)
+            else:
+                K.gemm(x, w16, self.batchsize, self.hdim, self.vdim, a_mn=False, b_mn=True, **_out(self.data),
+                       bias=self._bias_operand() if self.bias_term else None, act=self.fused_act,
+                       wait=self.pull_wait if training else None)
             self._x_saved = x
         else:
             y = R.ip_fwd(x, self.weight.data, self.bias.data if self.bias_term else None)
@@ -216,6 +228,10 @@ class InnerProductLayer(NeuronLayer):
         if self.native:
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
+            if self._small():     # weight and bias gradient in one launch
+                K.ip_small_wgrad(x, dy, self.weight.grad, self.batchsize, self.vdim, self.hdim,
+                                 db=self.bias.grad if self.bias_term else None, accumulate=accumulate)
+                return
             # the (tiny) bias reduction goes first: issued behind the GEMM it would run while the previous bucket's
             # push kernel occupies the SMs, and the push of THIS layer waits for both
             if self.bias_term:
@@ -244,7 +260,10 @@ class InnerProductLayer(NeuronLayer):
             K = _K()
             w16 = self._w16()
             if self.src4d:
-                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, **_out(self.dx_flat))
+                if self._small():
+                    K.ip_small_dgrad(dy, w16, self.dx_flat, self.batchsize, self.vdim, self.hdim)
+                else:
+                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, **_out(self.dx_flat))
                 n, c, h, w = self.srclayers[0].shape(self)
                 if self.vdim % self.ldq == 0:
                     K.transpose_planes(self.dx_flat, dst, n, c, h * w)   # (c,h,w) -> NHWC
@@ -255,8 +274,12 @@ class InnerProductLayer(NeuronLayer):
             else:
                 d2 = self._flat2d(dst)
                 a2 = self._flat2d(aux) if aux is not None else None
-                K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, grad_act=self.src_grad_act, aux=a2,
-                       **_out(d2))
+                if self._small():
+                    K.ip_small_dgrad(dy, w16, d2, self.batchsize, self.vdim, self.hdim,
+                                     grad_act=self.src_grad_act if a2 is not None else ACT_NONE, aux=a2)
+                else:
+                    K.gemm(dy, w16, self.batchsize, self.vdim, self.hdim, grad_act=self.src_grad_act, aux=a2,
+                           **_out(d2))
         else:
             with R._mm_ctx(dy):
                 dx = R._f(dy.float() @ self.weight.data.t())

@@ -29,6 +29,9 @@ SIGNATURES = {
     "sg_copy2d_bf16": [vp, i64, vp, i64, i32, i32, vp],
     "sg_copy2d": [vp, i64, vp, i64, i32, i32, i32, vp],
     "sg_transpose_planes": [vp, i32, vp, i32, i32, i32, i32, vp],
+    "sg_ip_small_fwd": [vp, i64, i32, vp, i64, i32, vp, i32, vp, i64, i32, i32, i32, i32, i32, vp],
+    "sg_ip_small_dgrad": [vp, i64, i32, vp, i64, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, i32, vp],
+    "sg_ip_small_wgrad": [vp, i64, i32, vp, i64, i32, vp, i64, vp, i32, i32, i32, i32, vp],
     "sg_space_to_depth": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "sg_gather_cols": [vp, i32, i64, vp, i64, i32, i32, vp, vp],
     "sg_scatter_cols": [vp, i64, vp, i64, i32, i32, vp, i32, vp],

@@ -66,6 +66,31 @@ def copy2d(src, lds, dst, ldd, rows, cols):
 copy2d_bf16 = copy2d
 
 
+IP_SMALL_MAX_N = 16
+
+
+def ip_small_fwd(x, w, y, M, K, N, bias=None, act=ACT_NONE):
+    """y[M][N] = act(x[M][K] . w[K][N] + bias), N <= 16 (csrc/ip_small.cu)."""
+    assert x.stride(-1) == 1 and w.stride(-1) == 1 and y.stride(-1) == 1
+    _call("sg_ip_small_fwd", x.data_ptr(), x.stride(0), _bf(x), w.data_ptr(), w.stride(0), _bf(w), native.ptr(bias),
+          _bf(bias) if bias is not None else 0, y.data_ptr(), y.stride(0), _bf(y), M, K, N, act)
+
+
+def ip_small_dgrad(dy, w, dx, M, K, N, grad_act=ACT_NONE, aux=None):
+    """dx[M][K] = (dy[M][N] . w[K][N]^T) * act'(aux)."""
+    assert dy.stride(-1) == 1 and w.stride(-1) == 1 and dx.stride(-1) == 1
+    _call("sg_ip_small_dgrad", dy.data_ptr(), dy.stride(0), _bf(dy), w.data_ptr(), w.stride(0), _bf(w), native.ptr(aux),
+          aux.stride(0) if aux is not None else 0, _bf(aux) if aux is not None else 0, grad_act, dx.data_ptr(),
+          dx.stride(0), _bf(dx), M, K, N)
+
+
+def ip_small_wgrad(x, dy, dw, M, K, N, db=None, accumulate=False):
+    """dw[K][N] (+)= x[M][K]^T . dy[M][N]; db[N] (+)= column sums of dy."""
+    assert dw.dtype == torch.float32 and (db is None or db.dtype == torch.float32)
+    _call("sg_ip_small_wgrad", x.data_ptr(), x.stride(0), _bf(x), dy.data_ptr(), dy.stride(0), _bf(dy), dw.data_ptr(),
+          dw.stride(0), native.ptr(db), M, K, N, 1 if accumulate else 0)
+
+
 def space_to_depth(x, xs, N, H, W, C, Hs, Ws, Cs, s, pad):
     assert x.dtype == xs.dtype
     _call("sg_space_to_depth", x.data_ptr(), xs.data_ptr(), N, H, W, C, Hs, Ws, Cs, s, pad, _bf(x))

@@ -353,3 +353,41 @@ def test_mnist_distort_kernel_matches_reference(dtype):
     ref = R.mnist_distort(src, A, disp, out, 127.5, 1.0)
     tol = dict(rtol=1e-2, atol=1e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
     torch.testing.assert_close(dst.float(), ref, **tol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,Kd,N", [(1000, 500, 10), (37, 1024, 16), (64, 13, 1)])
+def test_ip_small_kernels(M, Kd, N, dtype):
+    """Classifier-sized inner product (<= 16 outputs) on CUDA cores: forward with bias + activation, data gradient
+    with a fused activation gradient, weight + bias gradient (plain and accumulating) against fp32 torch."""
+    from singa_b200.ops import gemm as G
+    torch.manual_seed(M + N)
+    q = 8 if dtype == torch.bfloat16 else 4
+    ldn = (N + q - 1) // q * q
+    x = (torch.randn(M, Kd, device=DEV) * 0.5).to(dtype)
+    w = torch.zeros(Kd, ldn, device=DEV, dtype=dtype)
+    w[:, :N] = (torch.randn(Kd, N, device=DEV) * 0.1).to(dtype)
+    b = torch.randn(N, device=DEV)
+    y = torch.full((M, ldn), float("nan"), device=DEV)                       # fp32 output (feeds the loss)
+    K().ip_small_fwd(x, w[:, :N], y[:, :N], M, Kd, N, bias=b, act=G.ACT_STANH)
+    ref = 1.7159047 * torch.tanh(0.66666667 * (x.float() @ w[:, :N].float() + b))
+    torch.testing.assert_close(y[:, :N], ref, rtol=2e-3, atol=2e-3)
+    dy = (torch.randn(M, ldn, device=DEV) * 0.5).to(dtype)
+    aux = (torch.randn(M, Kd, device=DEV)).to(dtype)
+    dx = torch.full((M, Kd), float("nan"), device=DEV, dtype=dtype)
+    K().ip_small_dgrad(dy[:, :N], w[:, :N], dx, M, Kd, N, grad_act=G.ACT_RELU, aux=aux)
+    dref = (dy[:, :N].float() @ w[:, :N].float().t()) * (aux.float() > 0)
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(dx.float(), dref, **tol)
+    K().ip_small_dgrad(dy[:, :N], w[:, :N], dx, M, Kd, N)
+    torch.testing.assert_close(dx.float(), dy[:, :N].float() @ w[:, :N].float().t(), **tol)
+    dw = torch.full((Kd, ldn), float("nan"), device=DEV)
+    db = torch.full((N,), float("nan"), device=DEV)
+    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, db=db)
+    wref = x.float().t() @ dy[:, :N].float()
+    bref = dy[:, :N].float().sum(0)
+    torch.testing.assert_close(dw[:, :N], wref, rtol=1e-4, atol=1e-3)
+    torch.testing.assert_close(db, bref, rtol=1e-4, atol=1e-3)
+    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, db=db, accumulate=True)
+    torch.testing.assert_close(dw[:, :N], 2 * wref, rtol=1e-4, atol=2e-3)
+    torch.testing.assert_close(db, 2 * bref, rtol=1e-4, atol=2e-3)
