@@ -57,6 +57,11 @@ def parse_args():
     ap.add_argument("--sync-frequency", type=int, default=0, help="--push-pull async: steps between exchanges (0 = config's)")
     ap.add_argument("--server-groups", type=int, default=1, help="--push-pull async: server groups (neighbour averaging)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--expect-loss-window", default="",
+                    help="'loss,metric' of another arm's e2e.final_loss_sum_window for the same config / steps / GPUs "
+                         "(e.g. --push-pull nccl): the run fails (exit 3) when its own window differs by more than "
+                         "--loss-tol — tools/run_matrix.sh checks every fused run against the NCCL exchange this way")
+    ap.add_argument("--loss-tol", type=float, default=0.0, help="relative tolerance (0 = 2e-2 for bf16, 5e-3 otherwise)")
     return ap.parse_args()
 
 
@@ -445,7 +450,21 @@ def main():
                     "final_loss_sum_window": [round(float(x), 4) for x in last.tolist()] if last is not None else None},
             "gpu_launches": gpu_launches,
         }
+        loss_ok = True
+        if args.expect_loss_window and last is not None:
+            want = [float(v) for v in args.expect_loss_window.split(",")]
+            tol = args.loss_tol or (2e-2 if args.dtype == "bf16" else 5e-3)
+            got = [float(x) for x in last.tolist()]
+            errs = [abs(g - w_) / max(abs(w_), 1e-6) for g, w_ in zip(got, want)]
+            loss_ok = errs[0] <= tol      # the loss decides; the accuracy sum of a few steps at chance level is noise
+            out["loss_check"] = {"expected": want, "got": [round(g, 4) for g in got], "rel_err": [round(e, 5) for e in errs],
+                                 "tol": tol, "ok": loss_ok}
         print(json.dumps(out))
+        if not loss_ok:
+            sys.stderr.write(f"bench.py: loss window {out['loss_check']['got']} differs from the expected "
+                             f"{out['loss_check']['expected']} by more than {out['loss_check']['tol']}\n")
+            sys.stdout.flush()
+            os._exit(3)
     sys.stdout.flush()
     if world > 1:
         # NCCL work captured in CUDA graphs can make destroy_process_group hang; every rank has passed the final

@@ -31,8 +31,10 @@ for c in $CONFIGS; do
       run ${c}_n1_ours_$d --config $c --dtype $d --steps $steps --warmup $warm
       run ${c}_n1_torch_$d --config $c --dtype $d --impl torch --steps $steps --warmup $warm
     else
-      run ${c}_n${N}_fused_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull fused
       run ${c}_n${N}_nccl_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull nccl
+      # the fused exchange must train to the same loss as the NCCL exchange of the same kernels
+      want=$(python -c "import json;print(','.join(str(v) for v in json.loads(open('$OUT/${c}_n${N}_nccl_$d.json').read().strip().splitlines()[-1])['e2e']['final_loss_sum_window']))" 2>/dev/null)
+      run ${c}_n${N}_fused_$d --config $c --dtype $d --steps $steps --warmup $warm --push-pull fused ${want:+--expect-loss-window $want}
       run ${c}_n${N}_torch_$d --config $c --dtype $d --impl torch --steps $steps --warmup $warm
       if [ "$c" = "cifar10" ]; then
         for st in 0 2 8; do
