@@ -116,8 +116,11 @@ int sg_ip_small_fwd(const void* x, long long ldx, int x_bf16, const void* w, lon
 int sg_ip_small_dgrad(const void* dy, long long lddy, int dy_bf16, const void* w, long long ldw, int w_bf16,
                       const void* aux, long long ldaux, int aux_bf16, int grad_act, void* dx, long long lddx, int dx_bf16,
                       int M, int K, int N, void* stream);
+/* ws: zero-initialised device buffer of sg_ip_small_wgrad_ws_bytes(M, K) bytes, private to the calls that may run
+ * concurrently (partial sums per 32-row slice, added up in slice order by the last block: deterministic). */
+long long sg_ip_small_wgrad_ws_bytes(int M, int K);
 int sg_ip_small_wgrad(const void* x, long long ldx, int x_bf16, const void* dy, long long lddy, int dy_bf16, float* dw,
-                      long long lddw, float* db, int M, int K, int N, int accumulate, void* stream);
+                      long long lddw, float* db, int M, int K, int N, int accumulate, void* ws, void* stream);
 /* Space-to-depth for strided convolutions over thin (grey / RGB) inputs:
  *   xs[n][Y][X][(dy*s + dx)*C + c] = x[n][Y*s + dy - pad][X*s + dx - pad][c], zero outside the image and for the
  *   padding channels [s*s*C, Cs).  x: [N][H][W][C], xs: [N][Hs][Ws][Cs], both of one element type. */

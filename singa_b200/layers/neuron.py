@@ -192,7 +192,10 @@ class InnerProductLayer(NeuronLayer):
         """Classifier-sized layers (<= 16 outputs) run on the CUDA-core kernels of csrc/ip_small.cu: a 128-row
         tensor-core tile would be mostly padding and three GEMM launches cost more than the arithmetic.  Not when the
         forward GEMM itself has to wait for the parameter server's version flags (non-rotated fused pull)."""
-        return self.hdim <= 16 and self.pull_wait is None and os.environ.get("SINGA_B200_IP_SMALL", "1") != "0"
+        # measured: 0.394 -> 0.387 ms per MNIST step (batch 1000); no gain at batch 64-128 (LeNet, CIFAR-10), where a
+        # single 128-row tile already covers the batch
+        return (self.hdim <= 16 and self.batchsize >= 256 and self.vdim * (self.hdim | 1) * 4 <= 96 * 1024
+                and self.pull_wait is None and os.environ.get("SINGA_B200_IP_SMALL", "1") != "0")
 
     def compute_feature(self, training):
         x = self._x2d()
@@ -229,7 +232,9 @@ class InnerProductLayer(NeuronLayer):
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
             if self._small():     # weight and bias gradient in one launch
-                K.ip_small_wgrad(x, dy, self.weight.grad, self.batchsize, self.vdim, self.hdim,
+                if getattr(self, "_ips_ws", None) is None:
+                    self._ips_ws = K.ip_small_wgrad_workspace(self.batchsize, self.vdim, dy.device)
+                K.ip_small_wgrad(x, dy, self.weight.grad, self.batchsize, self.vdim, self.hdim, self._ips_ws,
                                  db=self.bias.grad if self.bias_term else None, accumulate=accumulate)
                 return
             # the (tiny) bias reduction goes first: issued behind the GEMM it would run while the previous bucket's

@@ -31,7 +31,7 @@ SIGNATURES = {
     "sg_transpose_planes": [vp, i32, vp, i32, i32, i32, i32, vp],
     "sg_ip_small_fwd": [vp, i64, i32, vp, i64, i32, vp, i32, vp, i64, i32, i32, i32, i32, i32, vp],
     "sg_ip_small_dgrad": [vp, i64, i32, vp, i64, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, i32, vp],
-    "sg_ip_small_wgrad": [vp, i64, i32, vp, i64, i32, vp, i64, vp, i32, i32, i32, i32, vp],
+    "sg_ip_small_wgrad": [vp, i64, i32, vp, i64, i32, vp, i64, vp, i32, i32, i32, i32, vp, vp],
     "sg_space_to_depth": [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp],
     "sg_gather_cols": [vp, i32, i64, vp, i64, i32, i32, vp, vp],
     "sg_scatter_cols": [vp, i64, vp, i64, i32, i32, vp, i32, vp],

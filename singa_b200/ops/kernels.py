@@ -84,11 +84,19 @@ def ip_small_dgrad(dy, w, dx, M, K, N, grad_act=ACT_NONE, aux=None):
           dx.stride(0), _bf(dx), M, K, N)
 
 
-def ip_small_wgrad(x, dy, dw, M, K, N, db=None, accumulate=False):
-    """dw[K][N] (+)= x[M][K]^T . dy[M][N]; db[N] (+)= column sums of dy."""
-    assert dw.dtype == torch.float32 and (db is None or db.dtype == torch.float32)
+def ip_small_wgrad_workspace(M, K, device):
+    """Zeroed workspace for ``ip_small_wgrad`` (one per layer: calls that may overlap must not share it)."""
+    lib = _lib()
+    lib.sg_ip_small_wgrad_ws_bytes.restype = ctypes.c_longlong
+    nbytes = int(lib.sg_ip_small_wgrad_ws_bytes(int(M), int(K)))
+    return torch.zeros((nbytes + 3) // 4, dtype=torch.float32, device=device)
+
+
+def ip_small_wgrad(x, dy, dw, M, K, N, ws, db=None, accumulate=False):
+    """dw[K][N] (+)= x[M][K]^T . dy[M][N]; db[N] (+)= column sums of dy.  Deterministic (no atomics on the result)."""
+    assert dw.dtype == torch.float32 and (db is None or db.dtype == torch.float32) and ws.dtype == torch.float32
     _call("sg_ip_small_wgrad", x.data_ptr(), x.stride(0), _bf(x), dy.data_ptr(), dy.stride(0), _bf(dy), dw.data_ptr(),
-          dw.stride(0), native.ptr(db), M, K, N, 1 if accumulate else 0)
+          dw.stride(0), native.ptr(db), M, K, N, 1 if accumulate else 0, ws.data_ptr())
 
 
 def space_to_depth(x, xs, N, H, W, C, Hs, Ws, Cs, s, pad):

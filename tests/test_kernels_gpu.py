@@ -383,11 +383,16 @@ def test_ip_small_kernels(M, Kd, N, dtype):
     torch.testing.assert_close(dx.float(), dy[:, :N].float() @ w[:, :N].float().t(), **tol)
     dw = torch.full((Kd, ldn), float("nan"), device=DEV)
     db = torch.full((N,), float("nan"), device=DEV)
-    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, db=db)
+    ws = K().ip_small_wgrad_workspace(M, Kd, DEV)
+    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, ws, db=db)
     wref = x.float().t() @ dy[:, :N].float()
     bref = dy[:, :N].float().sum(0)
     torch.testing.assert_close(dw[:, :N], wref, rtol=1e-4, atol=1e-3)
     torch.testing.assert_close(db, bref, rtol=1e-4, atol=1e-3)
-    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, db=db, accumulate=True)
+    first = dw.clone()
+    K().ip_small_wgrad(x, dy[:, :N], dw[:, :N], M, Kd, N, ws, db=db, accumulate=True)
     torch.testing.assert_close(dw[:, :N], 2 * wref, rtol=1e-4, atol=2e-3)
     torch.testing.assert_close(db, 2 * bref, rtol=1e-4, atol=2e-3)
+    again = torch.full_like(dw, float("nan"))
+    K().ip_small_wgrad(x, dy[:, :N], again[:, :N], M, Kd, N, ws)       # same bits on every run (slice-ordered sums)
+    assert torch.equal(again[:, :N], first[:, :N])

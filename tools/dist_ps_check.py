@@ -8,6 +8,7 @@ with (the operand mirrors, or the fp32 values themselves where no mirror exists)
 0 only if all pass.
 
     torchrun ... tools/dist_ps_check.py [config] [--dtype fp32|bf16] [--steps N] [--no-graph]
+                                        [--delay-rank R --delay-ms T]   (stress: one rank always late)
 Environment: SINGA_B200_NVLS=0/1 selects peer loads / in-switch reduction for the fused push.
 """
 import argparse
@@ -20,7 +21,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def run(push_pull, world, rank, steps, batch, hidden, config="mnist_mlp", graph=True):
+def run(push_pull, world, rank, steps, batch, hidden, config="mnist_mlp", graph=True, delay=(-1, 0.0)):
     from singa_b200 import device
     from singa_b200.cluster import Cluster
     from singa_b200.models import configs
@@ -53,6 +54,10 @@ def run(push_pull, world, rank, steps, batch, hidden, config="mnist_mlp", graph=
     ex = w.executor
     for step in range(steps):
         ex.ticks += 1
+        if push_pull is not None and rank == delay[0] and delay[1] > 0:
+            # stress: this rank's whole step (its gradients, ready flags and pushes) starts late, so every other rank's
+            # push kernel sits in the rendezvous and every consumer of its shard in the version-flag acquire
+            torch.cuda._sleep(int(delay[1] * 1.9e6))
         ex.train_one_batch(step)
     torch.cuda.synchronize()
     if push_pull is not None:
@@ -76,6 +81,8 @@ def main():
     ap.add_argument("--dtype", default="fp32")
     ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--delay-rank", type=int, default=-1, help="stress: delay every step of this rank ...")
+    ap.add_argument("--delay-ms", type=float, default=0.0, help="... by this many milliseconds of device time")
     args = ap.parse_args()
     from singa_b200 import device
     device.set_context(f"cuda:{local}", "native", args.dtype)
@@ -87,7 +94,7 @@ def main():
     ok = True
     results = {}
     for pp in ("nccl", "fused"):
-        results[pp] = run(pp, world, rank, steps, batch, hidden, config, graph)
+        results[pp] = run(pp, world, rank, steps, batch, hidden, config, graph, (args.delay_rank, args.delay_ms))
         dist.barrier()
     # every rank must hold identical mirrors
     for pp, (mir, loss) in results.items():
@@ -125,7 +132,8 @@ def main():
                 (2e-3 if config == "mnist_mlp" else 5e-2)
             status = "PASS" if worst < lim else "FAIL"
             ok = ok and status == "PASS"
-            print(f"{status} {pp} [{config} {args.dtype} graph={graph} nvls={os.environ.get('SINGA_B200_NVLS', 'auto')}]: world={world} worst relative weight difference vs 1 process x batch "
+            stress = f" rank {args.delay_rank} late by {args.delay_ms} ms" if args.delay_rank >= 0 else ""
+            print(f"{status} {pp} [{config} {args.dtype} graph={graph} nvls={os.environ.get('SINGA_B200_NVLS', 'auto')}{stress}]: world={world} worst relative weight difference vs 1 process x batch "
                   f"{batch * world}: {worst:.3e} ({worst_k}); mean loss {loss:.4f} vs {ref_loss:.4f}")
         a, b = results["nccl"][0], results["fused"][0]
         worst = max(float((a[k] - b[k]).abs().max()) for k in a)
