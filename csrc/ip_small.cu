@@ -207,6 +207,19 @@ static int ips_smem(int K, int N, const char* who) {
   return static_cast<int>(bytes);
 }
 
+// 96 KB of dynamic shared memory must be allowed once per kernel and device
+static int ips_allow_smem(const void* kern, int which) {
+  static thread_local int done_dev[2] = {-1, -1};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (done_dev[which] == dev) return 0;
+  if (check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024),
+                 "cudaFuncSetAttribute(ip_small smem)"))
+    return 1;
+  done_dev[which] = dev;
+  return 0;
+}
+
 extern "C" int sg_ip_small_fwd(const void* x, long long ldx, int x_bf16, const void* w, long long ldw, int w_bf16,
                                const void* bias, int bias_bf16, void* y, long long ldy, int y_bf16, int M, int K, int N,
                                int act, void* stream) {
@@ -214,8 +227,7 @@ extern "C" int sg_ip_small_fwd(const void* x, long long ldx, int x_bf16, const v
              "sg_ip_small_fwd: needs 1..%d outputs", IPS_NMAX);
   const int smem = ips_smem(K, N, "sg_ip_small_fwd");
   if (smem < 0) return 2;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(ip_small_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; }
+  if (ips_allow_smem(reinterpret_cast<const void*>(ip_small_fwd_kernel), 0)) return 1;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   int grid = (M + 7) / 8;
   if (grid > 2 * num_sms()) grid = 2 * num_sms();
@@ -232,8 +244,7 @@ extern "C" int sg_ip_small_dgrad(const void* dy, long long lddy, int dy_bf16, co
   SG_REQUIRE(grad_act == SG_ACT_NONE || aux != nullptr, "sg_ip_small_dgrad: grad_act needs aux");
   const int smem = ips_smem(K, N, "sg_ip_small_dgrad");
   if (smem < 0) return 2;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(ip_small_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; }
+  if (ips_allow_smem(reinterpret_cast<const void*>(ip_small_dgrad_kernel), 1)) return 1;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   ip_small_dgrad_kernel<<<(M + IPS_RB - 1) / IPS_RB, 256, smem, s>>>(dy, lddy, dy_bf16, w, ldw, w_bf16, aux, ldaux, aux_bf16, grad_act, dx, lddx, dx_bf16, M, K, N);
   SG_CHECK_LAUNCH("ip_small_dgrad");
