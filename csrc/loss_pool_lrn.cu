@@ -1,4 +1,5 @@
 // Softmax-loss (fwd+bwd fused), pooling and LRN for channels-last (NHWC) bf16/fp32 activations.
+#include <cuda_bf16.h>
 #include <float.h>
 #include <stdint.h>
 
@@ -222,11 +223,102 @@ pool_bwd_row_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
   }
 }
 
+// bf16 max pooling on packed pairs (HMNMX2 / HSET2 / HFMA2): the generic row kernels unpack every element to fp32 and
+// were instruction bound at 23-26 % of the copy bandwidth (fp32: 63-76 %).  Same blocks and windows as above.  The
+// backward sum of the (at most MW*MW) matching windows is accumulated in bf16 — one rounding per extra term, and only
+// pixels shared by several windows that all have their maximum there have more than one term.
+struct Bf16x8 {
+  uint4 u;
+  __device__ __forceinline__ __nv_bfloat162& h(int q) { return reinterpret_cast<__nv_bfloat162*>(&u)[q]; }
+};
+
+template <int K>
+__global__ void __launch_bounds__(256)
+pool_max_fwd_row_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int H, int W, int C,
+                             int OH, int OW, int s, int pad) {
+  const int cv = C / 8;
+  const int n = blockIdx.x / OH, oy = blockIdx.x - n * OH;
+  const int y0 = oy * s - pad;
+  const __nv_bfloat16* xn = x + static_cast<long long>(n) * H * W * C;
+  __nv_bfloat16* yrow = y + static_cast<long long>(blockIdx.x) * OW * C;
+  Bf16x8 lowest;
+  lowest.u = make_uint4(0xFF7FFF7Fu, 0xFF7FFF7Fu, 0xFF7FFF7Fu, 0xFF7FFF7Fu);     // -3.39e38 in both halves
+  for (int j = threadIdx.x; j < OW * cv; j += blockDim.x) {
+    const int ox = j / cv, c = (j - ox * cv) * 8;
+    const int x0 = ox * s - pad;
+    Bf16x8 v[K * K];
+#pragma unroll
+    for (int a = 0; a < K; ++a)
+#pragma unroll
+      for (int b = 0; b < K; ++b) {
+        const int yy = y0 + a, xx = x0 + b;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+          v[a * K + b].u = *reinterpret_cast<const uint4*>(xn + (static_cast<long long>(yy) * W + xx) * C + c);
+        else
+          v[a * K + b] = lowest;
+      }
+    Bf16x8 acc = v[0];
+#pragma unroll
+    for (int w = 1; w < K * K; ++w)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc.h(q) = __hmax2(acc.h(q), v[w].h(q));
+    *reinterpret_cast<uint4*>(yrow + static_cast<long long>(ox) * C + c) = acc.u;
+  }
+}
+
+template <int MW>
+__global__ void __launch_bounds__(256)
+pool_max_bwd_row_bf16_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                             const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int H, int W, int C,
+                             int OH, int OW, int k, int s, int pad) {
+  const int cv = C / 8;
+  const int n = blockIdx.x / H, yy = blockIdx.x - n * H;
+  const int oy_lo = max(0, (yy + pad - k + s) / s), oy_hi = min(OH - 1, (yy + pad) / s);
+  const long long obase = static_cast<long long>(n) * OH * OW * C;
+  const __nv_bfloat16* xrow = x + static_cast<long long>(blockIdx.x) * W * C;
+  __nv_bfloat16* dxrow = dx + static_cast<long long>(blockIdx.x) * W * C;
+  for (int j = threadIdx.x; j < W * cv; j += blockDim.x) {
+    const int xx = j / cv, c = (j - xx * cv) * 8;
+    const int ox_lo = max(0, (xx + pad - k + s) / s), ox_hi = min(OW - 1, (xx + pad) / s);
+    Bf16x8 xv, gv[MW * MW], yv[MW * MW];
+    bool live[MW * MW];
+    xv.u = *reinterpret_cast<const uint4*>(xrow + static_cast<long long>(xx) * C + c);
+#pragma unroll
+    for (int a = 0; a < MW; ++a)
+#pragma unroll
+      for (int b = 0; b < MW; ++b) {
+        const int oy = oy_lo + a, ox = ox_lo + b;
+        live[a * MW + b] = oy <= oy_hi && ox <= ox_hi;
+        if (live[a * MW + b]) {
+          const long long o = obase + (static_cast<long long>(oy) * OW + ox) * C + c;
+          gv[a * MW + b].u = *reinterpret_cast<const uint4*>(dy + o);
+          yv[a * MW + b].u = *reinterpret_cast<const uint4*>(y + o);
+        }
+      }
+    Bf16x8 g;
+    g.u = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+    for (int w = 0; w < MW * MW; ++w)
+      if (live[w]) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) g.h(q) = __hfma2(__heq2(yv[w].h(q), xv.h(q)), gv[w].h(q), g.h(q));
+      }
+    *reinterpret_cast<uint4*>(dxrow + static_cast<long long>(xx) * C + c) = g.u;
+  }
+}
+
 template <typename T>
 static bool launch_pool_fwd_rows(const T* x, T* y, int N, int H, int W, int C, int OH, int OW, int k, int st, int pad,
                                  int is_max, cudaStream_t s) {
   const int grid = N * OH;
 #define SG_POOL_F(K_, M_) pool_fwd_row_kernel<T, K_, M_><<<grid, 256, 0, s>>>(x, y, H, W, C, OH, OW, st, pad)
+  if (sizeof(T) == 2 && is_max && (k == 2 || k == 3)) {
+    const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+    __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y);
+    if (k == 2) pool_max_fwd_row_bf16_kernel<2><<<grid, 256, 0, s>>>(xb, yb, H, W, C, OH, OW, st, pad);
+    else pool_max_fwd_row_bf16_kernel<3><<<grid, 256, 0, s>>>(xb, yb, H, W, C, OH, OW, st, pad);
+    return true;
+  }
   if (k == 2) { if (is_max) SG_POOL_F(2, true); else SG_POOL_F(2, false); return true; }
   if (k == 3) { if (is_max) SG_POOL_F(3, true); else SG_POOL_F(3, false); return true; }
 #undef SG_POOL_F
@@ -238,6 +330,16 @@ static bool launch_pool_bwd_rows(const T* x, const T* y, const T* dy, T* dx, int
                                  int k, int st, int pad, int is_max, cudaStream_t s) {
   const int grid = N * H, mw = (k + st - 1) / st;
 #define SG_POOL_B(W_, M_) pool_bwd_row_kernel<T, W_, M_><<<grid, 256, 0, s>>>(x, y, dy, dx, H, W, C, OH, OW, k, st, pad)
+  if (sizeof(T) == 2 && is_max && mw >= 1 && mw <= 3) {
+    const __nv_bfloat16* xb = reinterpret_cast<const __nv_bfloat16*>(x);
+    const __nv_bfloat16* yb = reinterpret_cast<const __nv_bfloat16*>(y);
+    const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(dy);
+    __nv_bfloat16* db = reinterpret_cast<__nv_bfloat16*>(dx);
+    if (mw == 1) pool_max_bwd_row_bf16_kernel<1><<<grid, 256, 0, s>>>(xb, yb, gb, db, H, W, C, OH, OW, k, st, pad);
+    else if (mw == 2) pool_max_bwd_row_bf16_kernel<2><<<grid, 256, 0, s>>>(xb, yb, gb, db, H, W, C, OH, OW, k, st, pad);
+    else pool_max_bwd_row_bf16_kernel<3><<<grid, 256, 0, s>>>(xb, yb, gb, db, H, W, C, OH, OW, k, st, pad);
+    return true;
+  }
   if (mw == 1) { if (is_max) SG_POOL_B(1, true); else SG_POOL_B(1, false); return true; }
   if (mw == 2) { if (is_max) SG_POOL_B(2, true); else SG_POOL_B(2, false); return true; }
   if (mw == 3) { if (is_max) SG_POOL_B(3, true); else SG_POOL_B(3, false); return true; }
