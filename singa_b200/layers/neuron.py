@@ -154,6 +154,11 @@ class InnerProductLayer(NeuronLayer):
         # weight operand = the arena's mirror (or, fp32 on one GPU, the master values); when hdim is not a multiple
         # of 8 the arena stores the rows with a padded stride (ParamArena honours want_padded_ld): TMA-legal as is
         self.weight.want_padded_ld = True
+        # classifier-sized layers: workspace of the deterministic weight-gradient kernel (allocated here, not inside a
+        # step that may be under CUDA-graph capture)
+        self._ips_ws = None
+        if self.hdim <= 16 and self.batchsize >= 256 and dev.type == "cuda":
+            self._ips_ws = _K().ip_small_wgrad_workspace(self.batchsize, self.vdim, dev)
 
     def get_params(self):
         return [self.weight, self.bias] if self.bias_term else [self.weight]
@@ -194,7 +199,7 @@ class InnerProductLayer(NeuronLayer):
         forward GEMM itself has to wait for the parameter server's version flags (non-rotated fused pull)."""
         # measured: 0.394 -> 0.387 ms per MNIST step (batch 1000); no gain at batch 64-128 (LeNet, CIFAR-10), where a
         # single 128-row tile already covers the batch
-        return (self.hdim <= 16 and self.batchsize >= 256 and self.vdim * (self.hdim | 1) * 4 <= 96 * 1024
+        return (getattr(self, "_ips_ws", None) is not None and self.vdim * (self.hdim | 1) * 4 <= 96 * 1024
                 and self.pull_wait is None and os.environ.get("SINGA_B200_IP_SMALL", "1") != "0")
 
     def compute_feature(self, training):
@@ -232,8 +237,6 @@ class InnerProductLayer(NeuronLayer):
             K = _K()
             accumulate = getattr(self, "_accumulate_wgrad", False)
             if self._small():     # weight and bias gradient in one launch
-                if getattr(self, "_ips_ws", None) is None:
-                    self._ips_ws = K.ip_small_wgrad_workspace(self.batchsize, self.vdim, dy.device)
                 K.ip_small_wgrad(x, dy, self.weight.grad, self.batchsize, self.vdim, self.hdim, self._ips_ws,
                                  db=self.bias.grad if self.bias_term else None, accumulate=accumulate)
                 return

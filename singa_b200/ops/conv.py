@@ -140,6 +140,39 @@ class ConvPlan:
                       self.stride, self.pad, grad_act, aux2d)
 
 
+def s2d_filter_index(C: int, k: int, s: int, Cs: int) -> torch.Tensor:
+    """idx[j] = column of the reference filter layout [F][(c*k + ky)*k + kx] that column j of the space-to-depth filter
+    [F][(cs*ks + ty)*ks + tx] takes its value from (cs = (dy*s + dx)*C + c, ky = ty*s + dy, kx = tx*s + dx), or -1 for
+    taps beyond k and for the padding channels cs >= s*s*C."""
+    ks = (k + s - 1) // s
+    idx = torch.full((Cs * ks * ks,), -1, dtype=torch.int32)
+    for dy in range(s):
+        for dx in range(s):
+            for c in range(C):
+                cs = (dy * s + dx) * C + c
+                for ty in range(ks):
+                    for tx in range(ks):
+                        ky, kx = ty * s + dy, tx * s + dx
+                        if ky < k and kx < k:
+                            idx[(cs * ks + ty) * ks + tx] = (c * k + ky) * k + kx
+    return idx
+
+
+def space_to_depth_ref(x: torch.Tensor, s: int, pad: int, Hs: int, Ws: int, Cs: int) -> torch.Tensor:
+    """Plain-torch statement of ``sg_space_to_depth``: x [N,C,H,W] -> [N,Cs,Hs,Ws] with channel (dy*s + dx)*C + c of
+    pixel (Y, X) = x[n][c][Y*s + dy - pad][X*s + dx - pad] (zero outside)."""
+    N, C, H, W = x.shape
+    xp = torch.zeros(N, C, Hs * s, Ws * s, dtype=x.dtype, device=x.device)
+    h = min(H, Hs * s - pad)
+    w = min(W, Ws * s - pad)
+    xp[:, :, pad:pad + h, pad:pad + w] = x[:, :, :h, :w]
+    out = torch.zeros(N, Cs, Hs, Ws, dtype=x.dtype, device=x.device)
+    for dy in range(s):
+        for dx in range(s):
+            out[:, (dy * s + dx) * C:(dy * s + dx + 1) * C] = xp[:, :, dy::s, dx::s]
+    return out
+
+
 class S2dConvPlan:
     """k x k, stride s > 1 over C thin channels == ceil(k/s)^2, stride 1 over s*s*C channels of the space-to-depth
     image (taps beyond k are zero filters).  Same interface as ``ConvPlan`` for an input layer (no data gradient).
@@ -166,17 +199,7 @@ class S2dConvPlan:
         self.xs = torch.zeros(N, self.Hs, self.Ws, self.Cs, dtype=dtype, device=device)
         self.xs_cl = self.xs.permute(0, 3, 1, 2)          # [N, Cs, Hs, Ws] channels-last view for the inner plan
         ncol_in = self.Cs * self.ks * self.ks
-        idx = torch.full((ncol_in,), -1, dtype=torch.int32)
-        for dy in range(s):
-            for dx in range(s):
-                for c in range(C):
-                    cs = (dy * s + dx) * C + c
-                    for ty in range(self.ks):
-                        for tx in range(self.ks):
-                            ky, kx = ty * s + dy, tx * s + dx
-                            if ky < k and kx < k:
-                                idx[(cs * self.ks + ty) * self.ks + tx] = (c * k + ky) * k + kx
-        self.idx = idx.to(device)
+        self.idx = s2d_filter_index(C, k, s, self.Cs).to(device)
         self.w_inner = torch.zeros(F, ncol_in, dtype=torch.float32, device=device)
         self.dw_inner = torch.zeros(F, ncol_in, dtype=torch.float32, device=device)
 

@@ -320,3 +320,34 @@ def test_sharded_checkpoint_written_per_owner_and_resharded_on_load(tmp_path):
     with pytest.raises(FileNotFoundError):
         checkpoint.load(paths[0], w2.train_net, w2.pm)
     device.reset_context()
+
+
+@pytest.mark.parametrize("case", [(3, 11, 4, 0, 35), (3, 7, 2, 3, 31), (1, 5, 4, 1, 33)])
+def test_space_to_depth_convolution_identity(case):
+    """The re-statement behind ops/conv.py::S2dConvPlan: a k x k stride-s convolution equals a ceil(k/s)^2 stride-1
+    convolution of the space-to-depth image with the filter re-laid out through s2d_filter_index (CPU, fp64)."""
+    import torch.nn.functional as F_
+    from singa_b200.ops.conv import s2d_filter_index, space_to_depth_ref
+    C, k, s, pad, H = case
+    W, F, N = H - 2, 6, 2
+    torch.manual_seed(k)
+    x = torch.randn(N, C, H, W, dtype=torch.float64)
+    w = torch.randn(F, C * k * k, dtype=torch.float64)
+    ref = F_.conv2d(x, w.view(F, C, k, k), None, stride=s, padding=pad)
+    ks = (k + s - 1) // s
+    OH, OW = ref.shape[2], ref.shape[3]
+    Hs, Ws = OH + ks - 1, OW + ks - 1
+    Cs = (s * s * C + 3) // 4 * 4
+    idx = s2d_filter_index(C, k, s, Cs).long()
+    w_in = torch.where(idx >= 0, w[:, idx.clamp(min=0)], torch.zeros((), dtype=w.dtype))
+    xs = space_to_depth_ref(x, s, pad, Hs, Ws, Cs)
+    got = F_.conv2d(xs, w_in.view(F, Cs, ks, ks), None, stride=1, padding=0)
+    torch.testing.assert_close(got, ref)
+    # and back: the weight gradient of the inner convolution scatters onto the reference layout
+    dy = torch.randn_like(ref)
+    dw_ref = torch.nn.grad.conv2d_weight(x, (F, C, k, k), dy, stride=s, padding=pad).reshape(F, -1)
+    dw_in = torch.nn.grad.conv2d_weight(xs, (F, Cs, ks, ks), dy, stride=1, padding=0).reshape(F, -1)
+    dw = torch.zeros_like(dw_ref)
+    live = idx >= 0
+    dw[:, idx[live]] = dw_in[:, live]
+    torch.testing.assert_close(dw, dw_ref)
