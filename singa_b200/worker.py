@@ -563,7 +563,10 @@ class HogwildGroup:
     (src/worker/worker.cc:33-39) and ``ParamManager::UpdateParam`` either lets every thread update the shared
     Param without locks (hogwild, src/utils/param_manager.cc:165-167) or aggregates the threads' gradients under
     a mutex and applies one update with ``grad_scale = 1/shares`` (:169-190).  Each thread owns a replica of the
-    net (its own activations, gradients and data stream) whose parameters alias the master net's values.
+    net (its own activations, gradients and data stream) whose parameters alias the master net's values.  The
+    aggregated mode never blocks the host on the device: the mutex fixes the order in which the threads add their
+    gradients, a CUDA event per parameter makes each thread's stream wait for the previous add, and the thread that
+    arrives last launches the one update.
     """
 
     def __init__(self, worker: "Worker", nthreads: int, hogwild: bool):
@@ -577,6 +580,7 @@ class HogwildGroup:
             self.replicas.append(net)
         self._lock = threading.Lock()
         self._agg = {}
+        self._agg_evt = {}
         self._arrived = {}
         self.updates = 0
         self._cuda = ctx().device.type == "cuda"
@@ -624,19 +628,32 @@ class HogwildGroup:
                         self._apply(upd, step, o)
                         self.updates += 1
                     else:
-                        if self._cuda:                    # this thread's gradient must be complete before it is
-                            torch.cuda.current_stream().synchronize()   # summed on whichever stream gets the lock
+                        # aggregation without host synchronisation: the lock orders the threads on the host, and an
+                        # event per parameter carries that order to the device — every thread adds its gradient on its
+                        # OWN stream behind the previous thread's add (or update), into a buffer kept across steps
                         with self._lock:
-                            acc = self._agg.get(id(o))
-                            self._agg[id(o)] = p.grad.clone() if acc is None else acc.add_(p.grad)
-                            self._arrived[id(o)] = self._arrived.get(id(o), 0) + 1
-                            if self._arrived[id(o)] == self.nthreads:
-                                o.grad = self._agg.pop(id(o))
-                                self._arrived[id(o)] = 0
+                            key = id(o)
+                            st = torch.cuda.current_stream() if self._cuda else None
+                            if self._cuda and key in self._agg_evt:
+                                st.wait_event(self._agg_evt[key])
+                            acc = self._agg.get(key)
+                            if acc is None:
+                                acc = self._agg[key] = torch.empty_like(p.grad)
+                            n = self._arrived.get(key, 0)
+                            if n == 0:
+                                acc.copy_(p.grad)
+                            else:
+                                acc.add_(p.grad)
+                            self._arrived[key] = n + 1
+                            if n + 1 == self.nthreads:
+                                o.grad = acc
+                                self._arrived[key] = 0
                                 self._apply(upd, step, o, grad_scale=1.0 / self.nthreads)
                                 self.updates += 1
                             if self._cuda:
-                                torch.cuda.current_stream().synchronize()
+                                ev = torch.cuda.Event()
+                                ev.record(st)
+                                self._agg_evt[key] = ev
 
     def run(self, steps: int, start: int = 0) -> None:
         ths = [threading.Thread(target=self._thread, args=(t, steps, start)) for t in range(self.nthreads)]
